@@ -1,0 +1,46 @@
+"""Synthetic scene builders shared by tests and bench (inputs only; no compute).
+
+`cloth_sheet` reproduces the reference smoke-test sheet (multibody/gpu_mpm/cuda_mpm_test.cc:27-57):
+res x res vertices on a square of side `side` starting at (x0, y0, z), two triangles per quad with
+the reference's winding.  `stacked_sheets` is the SURVEY 8d cfg-2 scene: `n_sheets` such sheets,
+z from z0 in steps of dz, with a seeded xy jitter of U(-0.1, 0.1) * dx per sheet.
+"""
+import numpy as np
+
+SEED = 20261104
+
+
+def cloth_sheet(res=100, side=0.5, x0=0.25, y0=0.25, z=0.75, dtype=np.float64):
+    dx = side / res
+    i, j = np.meshgrid(np.arange(res), np.arange(res), indexing="ij")
+    pos = np.stack([x0 + i * dx, y0 + j * dx, np.full_like(i, z, dtype=np.float64)], axis=-1).reshape(-1, 3)
+    p = lambda a, b: a * res + b
+    ii, jj = np.meshgrid(np.arange(res - 1), np.arange(res - 1), indexing="ij")
+    ii, jj = ii.reshape(-1), jj.reshape(-1)
+    t0 = np.stack([p(ii, jj), p(ii + 1, jj), p(ii, jj + 1)], axis=-1)
+    t1 = np.stack([p(ii + 1, jj + 1), p(ii, jj + 1), p(ii + 1, jj)], axis=-1)
+    tri = np.stack([t0, t1], axis=1).reshape(-1, 3).astype(np.int32)
+    # the reference builds positions as T(0.25 + i * dx) with dx of type T
+    if np.dtype(dtype) == np.float32:
+        dxf = np.float32(np.float32(side) / np.float32(res))
+        pos = np.stack([(np.float64(x0) + i.astype(np.float64) * np.float64(dxf)),
+                        (np.float64(y0) + j.astype(np.float64) * np.float64(dxf)),
+                        np.full(i.shape, z, dtype=np.float64)], axis=-1).reshape(-1, 3)
+    pos = pos.astype(dtype)
+    vel = np.zeros_like(pos)
+    return pos, vel, tri
+
+
+def stacked_sheets(n_sheets, res=100, side=0.5, z0=0.15, dz=0.02, domain_bits=7, jitter=0.1, dtype=np.float64,
+                   seed=SEED, warm=False):
+    """Returns a list of (pos, vel, tri) -- one AddQRCloth call each."""
+    rng = np.random.default_rng(seed)
+    dx = 1.0 / (1 << domain_bits)
+    out = []
+    for s in range(n_sheets):
+        off = rng.uniform(-jitter, jitter, size=2) * dx
+        pos, vel, tri = cloth_sheet(res, side, 0.25 + off[0], 0.25 + off[1], z0 + s * dz, dtype)
+        if warm:
+            vel = rng.normal(0.0, 0.1, size=pos.shape).astype(dtype)
+        out.append((pos, vel, tri))
+    return out
