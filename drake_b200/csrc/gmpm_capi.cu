@@ -1,0 +1,227 @@
+// gmpm_capi.cu -- the extern "C" boundary of libgmpm_b200.so (include/gmpm_c.h).
+#include <new>
+#define GMPM_STR2(x) #x
+#define GMPM_STR(x) GMPM_STR2(x)
+
+#include "contact.cuh"
+#include "getters.cuh"
+#include "state.cuh"
+
+namespace {
+thread_local std::string g_last_error;
+
+template <typename Fn>
+int guarded(Fn&& fn) {
+  try {
+    fn();
+    return GMPM_OK;
+  } catch (const gmpm::CudaError& e) {
+    g_last_error = e.what();
+    if (e.code == cudaErrorNoDevice || e.code == cudaErrorInsufficientDriver) return GMPM_ERR_NO_DEVICE;
+    if (e.code == cudaErrorMemoryAllocation) return GMPM_ERR_OOM;
+    return GMPM_ERR_CUDA;
+  } catch (const std::out_of_range& e) {
+    g_last_error = e.what();
+    return GMPM_ERR_UNKNOWN_NAME;
+  } catch (const std::bad_alloc& e) {
+    g_last_error = e.what();
+    return GMPM_ERR_OOM;
+  } catch (const std::exception& e) {
+    g_last_error = e.what();
+    return GMPM_ERR_INVALID;
+  }
+}
+}  // namespace
+
+extern "C" {
+
+void gmpm_default_params(gmpm_params* p) {
+  p->domain_bits = 7;
+  p->boundary_cells = 3;
+  p->gravity_axis = 2;
+  p->device = -1;
+  p->youngs = 400000.;
+  p->poisson = .3;
+  p->density = 2000.;
+  p->gamma = 0.;
+  p->k_normal = 100000.;
+  p->v_blend = .8;
+  p->c_f = 0.;
+  p->sdf_friction = 0.3;
+  p->gravity = -9.8;
+  p->epsv = 1e-3;
+}
+const char* gmpm_last_error(void) { return g_last_error.c_str(); }
+const char* gmpm_version(void) { return "gmpm_b200 0.1 (sm_100a, CUDA " GMPM_STR(CUDART_VERSION) ")"; }
+int gmpm_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+uint32_t gmpm_morton_code(uint32_t x, uint32_t y, uint32_t z) { return gmpm::morton3(x, y, z); }
+uint32_t gmpm_cell_index(uint32_t x, uint32_t y, uint32_t z) { return gmpm::cell_key(x, y, z); }
+void gmpm_inverse_cell_index(uint32_t index, uint32_t* xyz) { gmpm::inverse_cell_key(index, xyz[0], xyz[1], xyz[2]); }
+
+int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_t n, int num_bit, uint32_t* keys_out,
+                          uint32_t* ids_out) {
+  return guarded([&] {
+    if (num_bit < 0 || num_bit > 32) throw std::invalid_argument("num_bit out of range");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+      throw gmpm::CudaError(cudaErrorNoDevice, "no CUDA device available (libgmpm_b200 has no CPU fallback)");
+    if (n == 0) return;
+    uint32_t *k[2], *v[2], *scratch;
+    for (int i = 0; i < 2; ++i) {
+      GMPM_CUDA(cudaMalloc(&k[i], n * 4));
+      GMPM_CUDA(cudaMalloc(&v[i], n * 4));
+    }
+    GMPM_CUDA(cudaMalloc(&scratch, gmpm::radix_sort_scratch_words(n) * 4));
+    GMPM_CUDA(cudaMemcpy(k[0], keys_in, n * 4, cudaMemcpyHostToDevice));
+    GMPM_CUDA(cudaMemcpy(v[0], ids_in, n * 4, cudaMemcpyHostToDevice));
+    const int r = gmpm::radix_sort_pairs(k, v, (uint32_t)n, num_bit, false, scratch, 0, [](const char*) {});
+    GMPM_CUDA(cudaDeviceSynchronize());
+    GMPM_CUDA(cudaMemcpy(keys_out, k[r], n * 4, cudaMemcpyDeviceToHost));
+    GMPM_CUDA(cudaMemcpy(ids_out, v[r], n * 4, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < 2; ++i) {
+      cudaFree(k[i]);
+      cudaFree(v[i]);
+    }
+    cudaFree(scratch);
+  });
+}
+
+#define GMPM_DEFINE(SUF, T)                                                                                    \
+  struct gmpm_state_##SUF {                                                                                    \
+    gmpm::State<T> st;                                                                                         \
+  };                                                                                                           \
+  int gmpm_create_##SUF(const gmpm_params* p, gmpm_state_##SUF** out) {                                        \
+    return guarded([&] {                                                                                       \
+      if (!out) throw std::invalid_argument("null out pointer");                                               \
+      *out = nullptr;                                                                                          \
+      gmpm_params prm;                                                                                         \
+      if (p) prm = *p; else gmpm_default_params(&prm);                                                         \
+      auto* s = new gmpm_state_##SUF();                                                                        \
+      try {                                                                                                    \
+        s->st.init(prm);                                                                                       \
+      } catch (...) {                                                                                          \
+        delete s;                                                                                              \
+        throw;                                                                                                 \
+      }                                                                                                        \
+      *out = s;                                                                                                \
+    });                                                                                                        \
+  }                                                                                                            \
+  int gmpm_destroy_##SUF(gmpm_state_##SUF* s) {                                                                \
+    return guarded([&] {                                                                                       \
+      if (!s) return;                                                                                          \
+      s->st.destroy();                                                                                         \
+      delete s;                                                                                                \
+    });                                                                                                        \
+  }                                                                                                            \
+  int gmpm_add_qr_cloth_##SUF(gmpm_state_##SUF* s, const T* pos, const T* vel, size_t nv, const int* tri,       \
+                              size_t nt) {                                                                     \
+    return guarded([&] { s->st.add_qr_cloth(pos, vel, nv, tri, nt); });                                        \
+  }                                                                                                            \
+  int gmpm_finalize_##SUF(gmpm_state_##SUF* s) { return guarded([&] { s->st.finalize(); }); }                  \
+  int gmpm_rebuild_mapping_##SUF(gmpm_state_##SUF* s, int sort) {                                              \
+    return guarded([&] { s->st.rebuild_mapping(sort != 0); });                                                 \
+  }                                                                                                            \
+  int gmpm_calc_fem_##SUF(gmpm_state_##SUF* s, T dt) { return guarded([&] { s->st.calc_fem(dt); }); }          \
+  int gmpm_p2g_##SUF(gmpm_state_##SUF* s, T dt) { return guarded([&] { s->st.p2g(dt); }); }                    \
+  int gmpm_update_grid_##SUF(gmpm_state_##SUF* s, int bc) { return guarded([&] { s->st.update_grid(bc); }); }  \
+  int gmpm_g2p_##SUF(gmpm_state_##SUF* s, T dt) { return guarded([&] { s->st.g2p(dt); }); }                    \
+  int gmpm_sync_##SUF(gmpm_state_##SUF* s) { return guarded([&] { s->st.sync(); }); }                          \
+  int gmpm_sync_particle_state_to_cpu_##SUF(gmpm_state_##SUF* s, T* out) {                                     \
+    return guarded([&] { s->st.positions_to_host(out); });                                                     \
+  }                                                                                                            \
+  int gmpm_copy_contact_pairs_##SUF(gmpm_state_##SUF* s, size_t n, const uint32_t* mpm_id,                     \
+                                    const uint32_t* rigid_id, const T* dist, const T* normal, const T* pos,    \
+                                    const T* rigid_v, const T* rigid_p) {                                      \
+    return guarded([&] { s->st.copy_contact_pairs(n, mpm_id, rigid_id, dist, normal, pos, rigid_v, rigid_p); });\
+  }                                                                                                            \
+  int gmpm_update_contact_##SUF(gmpm_state_##SUF* s, T dt, T mu, T stiffness, T damping, int exact, int max_it,\
+                                gmpm_contact_stats* stats) {                                                   \
+    return guarded([&] { s->st.update_contact(dt, mu, stiffness, damping, exact != 0, max_it, stats); });      \
+  }                                                                                                            \
+  int gmpm_reallocate_external_bodies_##SUF(gmpm_state_##SUF* s, size_t n) {                                   \
+    return guarded([&] { s->st.reallocate_external_bodies(n); });                                              \
+  }                                                                                                            \
+  int gmpm_external_body_force_to_host_##SUF(gmpm_state_##SUF* s, T* tau, T* f) {                              \
+    return guarded([&] { s->st.external_body_force_to_host(tau, f); });                                        \
+  }                                                                                                            \
+  int gmpm_dump_cpu_state_##SUF(gmpm_state_##SUF* s, T* vert_pos, int* tri) {                                  \
+    return guarded([&] { s->st.dump_cpu_state(vert_pos, tri); });                                              \
+  }                                                                                                            \
+  size_t gmpm_n_verts_##SUF(const gmpm_state_##SUF* s) { return s->st.n_verts; }                               \
+  size_t gmpm_n_faces_##SUF(const gmpm_state_##SUF* s) { return s->st.n_faces; }                               \
+  size_t gmpm_n_particles_##SUF(const gmpm_state_##SUF* s) { return s->st.N; }                                 \
+  size_t gmpm_n_cells_##SUF(const gmpm_state_##SUF* s) { return s->st.k.n_cells; }                             \
+  size_t gmpm_num_contacts_##SUF(const gmpm_state_##SUF* s) { return s->st.n_contacts; }                       \
+  int gmpm_grid_touched_cnt_host_##SUF(gmpm_state_##SUF* s, uint32_t* out) {                                   \
+    return guarded([&] { *out = s->st.touched_count_host(); });                                                \
+  }                                                                                                            \
+  int gmpm_read_##SUF(gmpm_state_##SUF* s, const char* name, void* out, size_t cap, size_t* written) {         \
+    return guarded([&] {                                                                                       \
+      const size_t b = s->st.read(name, out, cap);                                                             \
+      if (written) *written = b;                                                                               \
+    });                                                                                                        \
+  }                                                                                                            \
+  int gmpm_run_substeps_##SUF(gmpm_state_##SUF* s, int n, T dt, int bc, int sort_every) {                      \
+    return guarded([&] { s->st.run_substeps(n, dt, bc, sort_every); });                                        \
+  }                                                                                                            \
+  uint64_t gmpm_kernel_launches_##SUF(const gmpm_state_##SUF* s) { return s->st.launches; }                    \
+  int gmpm_set_profiling_##SUF(gmpm_state_##SUF* s, int on) {                                                  \
+    return guarded([&] {                                                                                       \
+      s->st.sync();                                                                                            \
+      s->st.prof.reset();                                                                                      \
+      s->st.prof.on = on != 0;                                                                                 \
+    });                                                                                                        \
+  }                                                                                                            \
+  int gmpm_kernel_time_##SUF(gmpm_state_##SUF* s, const char* prefix, double* ms, uint64_t* launches) {        \
+    return guarded([&] {                                                                                       \
+      s->st.sync();                                                                                            \
+      double t = 0;                                                                                            \
+      uint64_t c = 0;                                                                                          \
+      const std::string pre(prefix ? prefix : "");                                                             \
+      for (auto& kv : s->st.prof.acc)                                                                          \
+        if (kv.first.compare(0, pre.size(), pre) == 0) {                                                       \
+          t += kv.second.first;                                                                                \
+          c += kv.second.second;                                                                               \
+        }                                                                                                      \
+      if (ms) *ms = t;                                                                                         \
+      if (launches) *launches = c;                                                                             \
+    });                                                                                                        \
+  }                                                                                                            \
+  size_t gmpm_profile_report_##SUF(gmpm_state_##SUF* s, char* buf, size_t cap) {                               \
+    std::string r;                                                                                             \
+    if (guarded([&] {                                                                                          \
+          s->st.sync();                                                                                        \
+          char line[256];                                                                                      \
+          for (auto& kv : s->st.prof.acc) {                                                                    \
+            snprintf(line, sizeof(line), "%s %.6f %llu\n", kv.first.c_str(), kv.second.first,                  \
+                     (unsigned long long)kv.second.second);                                                    \
+            r += line;                                                                                         \
+          }                                                                                                    \
+        }) != GMPM_OK)                                                                                         \
+      return 0;                                                                                                \
+    if (buf && cap) {                                                                                          \
+      const size_t n = r.size() < cap - 1 ? r.size() : cap - 1;                                                \
+      memcpy(buf, r.data(), n);                                                                                \
+      buf[n] = 0;                                                                                              \
+    }                                                                                                          \
+    return r.size() + 1;                                                                                       \
+  }                                                                                                            \
+  size_t gmpm_device_bytes_##SUF(const gmpm_state_##SUF* s) { return s->st.device_bytes; }                     \
+  int gmpm_block_counts_##SUF(gmpm_state_##SUF* s, uint32_t* pb, uint32_t* tb) {                               \
+    return guarded([&] {                                                                                       \
+      if (pb) *pb = s->st.pblock_count_host();                                                                 \
+      if (tb) *tb = s->st.touched_count_host();                                                                \
+    });                                                                                                        \
+  }
+
+GMPM_DEFINE(f32, float)
+GMPM_DEFINE(f64, double)
+
+}  // extern "C"

@@ -1,0 +1,706 @@
+// kernels.cuh -- the per-timestep MPM kernels of libgmpm_b200 (sm_100a).
+//
+// Data layout (DESIGN.md "Data layout in HBM"):
+//   particles : planar SoA by PHYSICAL slot: pos[3][N] vel[3][N] C[9][N] vol[N] pid[N], double
+//               buffered; forces[3][N], taus[9][N] by slot.  slot_of_pid[N] is the inverse of pid[].
+//   faces     : planar by face id: tri[3][F] (original particle ids), F[9][F], Dm_inv[4][F].
+//   binning   : key[N] (block-major Morton cell key of every slot), order[N] = slots sorted by key,
+//               per-particle-block ranges pb_start/pb_end[n_blocks], compact list pb_list[].
+//   grid      : dense, block-major, channel-planar inside each 4^3 block:
+//               g_mass[b*64+l], g_vel[(b*3+d)*64+l] (momentum after P2G, velocity after update),
+//               g_vstar likewise.  P2G tiles: tiles[t][4][216] (6^3 nodes of particle block t).
+//
+// Every kernel cites the reference kernel (multibody/gpu_mpm/cuda_mpm_kernels.cuh) it replaces.
+#pragma once
+#include "common.cuh"
+#include "math.cuh"
+
+namespace gmpm {
+
+constexpr int kThreads = 256;
+
+// Device-resident counters (no host round trips inside a substep).
+struct DevCounters {
+  uint32_t n_pblocks;      // particle blocks of the current binning
+  uint32_t n_touched;      // touched grid blocks of the current P2G
+  uint32_t n_touched_prev; // ... of the previous P2G (for stale-block cleaning)
+  uint32_t work_p2g;       // dynamic work queues of the persistent kernels
+  uint32_t work_g2p;
+  uint32_t work_grid;
+  uint32_t grid_dofs;      // contact solve
+  uint32_t pad;
+};
+
+// Rolls the touched-block list and resets the P2G work queue (device side, no host round trip).
+__global__ void p2g_prologue_kernel(DevCounters* ctr) {
+  ctr->n_touched_prev = ctr->n_touched;
+  ctr->n_touched = 0;
+  ctr->work_p2g = 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Setup: rest shape, F = Q, volumes (replaces initialize_fem_state_kernel, :13-70).
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void init_fem_state_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ tri, T* pos, T* vel,
+                                      T* vol, T* Dm_inv, T* Fd, T dx) {
+  const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= n_faces) return;
+  const int v0 = tri[f], v1 = tri[n_faces + f], v2 = tri[2 * n_faces + f];  // slots == pids at setup
+  T x0[3], x1[3], x2[3];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    x0[d] = pos[d * N + v0];
+    x1[d] = pos[d * N + v1];
+    x2[d] = pos[d * N + v2];
+    pos[d * N + f] = (x0[d] + x1[d] + x2[d]) / T(3);
+    vel[d * N + f] = (vel[d * N + v0] + vel[d * N + v1] + vel[d * N + v2]) / T(3);
+  }
+  T D0[3], D1[3];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    D0[d] = x1[d] - x0[d];
+    D1[d] = x2[d] - x0[d];
+  }
+  const T Ds[6] = {D0[0], D1[0], D0[1], D1[1], D0[2], D1[2]};
+  T Q[9], R[6];
+  qr3<T, 2>(Ds, Q, R);
+  const T Dm[4] = {R[0], R[1], T(0), R[3]};
+  T Dmi[4];
+  inverse2(Dm, Dmi);
+#pragma unroll
+  for (int e = 0; e < 4; ++e) Dm_inv[e * n_faces + f] = Dmi[e];
+#pragma unroll
+  for (int e = 0; e < 9; ++e) Fd[e * n_faces + f] = Q[e];
+  const T cx = D0[1] * D1[2] - D1[1] * D0[2];
+  const T cy = D0[2] * D1[0] - D1[2] * D0[0];
+  const T cz = D0[0] * D1[1] - D1[0] * D0[1];
+  const T v4 = tsqrt(cx * cx + cy * cy + cz * cz) / T(8) * dx;
+  atomicAdd(&vol[f], v4);
+  atomicAdd(&vol[v0], v4);
+  atomicAdd(&vol[v1], v4);
+  atomicAdd(&vol[v2], v4);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Keys (replaces compute_base_cell_node_index_kernel, :365-382).  One key per physical slot.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void compute_keys_kernel(uint32_t N, const T* __restrict__ pos, uint32_t* __restrict__ key,
+                                    Consts<T> k) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const uint32_t bx = base_node(pos[i], k.dx_inv, k.domain_size);
+  const uint32_t by = base_node(pos[N + i], k.dx_inv, k.domain_size);
+  const uint32_t bz = base_node(pos[2 * N + i], k.dx_inv, k.domain_size);
+  key[i] = cell_key(bx, by, bz);
+}
+
+// Visible-order keys for the reference-compatible sort bookkeeping: vis_key[v] = key[slot(v)].
+__global__ void gather_visible_keys_kernel(uint32_t N, const uint32_t* __restrict__ key,
+                                           const int* __restrict__ pid_of_vis, const int* __restrict__ slot_of_pid,
+                                           uint32_t* __restrict__ vis_key, uint32_t* __restrict__ vis_id) {
+  const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= N) return;
+  vis_key[v] = key[slot_of_pid[pid_of_vis[v]]];
+  vis_id[v] = v;
+}
+
+// After the reference-compatible stable sort: permute the visible order
+// (the integer part of compute_sorted_state_kernel, :384-416: pids and index_mappings).
+__global__ void permute_visible_kernel(uint32_t N, const uint32_t* __restrict__ sort_ids,
+                                       const int* __restrict__ pid_of_vis_old, int* __restrict__ pid_of_vis_new,
+                                       int* __restrict__ vis_of_pid) {
+  const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= N) return;
+  const int p = pid_of_vis_old[sort_ids[v]];
+  pid_of_vis_new[v] = p;
+  vis_of_pid[p] = (int)v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Binning: per-particle-block ranges of the key-sorted order + compact list of particle blocks.
+// ------------------------------------------------------------------------------------------------
+__global__ void build_pblocks_kernel(uint32_t N, const uint32_t* __restrict__ sorted_key, uint32_t epoch,
+                                     uint32_t* __restrict__ pb_start, uint32_t* __restrict__ pb_end,
+                                     uint32_t* __restrict__ pb_epoch, uint32_t* __restrict__ pb_tile,
+                                     uint32_t* __restrict__ pb_list, DevCounters* ctr) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool in = i < N;
+  uint32_t b = 0;
+  bool head = false;
+  if (in) {
+    b = sorted_key[i] >> 6;
+    head = (i == 0) || ((sorted_key[i - 1] >> 6) != b);
+    const bool tail = (i + 1 == N) || ((sorted_key[i + 1] >> 6) != b);
+    if (head) pb_start[b] = i;
+    if (tail) pb_end[b] = i + 1;
+  }
+  // warp-aggregated append of the heads
+  const uint32_t m = __ballot_sync(kFullMask, head);
+  if (m) {
+    const int lane = threadIdx.x & 31;
+    uint32_t base = 0;
+    if (lane == (__ffs(m) - 1)) base = atomicAdd(&ctr->n_pblocks, (uint32_t)__popc(m));
+    base = __shfl_sync(kFullMask, base, __ffs(m) - 1);
+    if (head) {
+      const uint32_t t = base + __popc(m & ((1u << lane) - 1u));
+      pb_list[t] = b;
+      pb_tile[b] = t;
+      pb_epoch[b] = epoch;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Constitutive update (replaces calc_fem_state_and_force_kernel, :183-294).  One thread per face.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(128)
+fem_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ tri, const int* __restrict__ slot_of_pid,
+           const T* __restrict__ vol, const T* __restrict__ C, const T* __restrict__ Dm_inv, T* __restrict__ pos,
+           T* __restrict__ vel, T* __restrict__ Fd, T* __restrict__ forces, T* __restrict__ taus,
+           uint32_t* __restrict__ key, T dt, Consts<T> k) {
+  const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= n_faces) return;
+  const int sf = slot_of_pid[f];
+  const int s0 = slot_of_pid[tri[f]], s1 = slot_of_pid[tri[n_faces + f]], s2 = slot_of_pid[tri[2 * n_faces + f]];
+  T x0[3], x1[3], x2[3], xc[3];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    x0[d] = pos[d * N + s0];
+    x1[d] = pos[d * N + s1];
+    x2[d] = pos[d * N + s2];
+    xc[d] = (x0[d] + x1[d] + x2[d]) / T(3);
+    pos[d * N + sf] = xc[d];
+    vel[d * N + sf] = (vel[d * N + s0] + vel[d * N + s1] + vel[d * N + s2]) / T(3);
+  }
+  // the face particle moved: refresh its cell key (binning happens after this kernel)
+  key[sf] = cell_key(base_node(xc[0], k.dx_inv, k.domain_size), base_node(xc[1], k.dx_inv, k.domain_size),
+                     base_node(xc[2], k.dx_inv, k.domain_size));
+  T F[9], Cm[9];
+#pragma unroll
+  for (int e = 0; e < 9; ++e) {
+    F[e] = Fd[e * n_faces + f];
+    Cm[e] = C[e * N + sf];
+  }
+  T ctF[9];
+  ctF[0] = F[0];
+  ctF[1] = F[1];
+  ctF[2] = (T(1) + dt * Cm[0]) * F[2] + dt * Cm[1] * F[5] + dt * Cm[2] * F[8];
+  ctF[3] = F[3];
+  ctF[4] = F[4];
+  ctF[5] = dt * Cm[3] * F[2] + (T(1) + dt * Cm[4]) * F[5] + dt * Cm[5] * F[8];
+  ctF[6] = F[6];
+  ctF[7] = F[7];
+  ctF[8] = dt * Cm[6] * F[2] + dt * Cm[7] * F[5] + (T(1) + dt * Cm[8]) * F[8];
+  cloth_project_strain(k, ctF);
+
+  T Dmi[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) Dmi[e] = Dm_inv[e * n_faces + f];
+  // in-plane columns: ds * Dm^-1
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    const T a = x1[d] - x0[d], b = x2[d] - x0[d];
+    ctF[d * 3 + 0] = a * Dmi[0] + b * Dmi[2];
+    ctF[d * 3 + 1] = a * Dmi[1] + b * Dmi[3];
+  }
+#pragma unroll
+  for (int e = 0; e < 9; ++e) Fd[e * n_faces + f] = ctF[e];
+
+  T VP[9];
+  cloth_pk1(k, ctF, VP);
+  const T volume = vol[sf];
+#pragma unroll
+  for (int e = 0; e < 9; ++e) VP[e] *= volume;
+  // tau = V * P[:,2] (x) F[:,2]
+#pragma unroll
+  for (int a = 0; a < 3; ++a)
+#pragma unroll
+    for (int b = 0; b < 3; ++b) taus[(a * 3 + b) * N + sf] = VP[a * 3 + 2] * ctF[b * 3 + 2];
+  // grad_N = Dm^-T * [-1 1 0; -1 0 1]
+  T gN[6];
+  gN[0] = Dmi[0] * T(-1) + Dmi[2] * T(-1);
+  gN[1] = Dmi[0] * T(1) + Dmi[2] * T(0);
+  gN[2] = Dmi[0] * T(0) + Dmi[2] * T(1);
+  gN[3] = Dmi[1] * T(-1) + Dmi[3] * T(-1);
+  gN[4] = Dmi[1] * T(1) + Dmi[3] * T(0);
+  gN[5] = Dmi[1] * T(0) + Dmi[3] * T(1);
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    const T p0 = VP[d * 3 + 0], p1 = VP[d * 3 + 1];
+    atomicAdd(&forces[d * N + s0], -(p0 * gN[0] + p1 * gN[3]));
+    atomicAdd(&forces[d * N + s1], -(p0 * gN[1] + p1 * gN[4]));
+    atomicAdd(&forces[d * N + s2], -(p0 * gN[2] + p1 * gN[5]));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// P2G (replaces particle_to_grid_kernel :418-543 and clean_grid_kernel :585-602).
+//
+// One WARP per particle block (4^3 base cells).  The warp owns a private 6^3 x 4 shared-memory
+// tile, so there are no atomics and no barriers, and the summation order is fixed (run-to-run
+// reproducible).  Two alternating phases over batches of 32 particles of the block:
+//   (a) lanes = particles: coalesced loads through `order`, per-particle quantities to smem:
+//       the 9 one-dimensional B-spline weights, mass, a' = m v + m g dt + f dt - (B dx) fx, B dx;
+//   (b) lanes = the 27 stencil nodes: each lane accumulates its node's 4 channels in registers over
+//       a run of particles with the same base cell (the order is sorted by cell key), then adds
+//       the run total to the tile (distinct addresses across lanes -> plain read-modify-write).
+// The tile is written to tiles[t][4][216]; grid_assemble_update sums the <= 8 tiles that overlap
+// each grid block.  Touched grid blocks are appended to a device list (epoch-stamped, no flags scan).
+// ------------------------------------------------------------------------------------------------
+constexpr int kP2GWarps = 4;
+constexpr int kWStride = 10;  // 9 weights + pad (doubles/floats per particle)
+constexpr int kVStride = 14;  // m, a'[3], Bdx[9], pad -> 16-byte aligned rows
+
+template <typename T>
+struct P2GSmem {
+  T tile[kP2GWarps][4][kTileNodes];
+  T sw[kP2GWarps][32][kWStride];
+  T sv[kP2GWarps][32][kVStride];
+  int scell[kP2GWarps][32];
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kP2GWarps * 32)
+p2g_tile_kernel(uint32_t N, uint32_t n_faces, const uint32_t* __restrict__ order,
+                const uint32_t* __restrict__ sorted_key, const uint32_t* __restrict__ pb_list,
+                const uint32_t* __restrict__ pb_start, const uint32_t* __restrict__ pb_end,
+                const T* __restrict__ pos, const T* __restrict__ vel, const T* __restrict__ vol,
+                const T* __restrict__ C, const int* __restrict__ pid, const T* __restrict__ forces,
+                const T* __restrict__ taus, T* __restrict__ tiles, uint32_t* __restrict__ touched_epoch,
+                uint32_t* __restrict__ touched_list, uint32_t epoch, DevCounters* ctr, T dt, Consts<T> k) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  P2GSmem<T>& sm = *reinterpret_cast<P2GSmem<T>*>(smem_raw);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  T* tile = &sm.tile[warp][0][0];
+  const uint32_t n_pb = ctr->n_pblocks;
+  const int ni = lane / 9, nj = (lane / 3) % 3, nk = lane % 3;  // node of this lane (lane < 27)
+  const bool node_lane = lane < 27;
+  const T fi = T(ni), fj = T(nj), fk = T(nk);
+  const uint32_t blocks_per_axis = (uint32_t)k.domain_size >> 2;
+
+  for (;;) {
+    uint32_t t = 0;
+    if (lane == 0) t = atomicAdd(&ctr->work_p2g, 1u);
+    t = __shfl_sync(kFullMask, t, 0);
+    if (t >= n_pb) break;
+    const uint32_t blk = pb_list[t];
+    const uint32_t begin = pb_start[blk], end = pb_end[blk];
+    for (int i = lane; i < 4 * kTileNodes; i += 32) tile[i] = T(0);
+    uint32_t reach = 0;
+    T acc0 = T(0), acc1 = T(0), acc2 = T(0), acc3 = T(0);
+    int cur_cell = -1;
+    __syncwarp();
+
+    for (uint32_t p0 = begin; p0 < end; p0 += 32) {
+      // ---- phase (a): lanes = particles
+      const uint32_t i = p0 + lane;
+      if (i < end) {
+        const uint32_t s = order[i];
+        const uint32_t key = sorted_key[i];
+        const T px = pos[s], py = pos[N + s], pz = pos[2 * N + s];
+        const uint32_t bx = base_node(px, k.dx_inv, k.domain_size);
+        const uint32_t by = base_node(py, k.dx_inv, k.domain_size);
+        const uint32_t bz = base_node(pz, k.dx_inv, k.domain_size);
+        const T fx[3] = {px * k.dx_inv - T(bx), py * k.dx_inv - T(by), pz * k.dx_inv - T(bz)};
+        T* w = &sm.sw[warp][lane][0];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+          w[0 * 3 + d] = T(0.5) * (T(1.5) - fx[d]) * (T(1.5) - fx[d]);
+          w[1 * 3 + d] = T(0.75) - (fx[d] - T(1)) * (fx[d] - T(1));
+          w[2 * 3 + d] = T(0.5) * (fx[d] - T(0.5)) * (fx[d] - T(0.5));
+        }
+        const T mass = vol[s] * k.density;
+        T B[9];
+        const bool is_face = (uint32_t)pid[s] < n_faces;
+#pragma unroll
+        for (int e = 0; e < 9; ++e) B[e] = C[e * N + s] * mass;
+        T a[3] = {mass * vel[s], mass * vel[N + s], mass * vel[2 * N + s]};
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+          if (d == k.gravity_axis) a[d] += mass * k.gravity * dt;
+        if (is_face) {  // stress lives on face particles only (taus of vertices are zero)
+          const T cs = -dt * k.d_inv;
+#pragma unroll
+          for (int e = 0; e < 9; ++e) B[e] += cs * taus[e * N + s];
+        } else {        // nodal forces live on vertex particles only
+#pragma unroll
+          for (int d = 0; d < 3; ++d) a[d] += forces[d * N + s] * dt;
+        }
+        T* v = &sm.sv[warp][lane][0];
+        v[0] = mass;
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+          const T b0 = B[d * 3 + 0] * k.dx, b1 = B[d * 3 + 1] * k.dx, b2 = B[d * 3 + 2] * k.dx;
+          v[4 + d * 3 + 0] = b0;
+          v[4 + d * 3 + 1] = b1;
+          v[4 + d * 3 + 2] = b2;
+          v[1 + d] = a[d] - (b0 * fx[0] + b1 * fx[1] + b2 * fx[2]);
+        }
+        sm.scell[warp][lane] = (int)(key & 63u);
+        // which neighbour blocks (+x,+y,+z combinations) does this stencil reach
+        const uint32_t ox = (bx & 3u) >= 2u, oy = (by & 3u) >= 2u, oz = (bz & 3u) >= 2u;
+        uint32_t r = 1u;  // bit (dx*4+dy*2+dz) per reached neighbour; delta = 0 always
+        if (ox) r |= r << 4;
+        if (oy) r |= r << 2;
+        if (oz) r |= r << 1;
+        reach |= r;
+      }
+      __syncwarp();
+      // ---- phase (b): lanes = stencil nodes
+      const int cnt = (int)min(32u, end - p0);
+      for (int q = 0; q < cnt; ++q) {
+        const int c = sm.scell[warp][q];
+        if (c != cur_cell) {
+          if (cur_cell >= 0 && node_lane) {
+            const int n = (((cur_cell >> 4) & 3) + ni) * 36 + (((cur_cell >> 2) & 3) + nj) * 6 + ((cur_cell & 3) + nk);
+            tile[0 * kTileNodes + n] += acc0;
+            tile[1 * kTileNodes + n] += acc1;
+            tile[2 * kTileNodes + n] += acc2;
+            tile[3 * kTileNodes + n] += acc3;
+          }
+          __syncwarp();
+          acc0 = acc1 = acc2 = acc3 = T(0);
+          cur_cell = c;
+        }
+        if (node_lane) {
+          const T* w = &sm.sw[warp][q][0];
+          const T* v = &sm.sv[warp][q][0];
+          const T wt = w[ni * 3 + 0] * w[nj * 3 + 1] * w[nk * 3 + 2];
+          acc0 += v[0] * wt;
+          acc1 += (v[1] + v[4] * fi + v[5] * fj + v[6] * fk) * wt;
+          acc2 += (v[2] + v[7] * fi + v[8] * fj + v[9] * fk) * wt;
+          acc3 += (v[3] + v[10] * fi + v[11] * fj + v[12] * fk) * wt;
+        }
+      }
+      __syncwarp();
+    }
+    if (cur_cell >= 0 && node_lane) {
+      const int n = (((cur_cell >> 4) & 3) + ni) * 36 + (((cur_cell >> 2) & 3) + nj) * 6 + ((cur_cell & 3) + nk);
+      tile[0 * kTileNodes + n] += acc0;
+      tile[1 * kTileNodes + n] += acc1;
+      tile[2 * kTileNodes + n] += acc2;
+      tile[3 * kTileNodes + n] += acc3;
+    }
+    __syncwarp();
+    // ---- flush the tile (coalesced) and publish the touched grid blocks
+    T* out = tiles + (size_t)t * (4 * kTileNodes);
+    for (int i = lane; i < 4 * kTileNodes; i += 32) out[i] = tile[i];
+    reach = __reduce_or_sync(kFullMask, reach);
+    if (lane < 8 && ((reach >> lane) & 1u)) {
+      uint32_t bx, by, bz;
+      block_coords(blk, bx, by, bz);
+      bx += (lane >> 2) & 1u;
+      by += (lane >> 1) & 1u;
+      bz += lane & 1u;
+      if (bx < blocks_per_axis && by < blocks_per_axis && bz < blocks_per_axis) {
+        const uint32_t g = morton3(bx, by, bz);
+        if (atomicExch(&touched_epoch[g], epoch) != epoch) touched_list[atomicAdd(&ctr->n_touched, 1u)] = g;
+      }
+    }
+    __syncwarp();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Grid: assemble the P2G tiles into the dense grid and/or update it
+// (replaces gather_touched_grid_kernel :545-583 and update_grid_kernel :632-796).
+// 64 threads (one per cell) x 4 grid blocks per CTA, grid-stride over the touched list.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ void apply_boundary_and_colliders(const Consts<T>& k, int bc, uint32_t x, uint32_t y,
+                                                             uint32_t z, T* v) {
+  const uint32_t nb = (uint32_t)k.boundary_cells, dom = (uint32_t)k.domain_size;
+  if (x < nb && v[0] < T(0)) v[0] = T(0);
+  if (x >= dom - nb && v[0] > T(0)) v[0] = T(0);
+  if (y < nb && v[1] < T(0)) v[1] = T(0);
+  if (y >= dom - nb && v[1] > T(0)) v[1] = T(0);
+  if (z < nb && v[2] < T(0)) v[2] = T(0);
+  if (z >= dom - nb && v[2] > T(0)) v[2] = T(0);
+  if (bc < 0) return;
+  // hard-coded analytic colliders of the reference demos (:671-788)
+  const T p[3] = {(T(x) + T(.5)) * k.dx, (T(y) + T(.5)) * k.dx, (T(z) + T(.5)) * k.dx};
+  bool fixed = false, inside = false;
+  T diff[3] = {T(0), T(0), T(0)}, n[3] = {T(0), T(0), T(0)}, dotnv = T(0);
+  auto sphere = [&](T cx, T cy, T cz, T radius, bool need_approach) -> bool {
+    n[0] = p[0] - cx; n[1] = p[1] - cy; n[2] = p[2] - cz;
+    const T len = tsqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+    const T dist = len - radius;
+    const T inv = T(1) / len;
+    n[0] *= inv; n[1] *= inv; n[2] *= inv;
+    dotnv = T(0);
+    if (dist < T(0)) {
+      diff[0] = -v[0]; diff[1] = -v[1]; diff[2] = -v[2];   // collider velocity is zero
+      dotnv = n[0] * diff[0] + n[1] * diff[1] + n[2] * diff[2];
+      if (!need_approach || dotnv > T(0) || fixed) return true;
+    }
+    return false;
+  };
+  if (bc == 0) {
+    inside = sphere(T(0.5), T(0.5), T(0.5), T(0.08), true);
+  } else if (bc == 1) {
+    fixed = true;
+    inside = sphere(T(0.38), T(0.38), T(0.75), T(0.04), true);
+    if (!inside) inside = sphere(T(0.38), T(0.62), T(0.75), T(0.04), true);  // only when outside the first (:711-733)
+  } else if (bc == 2) {
+    n[0] = T(0); n[1] = T(0); n[2] = T(1);
+    if (p[2] - T(0.11) < T(0)) {
+      inside = true;
+      diff[0] = -v[0]; diff[1] = -v[1]; diff[2] = -v[2];
+      dotnv = diff[2];
+    }
+  } else if (bc == 3) {
+    fixed = true;
+    const T span[2] = {T(0.3), T(0.7)};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if (!inside) inside = sphere(span[q % 2], span[q / 2], T(0.5), T(0.02), false);
+    }
+  }
+  if (inside) {
+    if (fixed) {
+      v[0] += diff[0]; v[1] += diff[1]; v[2] += diff[2];
+    } else {
+      const T frac = dotnv * (T(1) - k.sdf_friction);
+#pragma unroll
+      for (int d = 0; d < 3; ++d) v[d] += diff[d] * k.sdf_friction + n[d] * frac;
+    }
+  }
+}
+
+template <typename T, bool ASSEMBLE, bool UPDATE>
+__global__ void __launch_bounds__(kThreads)
+grid_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __restrict__ ctr,
+            const T* __restrict__ tiles, const uint32_t* __restrict__ pb_tile, const uint32_t* __restrict__ pb_epoch,
+            uint32_t epoch, T* __restrict__ g_mass, T* __restrict__ g_vel, T* __restrict__ g_vstar, int bc,
+            Consts<T> k) {
+  const uint32_t n_touched = ctr->n_touched;
+  const uint32_t l = threadIdx.x & 63u;
+  const uint32_t lx = (l >> 4) & 3u, ly = (l >> 2) & 3u, lz = l & 3u;
+  for (uint32_t it = blockIdx.x * 4u + (threadIdx.x >> 6); it < n_touched; it += gridDim.x * 4u) {
+    const uint32_t g = touched_list[it];
+    uint32_t gx, gy, gz;
+    block_coords(g, gx, gy, gz);
+    T m, p[3];
+    const size_t cell = (size_t)g * 64 + l;
+    const size_t vbase = (size_t)g * 192 + l;
+    if (ASSEMBLE) {
+      m = T(0); p[0] = T(0); p[1] = T(0); p[2] = T(0);
+#pragma unroll
+      for (int d = 0; d < 8; ++d) {
+        const uint32_t ddx = (d >> 2) & 1u, ddy = (d >> 1) & 1u, ddz = d & 1u;
+        // tile of particle block g - delta covers local cells [4 delta, 4 delta + 6): needs l < 2 where delta = 1
+        if ((ddx && (lx >= 2u || gx == 0u)) || (ddy && (ly >= 2u || gy == 0u)) || (ddz && (lz >= 2u || gz == 0u))) continue;
+        const uint32_t src = morton3(gx - ddx, gy - ddy, gz - ddz);
+        if (pb_epoch[src] != epoch) continue;
+        const T* tl = tiles + (size_t)pb_tile[src] * (4 * kTileNodes);
+        const uint32_t n = (lx + 4u * ddx) * 36u + (ly + 4u * ddy) * 6u + (lz + 4u * ddz);
+        m += tl[n];
+        p[0] += tl[kTileNodes + n];
+        p[1] += tl[2 * kTileNodes + n];
+        p[2] += tl[3 * kTileNodes + n];
+      }
+      if (!UPDATE) {
+        g_mass[cell] = m;
+        g_vel[vbase] = p[0];
+        g_vel[vbase + 64] = p[1];
+        g_vel[vbase + 128] = p[2];
+      }
+    } else {
+      m = g_mass[cell];
+      p[0] = g_vel[vbase];
+      p[1] = g_vel[vbase + 64];
+      p[2] = g_vel[vbase + 128];
+    }
+    if (UPDATE) {
+      if (m > T(0)) {
+        p[0] /= m; p[1] /= m; p[2] /= m;
+        apply_boundary_and_colliders(k, bc, (gx << 2) | lx, (gy << 2) | ly, (gz << 2) | lz, p);
+        g_vstar[vbase] = p[0];
+        g_vstar[vbase + 64] = p[1];
+        g_vstar[vbase + 128] = p[2];
+      }
+      if (ASSEMBLE) g_mass[cell] = m;
+      g_vel[vbase] = p[0];
+      g_vel[vbase + 64] = p[1];
+      g_vel[vbase + 128] = p[2];
+    }
+  }
+}
+
+// Zero the blocks that were touched by the previous P2G but not by this one (the reference zeroes
+// all previously touched blocks in clean_grid_kernel; blocks touched again are overwritten here).
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+clean_stale_blocks_kernel(const uint32_t* __restrict__ prev_list, const DevCounters* __restrict__ ctr,
+                          const uint32_t* __restrict__ touched_epoch, uint32_t epoch, T* __restrict__ g_mass,
+                          T* __restrict__ g_vel) {
+  const uint32_t n_prev = ctr->n_touched_prev;
+  const uint32_t l = threadIdx.x & 63u;
+  for (uint32_t it = blockIdx.x * 4u + (threadIdx.x >> 6); it < n_prev; it += gridDim.x * 4u) {
+    const uint32_t g = prev_list[it];
+    if (touched_epoch[g] == epoch) continue;
+    g_mass[(size_t)g * 64 + l] = T(0);
+    g_vel[(size_t)g * 192 + l] = T(0);
+    g_vel[(size_t)g * 192 + 64 + l] = T(0);
+    g_vel[(size_t)g * 192 + 128 + l] = T(0);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// G2P + advection + reorder (replaces grid_to_particle_kernel<..,false> :798-924 and the
+// floating-point part of compute_sorted_state_kernel :384-416).
+//
+// One WARP per particle block: the 6^3 x 3 velocity nodes the block's stencils can reach are staged
+// in shared memory once, lanes = particles gather their 27 nodes from it.  Results are written to
+// the OTHER particle buffer at the particle's position in the key-sorted order, so the physical
+// order follows the spatial order with one step of lag and next step's loads stay coalesced.
+// ------------------------------------------------------------------------------------------------
+constexpr int kG2PWarps = 4;
+
+template <typename T>
+__global__ void __launch_bounds__(kG2PWarps * 32)
+g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const uint32_t* __restrict__ pb_list,
+           const uint32_t* __restrict__ pb_start, const uint32_t* __restrict__ pb_end,
+           const T* __restrict__ g_vel, const T* __restrict__ pos, const T* __restrict__ vol,
+           const int* __restrict__ pid, T* __restrict__ pos_out, T* __restrict__ vel_out, T* __restrict__ C_out,
+           T* __restrict__ vol_out, int* __restrict__ pid_out, int* __restrict__ slot_of_pid,
+           uint32_t* __restrict__ key_out, DevCounters* ctr, T dt, Consts<T> k) {
+  __shared__ T s_vel[kG2PWarps][3][kTileNodes];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  T* tv = &s_vel[warp][0][0];
+  const uint32_t n_pb = ctr->n_pblocks;
+  const uint32_t blocks_per_axis = (uint32_t)k.domain_size >> 2;
+  for (;;) {
+    uint32_t t = 0;
+    if (lane == 0) t = atomicAdd(&ctr->work_g2p, 1u);
+    t = __shfl_sync(kFullMask, t, 0);
+    if (t >= n_pb) break;
+    const uint32_t blk = pb_list[t];
+    const uint32_t begin = pb_start[blk], end = pb_end[blk];
+    uint32_t bx, by, bz;
+    block_coords(blk, bx, by, bz);
+    // stage the reachable velocity nodes
+    for (int n = lane; n < kTileNodes; n += 32) {
+      const uint32_t tx = n / 36, ty = (n / 6) % 6, tz = n % 6;
+      const uint32_t gx = bx + (tx >> 2), gy = by + (ty >> 2), gz = bz + (tz >> 2);
+      T v0 = T(0), v1 = T(0), v2 = T(0);
+      if (gx < blocks_per_axis && gy < blocks_per_axis && gz < blocks_per_axis) {
+        const size_t vb = (size_t)morton3(gx, gy, gz) * 192 + (((tx & 3u) << 4) | ((ty & 3u) << 2) | (tz & 3u));
+        v0 = g_vel[vb];
+        v1 = g_vel[vb + 64];
+        v2 = g_vel[vb + 128];
+      }
+      tv[n] = v0;
+      tv[kTileNodes + n] = v1;
+      tv[2 * kTileNodes + n] = v2;
+    }
+    __syncwarp();
+    for (uint32_t i = begin + lane; i < end; i += 32) {
+      const uint32_t s = order[i];
+      T x[3] = {pos[s], pos[N + s], pos[2 * N + s]};
+      uint32_t b[3];
+      T fx[3], w[3][3];
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        b[d] = base_node(x[d], k.dx_inv, k.domain_size);
+        fx[d] = x[d] * k.dx_inv - T(b[d]);
+        w[0][d] = T(0.5) * (T(1.5) - fx[d]) * (T(1.5) - fx[d]);
+        w[1][d] = T(0.75) - (fx[d] - T(1)) * (fx[d] - T(1));
+        w[2][d] = T(0.5) * (fx[d] - T(0.5)) * (fx[d] - T(0.5));
+      }
+      const int n0 = (int)((b[0] & 3u) * 36u + (b[1] & 3u) * 6u + (b[2] & 3u));
+      T nv[3] = {T(0), T(0), T(0)};
+      T S[9] = {T(0), T(0), T(0), T(0), T(0), T(0), T(0), T(0), T(0)};
+#pragma unroll
+      for (int ii = 0; ii < 3; ++ii)
+#pragma unroll
+        for (int jj = 0; jj < 3; ++jj) {
+          const T wij = w[ii][0] * w[jj][1];
+#pragma unroll
+          for (int kk = 0; kk < 3; ++kk) {
+            const int n = n0 + ii * 36 + jj * 6 + kk;
+            const T wt = wij * w[kk][2];
+            const T xi[3] = {T(ii) - fx[0], T(jj) - fx[1], T(kk) - fx[2]};
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+              const T wg = wt * tv[a * kTileNodes + n];
+              nv[a] += wg;
+              S[a * 3 + 0] += wg * xi[0];
+              S[a * 3 + 1] += wg * xi[1];
+              S[a * 3 + 2] += wg * xi[2];
+            }
+          }
+        }
+      const T scale = T(4) * k.dx_inv;
+      const T ca = (k.v_blend + T(1)) * T(.5), cb = (k.v_blend - T(1)) * T(.5);
+#pragma unroll
+      for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+          C_out[(a * 3 + c) * N + i] = ca * (scale * S[a * 3 + c]) + cb * (scale * S[c * 3 + a]);
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        x[d] += nv[d] * dt;
+        vel_out[d * N + i] = nv[d];
+        pos_out[d * N + i] = x[d];
+      }
+      vol_out[i] = vol[s];
+      const int p = pid[s];
+      pid_out[i] = p;
+      slot_of_pid[p] = (int)i;
+      key_out[i] = cell_key(base_node(x[0], k.dx_inv, k.domain_size), base_node(x[1], k.dx_inv, k.domain_size),
+                            base_node(x[2], k.dx_inv, k.domain_size));
+    }
+    __syncwarp();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Layout converters for the host-facing getters (reference layout, visible particle order).
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void gather_particle_field_kernel(uint32_t N, int comps, const T* __restrict__ src,
+                                             const int* __restrict__ pid_of_vis, const int* __restrict__ slot_of_pid,
+                                             T* __restrict__ out) {
+  const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= N) return;
+  const int s = slot_of_pid[pid_of_vis[v]];
+  for (int c = 0; c < comps; ++c) out[(size_t)v * comps + c] = src[(size_t)c * N + s];
+}
+template <typename T>
+__global__ void transpose_planar_kernel(uint32_t n, int comps, const T* __restrict__ src, T* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  for (int c = 0; c < comps; ++c) out[(size_t)i * comps + c] = src[(size_t)c * n + i];
+}
+template <typename T>
+__global__ void grid_vec_to_reference_kernel(uint32_t n_cells, const T* __restrict__ src, T* __restrict__ out) {
+  const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_cells) return;
+  const size_t vb = (size_t)(c >> 6) * 192 + (c & 63u);
+  out[(size_t)c * 3 + 0] = src[vb];
+  out[(size_t)c * 3 + 1] = src[vb + 64];
+  out[(size_t)c * 3 + 2] = src[vb + 128];
+}
+__global__ void flags_from_list_kernel(const uint32_t* __restrict__ list, const DevCounters* __restrict__ ctr,
+                                       uint32_t* __restrict__ flags) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < ctr->n_touched) flags[list[i]] = 1u;
+}
+// DumpCpuState (cuda_mpm_model.cu:245-265): vertex positions in original vertex order.
+template <typename T>
+__global__ void gather_vertex_positions_kernel(uint32_t n_verts, uint32_t n_faces, uint32_t N,
+                                               const T* __restrict__ pos, const int* __restrict__ slot_of_pid,
+                                               T* __restrict__ out) {
+  const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= n_verts) return;
+  const int s = slot_of_pid[n_faces + v];
+  out[(size_t)v * 3 + 0] = pos[s];
+  out[(size_t)v * 3 + 1] = pos[N + s];
+  out[(size_t)v * 3 + 2] = pos[2 * N + s];
+}
+
+}  // namespace gmpm

@@ -1,0 +1,574 @@
+// state.cuh -- host-side owner of the device state and the launch logic of one MPM scene.
+// Replaces GpuMpmState<T> (cuda_mpm_model.cuh/.cu) and GpuMpmSolver<T> (cuda_mpm_solver.cu) of the
+// reference; exposed through the C ABI in gmpm_capi.cu.  No CPU compute path exists here.
+#pragma once
+#include <algorithm>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/gmpm_c.h"
+#include "common.cuh"
+#include "kernels.cuh"
+#include "sort.cuh"
+
+namespace gmpm {
+
+// Event-based per-kernel timing: a mark is recorded on the stream before every launch; the time
+// between two consecutive marks is attributed to the first one's kernel.
+struct Profiler {
+  bool on = false;
+  std::vector<cudaEvent_t> pool;
+  std::vector<std::pair<const char*, cudaEvent_t>> marks;
+  std::map<std::string, std::pair<double, uint64_t>> acc;
+  size_t next = 0;
+  cudaEvent_t get() {
+    if (next == pool.size()) {
+      cudaEvent_t e;
+      GMPM_CUDA(cudaEventCreate(&e));
+      pool.push_back(e);
+    }
+    return pool[next++];
+  }
+  void mark(const char* name, cudaStream_t st) {
+    cudaEvent_t e = get();
+    GMPM_CUDA(cudaEventRecord(e, st));
+    marks.emplace_back(name, e);
+    if (marks.size() >= 4096) flush(st);
+  }
+  void flush(cudaStream_t st) {
+    if (marks.empty()) return;
+    cudaEvent_t e = get();
+    GMPM_CUDA(cudaEventRecord(e, st));
+    GMPM_CUDA(cudaEventSynchronize(e));
+    for (size_t i = 0; i < marks.size(); ++i) {
+      cudaEvent_t b = marks[i].second, n = (i + 1 < marks.size()) ? marks[i + 1].second : e;
+      float ms = 0.f;
+      GMPM_CUDA(cudaEventElapsedTime(&ms, b, n));
+      auto& a = acc[marks[i].first];
+      a.first += ms;
+      a.second += 1;
+    }
+    marks.clear();
+    next = 0;
+  }
+  void reset() {
+    marks.clear();
+    acc.clear();
+    next = 0;
+  }
+  ~Profiler() {
+    for (auto e : pool) cudaEventDestroy(e);
+  }
+};
+
+enum class GridStage { kClean, kTiles, kMomentum, kVelocity };
+
+template <typename T>
+struct State {
+  gmpm_params prm{};
+  Consts<T> k{};
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool finalized = false;
+
+  // host staging (AddQRCloth, cuda_mpm_model.cu:16-33)
+  std::vector<T> h_pos, h_vel;
+  std::vector<int> h_tri;
+  size_t n_verts = 0, n_faces = 0, N = 0;
+
+  // particles (physical slots), double buffered
+  T *pos[2]{}, *vel[2]{}, *C[2]{}, *vol[2]{};
+  int* pid[2]{};
+  int cur = 0;
+  T *forces = nullptr, *taus = nullptr;
+  int* slot_of_pid = nullptr;
+  // faces
+  int* tri = nullptr;
+  T *Fd = nullptr, *Dm_inv = nullptr;
+  // visible order (reference semantics: current_pids / index_mappings / sort_keys / sort_ids)
+  int* pid_of_vis[2]{};
+  int vis_cur = 0;
+  int* vis_of_pid = nullptr;
+  uint32_t *vis_keys[2]{}, *vis_ids[2]{};
+  int vis_res = 0;
+  bool vis_keys_valid = false;
+  // binning
+  uint32_t* key = nullptr;
+  uint32_t *skeys[2]{}, *svals[2]{};
+  int sres = 0;
+  uint32_t* sort_scratch = nullptr;
+  uint32_t *pb_start = nullptr, *pb_end = nullptr, *pb_epoch = nullptr, *pb_tile = nullptr, *pb_list = nullptr;
+  bool keys_valid = false, bin_valid = false, fem_valid = false;
+  uint32_t bin_epoch = 0, p2g_epoch = 0;
+  // grid
+  T *tiles = nullptr, *g_mass = nullptr, *g_vel = nullptr, *g_vstar = nullptr;
+  uint32_t* touched_epoch = nullptr;
+  uint32_t* touched_list[2]{};
+  int tl_cur = 0;
+  GridStage stage = GridStage::kClean;
+  DevCounters* ctr = nullptr;
+  // contact (contact.cuh)
+  size_t n_contacts = 0, contact_cap = 0;
+  uint32_t *c_pid = nullptr, *c_rigid_id = nullptr, *c_keys = nullptr;
+  T *c_pos = nullptr, *c_vel = nullptr, *c_vel0 = nullptr, *c_dist = nullptr, *c_normal = nullptr,
+    *c_rigid_v = nullptr, *c_rigid_p = nullptr, *c_mass = nullptr, *c_v0p = nullptr;
+  T *g_Hess = nullptr, *g_Grad = nullptr, *g_Dir = nullptr;
+  size_t n_bodies = 0, body_cap = 0;
+  T *F_tau = nullptr, *F_f = nullptr;
+  T* d_scalars = nullptr;     // device reduction scalars of the contact solve
+  T* h_scalars = nullptr;     // pinned mirror
+  // io
+  void* io_buf = nullptr;
+  size_t io_cap = 0;
+  void* h_pinned = nullptr;
+  size_t h_pinned_cap = 0;
+
+  std::vector<void*> allocs;
+  size_t device_bytes = 0;
+  uint64_t launches = 0;
+  Profiler prof;
+  int sm_count = 148;
+
+  // ---------------------------------------------------------------------------------------------
+  template <typename U>
+  U* dalloc(size_t n, bool zero = true) {
+    void* p = nullptr;
+    const size_t bytes = std::max<size_t>(n, 1) * sizeof(U);
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) {
+      char buf[160];
+      snprintf(buf, sizeof(buf), "cudaMalloc(%zu bytes) failed: %s", bytes, cudaGetErrorString(e));
+      throw CudaError(e, buf);
+    }
+    allocs.push_back(p);
+    device_bytes += bytes;
+    if (zero) GMPM_CUDA(cudaMemsetAsync(p, 0, bytes, stream));
+    return static_cast<U*>(p);
+  }
+  void launch(const char* name) {
+    ++launches;
+    if (prof.on) prof.mark(name, stream);
+  }
+  void note(const char* name) {  // non-kernel stream work (memset / memcpy) for the profiler only
+    if (prof.on) prof.mark(name, stream);
+  }
+  static uint32_t blocks_for(size_t n, int threads = kThreads) { return (uint32_t)((n + threads - 1) / threads); }
+
+  void init(const gmpm_params& p) {
+    prm = p;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) throw CudaError(cudaErrorNoDevice, "no CUDA device available (libgmpm_b200 has no CPU fallback)");
+    if (p.device >= 0) GMPM_CUDA(cudaSetDevice(p.device));
+    GMPM_CUDA(cudaGetDevice(&device));
+    GMPM_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
+    GMPM_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    if (p.domain_bits < 3 || p.domain_bits > 10) throw std::invalid_argument("domain_bits must be in [3,10]");
+    if (p.gravity_axis < 0 || p.gravity_axis > 2) throw std::invalid_argument("gravity_axis must be 0,1,2");
+    k.domain_bits = p.domain_bits;
+    k.domain_size = 1 << p.domain_bits;
+    k.n_cells = 1u << (3 * p.domain_bits);
+    k.n_blocks = 1u << (3 * (p.domain_bits - kBlockBits));
+    k.boundary_cells = p.boundary_cells;
+    k.gravity_axis = p.gravity_axis;
+    k.dx_inv = T(1) * T(1 << p.domain_bits);  // settings.h:50,57
+    k.dx = T(1) / k.dx_inv;
+    k.d_inv = T(4) * k.dx_inv * k.dx_inv;     // settings.h:59
+    const T E = T(p.youngs), nu = T(p.poisson);
+    k.mu = E / (T(2) * (T(1) + nu));          // settings.h:114-115
+    k.lambda = E * nu / ((T(1) + nu) * (T(1) - T(2) * nu));
+    k.density = T(p.density);
+    k.gamma = T(p.gamma);
+    k.k_normal = T(p.k_normal);
+    k.v_blend = T(p.v_blend);
+    k.c_f = T(p.c_f);
+    k.sdf_friction = T(p.sdf_friction);
+    k.gravity = T(p.gravity);
+    k.epsv = T(p.epsv);
+  }
+
+  void destroy() {
+    if (stream) cudaStreamSynchronize(stream);
+    for (void* p : allocs) cudaFree(p);
+    allocs.clear();
+    if (io_buf) cudaFree(io_buf);
+    if (h_pinned) cudaFreeHost(h_pinned);
+    if (h_scalars) cudaFreeHost(h_scalars);
+    io_buf = nullptr;
+    h_pinned = nullptr;
+    h_scalars = nullptr;
+    if (stream) cudaStreamDestroy(stream);
+    stream = nullptr;
+  }
+
+  void bind_device() const { GMPM_CUDA(cudaSetDevice(device)); }
+
+  // cuda_mpm_model.cu:16-33
+  void add_qr_cloth(const T* p, const T* v, size_t nv, const int* t, size_t nt) {
+    if (finalized) throw std::invalid_argument("AddQRCloth after Finalize");
+    for (size_t i = 0; i < nt * 3; ++i)
+      if (t[i] < 0 || (size_t)t[i] >= nv) throw std::invalid_argument("triangle index out of range");
+    h_pos.insert(h_pos.end(), p, p + nv * 3);
+    h_vel.insert(h_vel.end(), v, v + nv * 3);
+    for (size_t i = 0; i < nt * 3; ++i) h_tri.push_back(t[i] + (int)n_verts);
+    n_verts += nv;
+    n_faces += nt;
+    N += nv + nt;
+  }
+
+  // cuda_mpm_model.cu:36-122: every device allocation happens here.
+  void finalize() {
+    if (finalized) throw std::invalid_argument("Finalize called twice");
+    bind_device();
+    const size_t F = n_faces, V = n_verts;
+    if (N >= (size_t)1 << 31) throw std::invalid_argument("too many particles");
+    for (int b = 0; b < 2; ++b) {
+      pos[b] = dalloc<T>(3 * N);
+      vel[b] = dalloc<T>(3 * N);
+      C[b] = dalloc<T>(9 * N);
+      vol[b] = dalloc<T>(N);
+      pid[b] = dalloc<int>(N);
+      pid_of_vis[b] = dalloc<int>(N);
+      vis_keys[b] = dalloc<uint32_t>(N);
+      vis_ids[b] = dalloc<uint32_t>(N);
+      skeys[b] = dalloc<uint32_t>(N);
+      svals[b] = dalloc<uint32_t>(N);
+      touched_list[b] = dalloc<uint32_t>(k.n_blocks);
+    }
+    forces = dalloc<T>(3 * N);
+    taus = dalloc<T>(9 * N);
+    slot_of_pid = dalloc<int>(N);
+    vis_of_pid = dalloc<int>(N);
+    key = dalloc<uint32_t>(N);
+    tri = dalloc<int>(3 * F);
+    Fd = dalloc<T>(9 * F);
+    Dm_inv = dalloc<T>(4 * F);
+    sort_scratch = dalloc<uint32_t>(radix_sort_scratch_words(N));
+    pb_start = dalloc<uint32_t>(k.n_blocks);
+    pb_end = dalloc<uint32_t>(k.n_blocks);
+    pb_epoch = dalloc<uint32_t>(k.n_blocks);
+    pb_tile = dalloc<uint32_t>(k.n_blocks);
+    pb_list = dalloc<uint32_t>(k.n_blocks);
+    const size_t tile_cap = std::min<size_t>(k.n_blocks, std::max<size_t>(N, 1));
+    tiles = dalloc<T>(tile_cap * 4 * kTileNodes, false);
+    g_mass = dalloc<T>(k.n_cells);
+    g_vel = dalloc<T>((size_t)k.n_cells * 3);
+    g_vstar = dalloc<T>((size_t)k.n_cells * 3);
+    touched_epoch = dalloc<uint32_t>(k.n_blocks);
+    ctr = dalloc<DevCounters>(1);
+    d_scalars = dalloc<T>(16);
+    GMPM_CUDA(cudaMallocHost(&h_scalars, 16 * sizeof(T)));
+
+    // upload: [faces | verts] (cuda_mpm_model.cu:40-45), planar
+    std::vector<T> hp(3 * N, T(0)), hv(3 * N, T(0));
+    for (size_t v = 0; v < V; ++v)
+      for (int d = 0; d < 3; ++d) {
+        hp[d * N + F + v] = h_pos[v * 3 + d];
+        hv[d * N + F + v] = h_vel[v * 3 + d];
+      }
+    std::vector<int> ht(3 * F), iota(N);
+    for (size_t f = 0; f < F; ++f)
+      for (int c = 0; c < 3; ++c) ht[c * F + f] = h_tri[f * 3 + c] + (int)F;
+    for (size_t i = 0; i < N; ++i) iota[i] = (int)i;
+    GMPM_CUDA(cudaMemcpyAsync(pos[0], hp.data(), sizeof(T) * 3 * N, cudaMemcpyHostToDevice, stream));
+    GMPM_CUDA(cudaMemcpyAsync(vel[0], hv.data(), sizeof(T) * 3 * N, cudaMemcpyHostToDevice, stream));
+    GMPM_CUDA(cudaMemcpyAsync(tri, ht.data(), sizeof(int) * 3 * F, cudaMemcpyHostToDevice, stream));
+    for (int* dst : {pid[0], slot_of_pid, pid_of_vis[0], vis_of_pid})
+      GMPM_CUDA(cudaMemcpyAsync(dst, iota.data(), sizeof(int) * N, cudaMemcpyHostToDevice, stream));
+    if (F) {
+      launch("init_fem_state");
+      init_fem_state_kernel<T><<<blocks_for(F), kThreads, 0, stream>>>((uint32_t)F, (uint32_t)N, tri, pos[0], vel[0],
+                                                                      vol[0], Dm_inv, Fd, k.dx);
+      GMPM_CUDA(cudaGetLastError());
+    }
+    GMPM_CUDA(cudaFuncSetAttribute(p2g_tile_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)sizeof(P2GSmem<T>)));
+    GMPM_CUDA(cudaStreamSynchronize(stream));  // host staging vectors go out of scope
+    finalized = true;
+    keys_valid = bin_valid = false;
+  }
+
+  void require_finalized() const {
+    if (!finalized) throw std::invalid_argument("state is not finalized");
+    bind_device();
+  }
+
+  // ---- binning ---------------------------------------------------------------------------------
+  int key_bits() const { return 3 * k.domain_bits; }
+
+  void ensure_keys() {
+    if (keys_valid || N == 0) return;
+    launch("compute_keys");
+    compute_keys_kernel<T><<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, pos[cur], key, k);
+    GMPM_CUDA(cudaGetLastError());
+    keys_valid = true;
+    bin_valid = false;
+  }
+
+  const uint32_t* order() const { return svals[sres]; }
+  const uint32_t* sorted_keys() const { return skeys[sres]; }
+
+  void ensure_binning() {
+    ensure_keys();
+    if (bin_valid || N == 0) return;
+    // first pass reads `key` (by slot) and generates slot ids; later passes ping-pong skeys/svals
+    sres = sort_from(key, skeys, svals, (uint32_t)N, key_bits());
+    ++bin_epoch;
+    note("memset");
+    GMPM_CUDA(cudaMemsetAsync(&ctr->n_pblocks, 0, sizeof(uint32_t), stream));
+    launch("build_pblocks");
+    build_pblocks_kernel<<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, skeys[sres], bin_epoch, pb_start,
+                                                                pb_end, pb_epoch, pb_tile, pb_list, ctr);
+    GMPM_CUDA(cudaGetLastError());
+    bin_valid = true;
+  }
+
+  // Sort (in_keys, iota) on `bits` key bits; result pair index in (ks, vs).
+  int sort_from(uint32_t* in_keys, uint32_t* ks[2], uint32_t* vs[2], uint32_t n, int bits) {
+    // pass 0: in_keys -> ks[0]; then ks[0] <-> ks[1]
+    const uint32_t n_tiles = (n + kSortTile - 1) / kSortTile;
+    uint32_t* hist = sort_scratch;
+    uint32_t* totals = sort_scratch + (size_t)kRadix * n_tiles;
+    const int passes = (bits + kRadixBits - 1) / kRadixBits;
+    note("memset");
+    GMPM_CUDA(cudaMemsetAsync(totals, 0, sizeof(uint32_t) * kRadix * 4, stream));
+    const uint32_t* src_k = in_keys;
+    const uint32_t* src_v = nullptr;
+    int dst = 0;
+    for (int p = 0; p < passes; ++p) {
+      const int shift = p * kRadixBits;
+      const int nb = std::min(bits - shift, kRadixBits);
+      const uint32_t mask = (1u << nb) - 1u;
+      uint32_t* tot = totals + (size_t)p * kRadix;
+      launch("radix_hist");
+      radix_hist_kernel<<<n_tiles, kSortThreads, 0, stream>>>(src_k, n, shift, mask, n_tiles, hist, tot);
+      launch("radix_scan");
+      radix_scan_kernel<<<kRadix, kSortThreads, 0, stream>>>(hist, tot, n_tiles);
+      launch("radix_scatter");
+      if (p == 0)
+        radix_scatter_kernel<true><<<n_tiles, kSortThreads, 0, stream>>>(src_k, nullptr, ks[dst], vs[dst], n, shift,
+                                                                         mask, n_tiles, hist);
+      else
+        radix_scatter_kernel<false><<<n_tiles, kSortThreads, 0, stream>>>(src_k, src_v, ks[dst], vs[dst], n, shift,
+                                                                          mask, n_tiles, hist);
+      GMPM_CUDA(cudaGetLastError());
+      src_k = ks[dst];
+      src_v = vs[dst];
+      dst ^= 1;
+    }
+    return dst ^ 1;
+  }
+
+  // ---- GpuMpmSolver<T>::RebuildMapping (cuda_mpm_solver.cu:18-70) -------------------------------
+  // The physical order is maintained by g2p (sorted by full cell key every step); the reference's
+  // observable result of a sort -- sorted keys, permutation ids, pids, index_mappings -- is kept as
+  // integer bookkeeping of the VISIBLE order, bit-identical to the reference's 16-bit stable sort.
+  void rebuild_mapping(bool sort) {
+    require_finalized();
+    if (N == 0) return;
+    ensure_keys();
+    if (!sort) {
+      vis_keys_valid = false;  // keys = key of each visible particle, ids = iota: materialised lazily
+      return;
+    }
+    launch("gather_visible_keys");
+    gather_visible_keys_kernel<<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, key, pid_of_vis[vis_cur],
+                                                                      slot_of_pid, vis_keys[0], vis_ids[0]);
+    GMPM_CUDA(cudaGetLastError());
+    const int bits = std::min(key_bits(), 16);  // cuda_mpm_solver.cu:57
+    // sort_from reads vis_keys[0] as the input and would overwrite it in pass 0 -> stage through vis_keys[1]
+    uint32_t* ks[2] = {vis_keys[1], vis_keys[0]};
+    uint32_t* vs[2] = {vis_ids[1], vis_ids[0]};
+    const int r = sort_from(vis_keys[0], ks, vs, (uint32_t)N, bits);
+    vis_res = (r == 0) ? 1 : 0;
+    launch("permute_visible");
+    permute_visible_kernel<<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, vis_ids[vis_res], pid_of_vis[vis_cur],
+                                                                  pid_of_vis[vis_cur ^ 1], vis_of_pid);
+    GMPM_CUDA(cudaGetLastError());
+    vis_cur ^= 1;
+    vis_keys_valid = true;
+  }
+
+  void materialize_visible_keys() {
+    if (vis_keys_valid) return;
+    ensure_keys();
+    launch("gather_visible_keys");
+    gather_visible_keys_kernel<<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, key, pid_of_vis[vis_cur],
+                                                                      slot_of_pid, vis_keys[0], vis_ids[0]);
+    GMPM_CUDA(cudaGetLastError());
+    vis_res = 0;
+    vis_keys_valid = true;
+  }
+
+  // ---- GpuMpmSolver<T>::CalcFemStateAndForce (cuda_mpm_solver.cu:73-84) -------------------------
+  void calc_fem(T dt) {
+    require_finalized();
+    if (N == 0) return;
+    ensure_keys();
+    note("memset");
+    GMPM_CUDA(cudaMemsetAsync(forces, 0, sizeof(T) * 3 * N, stream));
+    if (n_faces) {
+      launch("fem");
+      fem_kernel<T><<<blocks_for(n_faces, 128), 128, 0, stream>>>((uint32_t)n_faces, (uint32_t)N, tri, slot_of_pid,
+                                                                  vol[cur], C[cur], Dm_inv, pos[cur], vel[cur], Fd,
+                                                                  forces, taus, key, dt, k);
+      GMPM_CUDA(cudaGetLastError());
+      bin_valid = false;  // face particles moved to their centroids
+    }
+    fem_valid = true;
+  }
+
+  uint32_t persistent_ctas(int ctas_per_sm) const { return (uint32_t)(sm_count * ctas_per_sm); }
+
+  // ---- GpuMpmSolver<T>::ParticleToGrid (cuda_mpm_solver.cu:87-105) ------------------------------
+  void p2g(T dt) {
+    require_finalized();
+    if (N == 0) return;
+    ensure_binning();
+    ++p2g_epoch;
+    tl_cur ^= 1;
+    launch("p2g_prologue");
+    p2g_prologue_kernel<<<1, 1, 0, stream>>>(ctr);
+    launch("p2g_tile");
+    p2g_tile_kernel<T><<<persistent_ctas(4), kP2GWarps * 32, sizeof(P2GSmem<T>), stream>>>(
+        (uint32_t)N, (uint32_t)n_faces, order(), sorted_keys(), pb_list, pb_start, pb_end, pos[cur], vel[cur],
+        vol[cur], C[cur], pid[cur], forces, taus, tiles, touched_epoch, touched_list[tl_cur], p2g_epoch, ctr, dt, k);
+    launch("clean_stale_blocks");
+    clean_stale_blocks_kernel<T><<<persistent_ctas(2), kThreads, 0, stream>>>(touched_list[tl_cur ^ 1], ctr,
+                                                                             touched_epoch, p2g_epoch, g_mass, g_vel);
+    GMPM_CUDA(cudaGetLastError());
+    stage = GridStage::kTiles;
+  }
+
+  void assemble_momentum() {  // observable P2G result (grid_masses / grid_momentum before UpdateGrid)
+    if (stage != GridStage::kTiles) return;
+    launch("grid_assemble");
+    grid_kernel<T, true, false><<<persistent_ctas(4), kThreads, 0, stream>>>(
+        touched_list[tl_cur], ctr, tiles, pb_tile, pb_epoch, bin_epoch, g_mass, g_vel, g_vstar, -1, k);
+    GMPM_CUDA(cudaGetLastError());
+    stage = GridStage::kMomentum;
+  }
+
+  // ---- GpuMpmSolver<T>::UpdateGrid (cuda_mpm_solver.cu:108-151) ---------------------------------
+  void update_grid(int bc) {
+    require_finalized();
+    if (N == 0) return;
+    if (stage == GridStage::kTiles) {
+      launch("grid_assemble_update");
+      grid_kernel<T, true, true><<<persistent_ctas(4), kThreads, 0, stream>>>(
+          touched_list[tl_cur], ctr, tiles, pb_tile, pb_epoch, bin_epoch, g_mass, g_vel, g_vstar, bc, k);
+    } else {
+      launch("grid_update");
+      grid_kernel<T, false, true><<<persistent_ctas(4), kThreads, 0, stream>>>(
+          touched_list[tl_cur], ctr, tiles, pb_tile, pb_epoch, bin_epoch, g_mass, g_vel, g_vstar, bc, k);
+    }
+    GMPM_CUDA(cudaGetLastError());
+    stage = GridStage::kVelocity;
+  }
+
+  // ---- GpuMpmSolver<T>::GridToParticle (cuda_mpm_solver.cu:154-161) -----------------------------
+  void g2p(T dt) {
+    require_finalized();
+    if (N == 0) return;
+    assemble_momentum();  // only if UpdateGrid was skipped by the caller
+    ensure_binning();
+    note("memset");
+    GMPM_CUDA(cudaMemsetAsync(&ctr->work_g2p, 0, sizeof(uint32_t), stream));
+    launch("g2p");
+    const int nx = cur ^ 1;
+    g2p_kernel<T><<<persistent_ctas(4), kG2PWarps * 32, 0, stream>>>(
+        (uint32_t)N, order(), pb_list, pb_start, pb_end, g_vel, pos[cur], vol[cur], pid[cur], pos[nx], vel[nx], C[nx],
+        vol[nx], pid[nx], slot_of_pid, key, ctr, dt, k);
+    GMPM_CUDA(cudaGetLastError());
+    cur = nx;
+    keys_valid = true;   // g2p wrote the key of every new slot
+    bin_valid = false;
+    fem_valid = false;
+  }
+
+  void sync() {
+    bind_device();
+    GMPM_CUDA(cudaStreamSynchronize(stream));
+    if (prof.on) prof.flush(stream);
+  }
+
+  void run_substeps(int n, T dt, int bc, int sort_every) {
+    for (int i = 0; i < n; ++i) {
+      rebuild_mapping(sort_every > 0 && (i % sort_every) == 0);
+      calc_fem(dt);
+      p2g(dt);
+      update_grid(bc);
+      g2p(dt);
+    }
+  }
+
+  // ---- host I/O --------------------------------------------------------------------------------
+  void* io(size_t bytes) {
+    if (bytes > io_cap) {
+      GMPM_CUDA(cudaStreamSynchronize(stream));
+      if (io_buf) cudaFree(io_buf);
+      io_buf = nullptr;
+      io_cap = 0;
+      GMPM_CUDA(cudaMalloc(&io_buf, bytes));
+      io_cap = bytes;
+    }
+    return io_buf;
+  }
+  void to_host(void* dst, const void* src, size_t bytes) {
+    GMPM_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, stream));
+    GMPM_CUDA(cudaStreamSynchronize(stream));
+  }
+
+  // GpuMpmSolver<T>::SyncParticleStateToCpu (cuda_mpm_solver.cu:187-191)
+  void positions_to_host(T* out) {
+    require_finalized();
+    if (N == 0) return;
+    T* buf = static_cast<T*>(io(sizeof(T) * 3 * N));
+    launch("gather_positions");
+    gather_particle_field_kernel<T><<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, 3, pos[cur],
+                                                                           pid_of_vis[vis_cur], slot_of_pid, buf);
+    GMPM_CUDA(cudaGetLastError());
+    to_host(out, buf, sizeof(T) * 3 * N);
+    if (prof.on) prof.flush(stream);
+  }
+
+  // GpuMpmState<T>::DumpCpuState (cuda_mpm_model.cu:245-265)
+  void dump_cpu_state(T* vert_pos, int* tri_out) {
+    require_finalized();
+    if (n_verts) {
+      T* buf = static_cast<T*>(io(sizeof(T) * 3 * n_verts));
+      launch("gather_vertex_positions");
+      gather_vertex_positions_kernel<T><<<blocks_for(n_verts), kThreads, 0, stream>>>(
+          (uint32_t)n_verts, (uint32_t)n_faces, (uint32_t)N, pos[cur], slot_of_pid, buf);
+      GMPM_CUDA(cudaGetLastError());
+      to_host(vert_pos, buf, sizeof(T) * 3 * n_verts);
+    }
+    std::memcpy(tri_out, h_tri.data(), sizeof(int) * 3 * n_faces);
+  }
+
+  uint32_t touched_count_host() {
+    require_finalized();
+    uint32_t c = 0;
+    to_host(&c, &ctr->n_touched, sizeof(uint32_t));
+    return c;
+  }
+  uint32_t pblock_count_host() {
+    require_finalized();
+    uint32_t c = 0;
+    to_host(&c, &ctr->n_pblocks, sizeof(uint32_t));
+    return c;
+  }
+
+  size_t read(const char* name, void* out, size_t cap);  // getters.cuh
+  // contact.cuh
+  void copy_contact_pairs(size_t n, const uint32_t* mpm_id, const uint32_t* rigid_id, const T* dist, const T* normal,
+                          const T* cpos, const T* rigid_v, const T* rigid_p);
+  void update_contact(T dt, T mu, T stiffness, T damping, bool exact, int max_it, gmpm_contact_stats* stats);
+  void reallocate_external_bodies(size_t n);
+  void external_body_force_to_host(T* tau, T* f);
+  void ensure_contact_grids();
+};
+
+}  // namespace gmpm

@@ -1,0 +1,169 @@
+/*
+ * gmpm_c.h -- C ABI of libgmpm_b200.so: the B200-native (sm_100a) MPM per-timestep hot path.
+ *
+ * The reference (g1n0st/drake, multibody/gpu_mpm) has no FFI of its own: the path is reached through
+ * two C++ class templates, GpuMpmState<T> (cuda_mpm_model.cuh:37-260) and GpuMpmSolver<T>
+ * (cuda_mpm_solver.cuh:19-35), called from DeformableDriver::CalcAbstractStates
+ * (multibody/plant/deformable_driver.h:221-271).  Every entry point below replaces exactly one
+ * method of those two classes (cited per function); include/multibody/gpu_mpm/ holds header-only
+ * C++ shims that re-create the two classes on top of this ABI so deformable_driver.h compiles
+ * unchanged.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every buffer argument is a HOST pointer borrowed for the call
+ *     and laid out as the reference lays it out (interleaved xyz, row-major 3x3, visible order);
+ *   - one suffix per scalar: _f32 (the reference's product build, settings.h:37) and _f64;
+ *   - every function returns 0 on success and a negative gmpm_status otherwise; the message is
+ *     available from gmpm_last_error() (thread-local).  The reference has no error reporting
+ *     (CUDA_SAFE_CALL is a no-op unless DEBUG=1, settings.h:11-25);
+ *   - there is NO CPU fallback: without a CUDA device gmpm_create_* fails with GMPM_ERR_NO_DEVICE;
+ *   - all work of one state is issued on one private CUDA stream; calls are asynchronous unless
+ *     they return data to the host.  Not re-entrant per state (same as the reference).
+ */
+#ifndef GMPM_C_H_
+#define GMPM_C_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum gmpm_status {
+  GMPM_OK = 0,
+  GMPM_ERR_INVALID = -1,   /* bad argument / call order                    */
+  GMPM_ERR_NO_DEVICE = -2, /* no usable CUDA device (no CPU fallback)      */
+  GMPM_ERR_CUDA = -3,      /* a CUDA runtime call or kernel failed         */
+  GMPM_ERR_OOM = -4,       /* device allocation failed                     */
+  GMPM_ERR_UNKNOWN_NAME = -5
+} gmpm_status;
+
+/* Runtime copy of the reference's compile-time constants (settings.h:37-126).  gmpm_default_params
+ * fills in the reference's values.  domain_bits may be raised (8, 9) for the larger scenes. */
+typedef struct gmpm_params {
+  int domain_bits;     /* settings.h:49  DOMAIN_BITS = 7 -> 128^3 cells, 4^3-cell blocks            */
+  int boundary_cells;  /* settings.h:56  G_BOUNDARY_CONDITION = 3                                   */
+  int gravity_axis;    /* settings.h:118 GRAVITY_AXIS = 2                                           */
+  int device;          /* CUDA device ordinal; -1 = current device                                  */
+  double youngs;       /* settings.h:72-74   4e5                                                    */
+  double poisson;      /* settings.h:76-78   0.3                                                    */
+  double density;      /* settings.h:80-82   2000                                                   */
+  double gamma;        /* settings.h:84-86   0                                                      */
+  double k_normal;     /* settings.h:91-93   1e5                                                    */
+  double v_blend;      /* settings.h:98-100  0.8                                                    */
+  double c_f;          /* settings.h:102-104 0                                                      */
+  double sdf_friction; /* settings.h:109-111 0.3                                                    */
+  double gravity;      /* settings.h:120-122 -9.8                                                   */
+  double epsv;         /* settings.h:124-126 1e-3                                                   */
+} gmpm_params;
+
+/* Result of one UpdateContact call (the reference prints these, cuda_mpm_solver.cu:577-582). */
+typedef struct gmpm_contact_stats {
+  int iterations;        /* Newton iterations (`count`, cuda_mpm_solver.cu:241,570)            */
+  int grid_dofs;         /* active grid nodes (`grid_DoFs`, :251,564)                          */
+  int line_search_evals; /* total line-search evaluations (:530)                               */
+  int reserved;
+  double residual;       /* final sqrt(sum |Dir|^2)/DoFs (:569)                                */
+  double energy;         /* last accepted E1 (:531)                                            */
+} gmpm_contact_stats;
+
+void gmpm_default_params(gmpm_params* p);
+const char* gmpm_last_error(void);
+/* Library build string, e.g. "gmpm_b200 sm_100a". */
+const char* gmpm_version(void);
+/* Number of CUDA devices visible (0 -> every create fails). */
+int gmpm_device_count(void);
+
+#define GMPM_DECLARE(SUF, T)                                                                        \
+  typedef struct gmpm_state_##SUF gmpm_state_##SUF;                                                 \
+  /* GpuMpmState<T>() */                                                                            \
+  int gmpm_create_##SUF(const gmpm_params* p, gmpm_state_##SUF** out);                              \
+  /* GpuMpmState<T>::Destroy, cuda_mpm_model.cu:125-242 */                                          \
+  int gmpm_destroy_##SUF(gmpm_state_##SUF* s);                                                      \
+  /* GpuMpmState<T>::AddQRCloth, cuda_mpm_model.cu:16-33.  tri indexes this call's vertices. */    \
+  int gmpm_add_qr_cloth_##SUF(gmpm_state_##SUF* s, const T* pos, const T* vel, size_t n_verts,      \
+                              const int* tri, size_t n_tris);                                       \
+  /* GpuMpmState<T>::Finalize, cuda_mpm_model.cu:36-122 (+ initialize_fem_state_kernel) */          \
+  int gmpm_finalize_##SUF(gmpm_state_##SUF* s);                                                     \
+  /* GpuMpmSolver<T>::RebuildMapping, cuda_mpm_solver.cu:18-70 */                                   \
+  int gmpm_rebuild_mapping_##SUF(gmpm_state_##SUF* s, int sort);                                    \
+  /* GpuMpmSolver<T>::CalcFemStateAndForce, cuda_mpm_solver.cu:73-84 */                             \
+  int gmpm_calc_fem_##SUF(gmpm_state_##SUF* s, T dt);                                               \
+  /* GpuMpmSolver<T>::ParticleToGrid, cuda_mpm_solver.cu:87-105 */                                  \
+  int gmpm_p2g_##SUF(gmpm_state_##SUF* s, T dt);                                                    \
+  /* GpuMpmSolver<T>::UpdateGrid, cuda_mpm_solver.cu:108-151 */                                     \
+  int gmpm_update_grid_##SUF(gmpm_state_##SUF* s, int mpm_bc);                                      \
+  /* GpuMpmSolver<T>::GridToParticle, cuda_mpm_solver.cu:154-161 */                                 \
+  int gmpm_g2p_##SUF(gmpm_state_##SUF* s, T dt);                                                    \
+  /* GpuMpmSolver<T>::GpuSync, cuda_mpm_solver.cu:164-166 */                                        \
+  int gmpm_sync_##SUF(gmpm_state_##SUF* s);                                                         \
+  /* GpuMpmSolver<T>::SyncParticleStateToCpu, cuda_mpm_solver.cu:187-191: positions_host(), 3N */  \
+  int gmpm_sync_particle_state_to_cpu_##SUF(gmpm_state_##SUF* s, T* positions_host);                \
+  /* GpuMpmSolver<T>::CopyContactPairs, cuda_mpm_solver.cu:194-212 (+ ReallocateContacts) */        \
+  int gmpm_copy_contact_pairs_##SUF(gmpm_state_##SUF* s, size_t n, const uint32_t* mpm_id,          \
+                                    const uint32_t* rigid_id, const T* dist, const T* normal,       \
+                                    const T* pos, const T* rigid_v, const T* rigid_p_WB);           \
+  /* GpuMpmSolver<T>::UpdateContact, cuda_mpm_solver.cu:215-621.  max_iterations <= 0 -> 2000. */   \
+  int gmpm_update_contact_##SUF(gmpm_state_##SUF* s, T dt, T friction_mu, T stiffness, T damping,   \
+                                int exact_line_search, int max_iterations,                          \
+                                gmpm_contact_stats* stats);                                         \
+  /* GpuMpmState<T>::ReallocateExternelBodies, cuda_mpm_model.cu:320-338 (zeroes the buffers) */    \
+  int gmpm_reallocate_external_bodies_##SUF(gmpm_state_##SUF* s, size_t n_bodies);                  \
+  /* GpuMpmState<T>::ExternelBodyForceToHost, cuda_mpm_model.cu:341-345: tau[3n], f[3n] */          \
+  int gmpm_external_body_force_to_host_##SUF(gmpm_state_##SUF* s, T* tau, T* f);                    \
+  /* GpuMpmState<T>::DumpCpuState, cuda_mpm_model.cu:245-265: vert_pos[3*n_verts], tri[3*n_faces] */\
+  int gmpm_dump_cpu_state_##SUF(gmpm_state_##SUF* s, T* vert_pos, int* tri);                        \
+  /* sizes: n_verts()/n_faces()/n_particles()/num_contacts(), grid_touched_cnt_host() */            \
+  size_t gmpm_n_verts_##SUF(const gmpm_state_##SUF* s);                                             \
+  size_t gmpm_n_faces_##SUF(const gmpm_state_##SUF* s);                                             \
+  size_t gmpm_n_particles_##SUF(const gmpm_state_##SUF* s);                                         \
+  size_t gmpm_n_cells_##SUF(const gmpm_state_##SUF* s);                                             \
+  size_t gmpm_num_contacts_##SUF(const gmpm_state_##SUF* s);                                        \
+  int gmpm_grid_touched_cnt_host_##SUF(gmpm_state_##SUF* s, uint32_t* out);                         \
+  /* Raw-accessor replacement (cuda_mpm_model.cuh:43-143): copies the named buffer to the host in */\
+  /* the REFERENCE's layout and visible particle order.  Names = the reference accessor names     */\
+  /* without the current_ prefix: positions velocities volumes affine_matrices pids sort_keys     */\
+  /* sort_ids forces taus index_mappings indices Dm_inverses deformation_gradients grid_masses    */\
+  /* grid_momentum grid_v_star grid_touched_flags grid_touched_ids grid_Hess grid_Grad grid_Dir   */\
+  /* contact_vel contact_vel0 contact_sort_keys.  *bytes_written <- size; fails if cap too small. */\
+  int gmpm_read_##SUF(gmpm_state_##SUF* s, const char* name, void* out, size_t cap_bytes,           \
+                      size_t* bytes_written);                                                       \
+  /* One substep of the driver loop without contact (deformable_driver.h:240-260 /                */\
+  /* cuda_mpm_test.cc:66-72): RebuildMapping(sort) CalcFemStateAndForce ParticleToGrid            */\
+  /* UpdateGrid(mpm_bc) GridToParticle, n_substeps times; sort_every = k sorts at substeps        */\
+  /* 0,k,2k.. (0 = never).  Same results as the individual calls; replayed from a CUDA graph.     */\
+  int gmpm_run_substeps_##SUF(gmpm_state_##SUF* s, int n_substeps, T dt, int mpm_bc,                \
+                              int sort_every);                                                      \
+  /* Instrumentation: number of kernels launched so far by this state, and per-kernel device time.*/\
+  uint64_t gmpm_kernel_launches_##SUF(const gmpm_state_##SUF* s);                                   \
+  /* profiling on: every kernel is bracketed by CUDA events on the state's stream (graphs off).   */\
+  int gmpm_set_profiling_##SUF(gmpm_state_##SUF* s, int on);                                        \
+  /* total ms and launches of kernels whose name starts with `prefix` since profiling was enabled */\
+  int gmpm_kernel_time_##SUF(gmpm_state_##SUF* s, const char* prefix, double* total_ms,             \
+                             uint64_t* launches);                                                   \
+  /* writes "name ms launches\n" lines for every profiled kernel; returns bytes needed */          \
+  size_t gmpm_profile_report_##SUF(gmpm_state_##SUF* s, char* buf, size_t cap);                     \
+  /* device bytes currently held by the state */                                                   \
+  size_t gmpm_device_bytes_##SUF(const gmpm_state_##SUF* s);                                        \
+  /* binning summary of the last RebuildMapping: particle blocks and touched grid blocks */        \
+  int gmpm_block_counts_##SUF(gmpm_state_##SUF* s, uint32_t* particle_blocks,                       \
+                              uint32_t* touched_blocks);
+
+GMPM_DECLARE(f32, float)
+GMPM_DECLARE(f64, double)
+
+/* Integer helpers of the path (cuda_mpm_kernels.cuh:296-363), host-callable for hosts that need
+ * the same cell addressing (contact queries, I/O). */
+uint32_t gmpm_morton_code(uint32_t x, uint32_t y, uint32_t z);
+uint32_t gmpm_cell_index(uint32_t xi, uint32_t yi, uint32_t zi);
+void gmpm_inverse_cell_index(uint32_t index, uint32_t* xyz);
+/* Stable device radix sort of (key,id) pairs on key bits [0,num_bit) -- the reference's radix_sort
+ * (radix_sort.cuh:202-286) semantics.  Host arrays in/out (testing / standalone use). */
+int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_t n, int num_bit,
+                          uint32_t* keys_out, uint32_t* ids_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GMPM_C_H_ */

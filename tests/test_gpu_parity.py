@@ -1,0 +1,386 @@
+"""GPU parity tests (run on the B200 box with `-m gpu`), all through the C ABI.
+
+Checker = the CPU oracle (oracle/, pinned against the reference's own helpers in test_oracle_golden.py
+and, here, against the reference's own kernels rebuilt for sm_100: oracle/_ref).  Bars:
+  * integer / index work (keys, sort permutation, pids, index_mappings, touched-block set): bit-exact;
+  * fp64: <= 1e-9 relative per step, <= 1e-6 after 100 steps (BASELINE.json north_star);
+  * fp32: <= 1e-3 relative over the few steps tested against the fp32 oracle (1e-2 on stress/force, which amplify
+    the rounding of positions by 1/edge length).
+"Relative" is norm-wise: max|a - b| / max|b| over the array (momenta and affine matrices cancel to
+zero in places, an element-wise ratio is meaningless there).
+"""
+import numpy as np
+import pytest
+
+import oracle_py as O
+import refgpu
+from drake_b200 import scenes
+from drake_b200.gpu_mpm import GpuMpmSolver, GpuMpmState, radix_sort_pairs
+
+pytestmark = pytest.mark.gpu
+
+TOL = {np.dtype(np.float64): 1e-9, np.dtype(np.float32): 1e-3}
+# stress and nodal force amplify the rounding of positions by 1/edge-length (strain = dx/edge)
+TOL_STRESS = {np.dtype(np.float64): 1e-9, np.dtype(np.float32): 1e-2}
+PARTICLE_FIELDS = ["positions", "velocities", "affine_matrices", "volumes"]
+
+
+def rel(a, b, floor=0.0):
+    """Norm-wise relative error max|a - b| / max(max|b|, floor)."""
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    assert a.shape == b.shape
+    if a.size == 0:
+        return 0.0
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), floor, 1e-300))
+
+
+def assert_particles_close(get_a, get_b, tol, tag=""):
+    """Compares positions / velocities / affine matrices / volumes.  The affine matrix is a velocity
+    gradient: where the motion is (nearly) rigid it cancels to rounding noise, so its error is
+    measured against max|v| / dx (the size of its summands), not against its own noise."""
+    vel_b = get_b("velocities")
+    vmax = float(np.max(np.abs(vel_b))) if vel_b.size else 0.0
+    floors = {"positions": 0.0, "velocities": 0.0, "volumes": 0.0, "affine_matrices": vmax * 128.0}
+    for name in PARTICLE_FIELDS:
+        r = rel(get_a(name), get_b(name), floors[name])
+        assert r <= tol, (tag, name, r)
+
+
+def make_pair(dtype, sheets, **params):
+    """(ours, solver, oracle) on the same cloth sheets."""
+    st = GpuMpmState(dtype, **params)
+    orc = O.OracleMpm(dtype, O.default_params(**params))
+    for pos, vel, tri in sheets:
+        st.AddQRCloth(pos, vel, tri)
+        orc.AddQRCloth(pos, vel, tri)
+    st.Finalize()
+    orc.Finalize()
+    return st, GpuMpmSolver(), orc
+
+
+def small_scene(dtype, res=40, warm=True, n_sheets=2, seed=3):
+    rng = np.random.default_rng(seed)
+    out = []
+    for s in range(n_sheets):
+        pos, vel, tri = scenes.cloth_sheet(res, 0.3, 0.31 + 0.013 * s, 0.33, 0.5 + 0.021 * s, dtype)
+        pos = pos.astype(np.float64)
+        pos[:, 2] += 0.01 * np.sin(9 * pos[:, 0]) * np.cos(7 * pos[:, 1])  # not axis aligned
+        pos = pos.astype(dtype)
+        if warm:
+            vel = rng.normal(0, 0.3, pos.shape).astype(dtype)
+        out.append((pos, vel, tri))
+    return out
+
+
+def by_pid(values, pids, comps):
+    """Reorders a visible-order array to original-particle order."""
+    v = np.asarray(values).reshape(-1, comps)
+    out = np.empty_like(v)
+    out[np.asarray(pids)] = v
+    return out
+
+
+# ------------------------------------------------------------------------------------------ sort
+@pytest.mark.parametrize("n", [1, 2, 31, 32, 33, 4095, 4096, 4097, 100003])
+@pytest.mark.parametrize("bits", [16, 21])
+def test_radix_sort_bit_exact_vs_oracle(n, bits):
+    rng = np.random.default_rng(n + bits)
+    keys = rng.integers(0, 1 << 21, size=n, dtype=np.uint32)
+    keys[rng.integers(0, n, size=n // 3)] = keys[0]  # many ties: stability matters
+    ids = np.arange(n, dtype=np.uint32)
+    ko, io = radix_sort_pairs(keys, ids, bits)
+    import ctypes as C
+    eko, eio = np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    O.lib().ogmpm_stable_sort_low_bits(p(keys), p(ids), n, bits, p(eko), p(eio))
+    assert np.array_equal(io, eio)
+    assert np.array_equal(ko, eko)
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_rebuild_mapping_sort_bit_exact(dtype):
+    import ctypes as C
+    st, sv, orc = make_pair(dtype, small_scene(dtype, res=60))
+    N = st.n_particles()
+    for it in range(3):
+        # unsorted call: keys of the current visible order, ids = iota
+        sv.RebuildMapping(st, False)
+        orc.RebuildMapping(False)
+        keys = st.read("sort_keys")
+        same_keys = np.array_equal(keys, orc.read("sort_keys"))
+        assert np.array_equal(st.read("sort_ids"), np.arange(N, dtype=np.uint32))
+        if it == 0:
+            assert same_keys  # identical inputs -> identical keys
+        pids_before = st.read("pids")
+        sv.RebuildMapping(st, True)
+        orc.RebuildMapping(True)
+        # (a) against the oracle's restatement of radix_sort.cuh applied to OUR keys
+        eko, eio = np.zeros(N, np.uint32), np.zeros(N, np.uint32)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        ids = np.arange(N, dtype=np.uint32)
+        O.lib().ogmpm_stable_sort_low_bits(p(keys), p(ids), N, 16, p(eko), p(eio))
+        assert np.array_equal(st.read("sort_ids"), eio), it
+        assert np.array_equal(st.read("sort_keys"), eko), it
+        pids = st.read("pids")
+        assert np.array_equal(pids, pids_before[eio]), it
+        assert np.array_equal(st.read("index_mappings")[pids], np.arange(N)), it
+        # (b) against the oracle state itself (same keys unless a last-ulp difference moved a
+        # particle across a cell boundary, which the tolerance on positions allows)
+        if same_keys:
+            for name in ("sort_keys", "sort_ids", "pids", "index_mappings"):
+                assert np.array_equal(st.read(name), orc.read(name)), (it, name)
+        if it == 0:  # nothing but copies so far: the permuted state is bit-identical
+            for name in ("positions", "velocities", "affine_matrices"):
+                assert np.array_equal(st.read(name), orc.read(name)), (it, name)
+            # volumes are accumulated with atomics at setup (as in the reference): order-dependent last bit
+            assert rel(st.read("volumes"), orc.read("volumes")) <= 4 * np.finfo(dtype).eps
+        for _ in range(2):  # move on so that the next sort sees a different order
+            sv.RebuildMapping(st, False); sv.CalcFemStateAndForce(st, 1e-3); sv.ParticleToGrid(st, 1e-3)
+            sv.UpdateGrid(st); sv.GridToParticle(st, 1e-3)
+            orc.substep(1e-3)
+        assert_particles_close(st.read, orc.read, TOL[np.dtype(dtype)] * 10, it)
+
+
+# ------------------------------------------------------------------------------------------ one substep, stage by stage
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("bc", [-1, 2])
+def test_single_substep_stage_by_stage(dtype, bc):
+    tol = TOL[np.dtype(dtype)]
+    dt = 1e-3
+    st, sv, orc = make_pair(dtype, small_scene(dtype))
+    # Finalize: rest shape, F = Q, volumes
+    for name in ("positions", "velocities", "Dm_inverses", "deformation_gradients", "volumes", "indices", "pids"):
+        assert rel(st.read(name), orc.read(name)) <= tol, name
+    sv.RebuildMapping(st, False)
+    orc.RebuildMapping(False)
+    assert np.array_equal(st.read("sort_keys"), orc.read("sort_keys"))
+    # three warm-up substeps: the rest shape is the initial shape, so the very first stress is pure
+    # rounding noise; compare the stages on a step with real strains
+    run_both(st, sv, orc, 3, dt, bc)
+    assert_particles_close(st.read, orc.read, tol, "warm-up")
+    sv.RebuildMapping(st, False)
+    orc.RebuildMapping(False)
+    sv.CalcFemStateAndForce(st, dt)
+    orc.CalcFemStateAndForce(dt)
+    for name in ("positions", "velocities", "deformation_gradients", "taus", "forces"):
+        t = TOL_STRESS[np.dtype(dtype)] if name in ("taus", "forces") else tol
+        r = rel(st.read(name), orc.read(name))
+        print(name, r)
+        assert r <= t, name
+    sv.ParticleToGrid(st, dt)
+    orc.ParticleToGrid(dt)
+    for name in ("grid_masses", "grid_momentum"):
+        assert rel(st.read(name), orc.read(name)) <= tol, name
+    assert np.array_equal(st.read("grid_touched_flags"), orc.read("grid_touched_flags"))
+    sv.UpdateGrid(st, bc)
+    orc.UpdateGrid(bc)
+    assert st.grid_touched_cnt_host() == orc.touched_count()
+    n_t = orc.touched_count()
+    assert np.array_equal(np.sort(st.read("grid_touched_ids")[:n_t]), np.sort(orc.read("grid_touched_ids")[:n_t]))
+    for name in ("grid_masses", "grid_momentum", "grid_v_star"):
+        assert rel(st.read(name), orc.read(name)) <= tol, name
+    sv.GridToParticle(st, dt)
+    orc.GridToParticle(dt)
+    assert_particles_close(st.read, orc.read, tol, "g2p")
+    assert np.array_equal(st.read("pids"), orc.read("pids"))
+
+
+@pytest.mark.parametrize("bc", [0, 1, 3])
+def test_grid_colliders(bc):
+    """The hard-coded analytic colliders of update_grid_kernel (:671-788), sheet draped through them."""
+    dtype = np.float64
+    z = {0: 0.55, 1: 0.76, 3: 0.505}[bc]
+    pos, vel, tri = scenes.cloth_sheet(60, 0.5, 0.25, 0.25, z, dtype)
+    vel = vel + np.array([0.05, -0.02, -1.0])
+    st, sv, orc = make_pair(dtype, [(pos, vel, tri)])
+    for _ in range(3):
+        sv.RebuildMapping(st, False); sv.CalcFemStateAndForce(st, 1e-3); sv.ParticleToGrid(st, 1e-3)
+        sv.UpdateGrid(st, bc); sv.GridToParticle(st, 1e-3)
+        orc.substep(1e-3, bc)
+    hit = np.abs(orc.read("grid_v_star")).reshape(-1, 3)
+    assert (hit.max() > 0)
+    for name in ("grid_v_star", "grid_momentum"):
+        assert rel(st.read(name), orc.read(name)) <= 1e-9, name
+    assert_particles_close(st.read, orc.read, 1e-9, bc)
+
+
+# ------------------------------------------------------------------------------------------ many steps
+def run_both(st, sv, orc, steps, dt, bc=-1, sort_every=0):
+    for i in range(steps):
+        s = sort_every > 0 and i % sort_every == 0
+        sv.RebuildMapping(st, s)
+        sv.CalcFemStateAndForce(st, dt)
+        sv.ParticleToGrid(st, dt)
+        sv.UpdateGrid(st, bc)
+        sv.GridToParticle(st, dt)
+        orc.substep(dt, bc, s)
+
+
+def test_fp64_100_steps_reference_smoke_scene():
+    """The reference's own scene (cuda_mpm_test.cc:27-68): 100x100 sheet, dt = 1e-3, sort every 40."""
+    dtype = np.float64
+    sheet = scenes.cloth_sheet(100, 0.5, 0.25, 0.25, 0.75, dtype)
+    st, sv, orc = make_pair(dtype, [sheet])
+    assert st.n_particles() == 29602
+    run_both(st, sv, orc, 1, 1e-3, sort_every=40)
+    assert_particles_close(st.read, orc.read, 1e-9, "1 step")
+    run_both(st, sv, orc, 99, 1e-3, sort_every=40)
+    assert_particles_close(st.read, orc.read, 1e-6, "100 steps")
+    assert np.array_equal(st.read("pids"), orc.read("pids"))
+    assert np.array_equal(st.read("index_mappings"), orc.read("index_mappings"))
+    # DumpCpuState: vertices in original order
+    vp, tri = st.DumpCpuState()
+    ovp, otri = orc.DumpCpuState()
+    assert rel(vp, ovp) <= 1e-6 and np.array_equal(tri.reshape(-1), otri.reshape(-1))
+    # SyncParticleStateToCpu == positions in visible order
+    ph = sv.SyncParticleStateToCpu(st)
+    assert np.array_equal(ph.reshape(-1), st.read("positions"))
+
+
+def test_fp64_warm_folding_100_steps():
+    """Two warm, wavy sheets that collide with the floor boundary: particles change cells and blocks."""
+    dtype = np.float64
+    sheets = small_scene(dtype, res=50, warm=True)
+    sheets = [(p - np.array([0, 0, 0.45]), v, t) for p, v, t in sheets]  # start near the z wall
+    st, sv, orc = make_pair(dtype, sheets)
+    run_both(st, sv, orc, 100, 5e-4, sort_every=17)
+    assert_particles_close(st.read, orc.read, 1e-6, "100 steps")
+
+
+def test_fp32_20_steps():
+    dtype = np.float32
+    st, sv, orc = make_pair(dtype, small_scene(dtype, res=50))
+    run_both(st, sv, orc, 20, 1e-3, sort_every=8)
+    for name in ("positions", "velocities"):
+        assert rel(st.read(name), orc.read(name)) <= 1e-3, name
+
+
+def test_run_substeps_equals_individual_calls_and_is_reproducible():
+    dtype = np.float64
+    outs = []
+    for mode in range(3):
+        st, sv, _ = make_pair(dtype, small_scene(dtype, res=50))
+        if mode == 0:
+            for i in range(12):
+                sv.RebuildMapping(st, i % 5 == 0); sv.CalcFemStateAndForce(st, 1e-3); sv.ParticleToGrid(st, 1e-3)
+                sv.UpdateGrid(st, -1); sv.GridToParticle(st, 1e-3)
+        else:
+            sv.RunSubsteps(st, 12, 1e-3, -1, 5)
+        outs.append({n: st.read(n) for n in PARTICLE_FIELDS + ["pids"]})
+        st.Destroy()
+    for n in PARTICLE_FIELDS:
+        # everything except the nodal-force atomics of the FEM kernel is order-deterministic
+        assert rel(outs[0][n], outs[1][n]) <= 1e-10, n
+        assert rel(outs[1][n], outs[2][n]) <= 1e-10, n
+    assert np.array_equal(outs[0]["pids"], outs[1]["pids"])
+
+
+# ------------------------------------------------------------------------------------------ edge cases
+def test_single_triangle_and_domain_bits():
+    dtype = np.float64
+    pos = np.array([[0.40, 0.40, 0.40], [0.43, 0.40, 0.41], [0.40, 0.44, 0.40]], dtype)
+    vel = np.array([[0.1, 0, 0], [0, 0.2, 0], [0, 0, -0.3]], dtype)
+    tri = np.array([[0, 1, 2]], np.int32)
+    for bits in (6, 7, 8):
+        st, sv, orc = make_pair(dtype, [(pos, vel, tri)], domain_bits=bits)
+        run_both(st, sv, orc, 5, 1e-3, sort_every=2)
+        assert_particles_close(st.read, orc.read, 1e-9, bits)
+
+
+def test_near_walls_and_block_corners():
+    """Particles whose stencils straddle block corners and the 3-cell sticky walls."""
+    dtype = np.float64
+    dx = 1.0 / 128
+    pos, vel, tri = scenes.cloth_sheet(24, 24 * 0.6 * dx, 3.2 * dx, 3.3 * dx, 3.6 * dx, dtype)
+    vel = vel + np.array([-0.5, -0.4, -0.8])
+    st, sv, orc = make_pair(dtype, [(pos, vel, tri)])
+    run_both(st, sv, orc, 10, 1e-3)
+    assert_particles_close(st.read, orc.read, 1e-9, "walls")
+
+
+def test_empty_state():
+    st = GpuMpmState(np.float64)
+    st.Finalize()
+    sv = GpuMpmSolver()
+    sv.RunSubsteps(st, 2, 1e-3)
+    sv.GpuSync(st)
+    assert st.n_particles() == 0 and st.read("positions").size == 0
+
+
+def test_size_independent_properties_1m():
+    """BASELINE config 2 size (34 stacked 100x100 sheets, N = 1 006 468), properties that need no
+    oracle run: mass conservation P2G (sum grid mass == sum particle mass), momentum conservation in
+    free fall, pid permutation validity, reproducibility of the grid."""
+    dtype = np.float64
+    st = GpuMpmState(dtype)
+    for pos, vel, tri in scenes.stacked_sheets(34, dtype=dtype, warm=True):
+        st.AddQRCloth(pos, vel, tri)
+    st.Finalize()
+    sv = GpuMpmSolver()
+    assert st.n_particles() == 1006468
+    dt = 1e-4
+    sv.RebuildMapping(st, True)
+    sv.CalcFemStateAndForce(st, dt)
+    sv.ParticleToGrid(st, dt)
+    mass_p = st.read("volumes").astype(np.float64) * st.params.density
+    gm = st.read("grid_masses")
+    assert abs(gm.sum() - mass_p.sum()) <= 1e-10 * mass_p.sum()
+    # momentum: sum_i p_i = sum_p m v + m g dt + f dt (internal forces and the affine term cancel)
+    mom = st.read("grid_momentum").reshape(-1, 3).sum(0)
+    vel = st.read("velocities").reshape(-1, 3)
+    want = (mass_p[:, None] * vel).sum(0) + np.array([0, 0, st.params.gravity * dt * mass_p.sum()])
+    assert np.max(np.abs(mom - want)) <= 1e-8 * np.abs(mass_p[:, None] * vel).sum()
+    sv.UpdateGrid(st, -1)
+    sv.GridToParticle(st, dt)
+    sv.RunSubsteps(st, 5, dt, -1, 2)
+    pids = st.read("pids")
+    assert np.array_equal(np.sort(pids), np.arange(st.n_particles()))
+    assert np.array_equal(st.read("index_mappings")[pids], np.arange(st.n_particles()))
+    assert np.isfinite(st.read("positions")).all()
+
+
+# ------------------------------------------------------------------------------------------ oracle <-> reference kernels
+@pytest.mark.skipif(not refgpu.available(), reason="oracle/_ref not built (needs /root/reference at build time)")
+@pytest.mark.parametrize("dtype,tol1,tol20", [(np.float64, 1e-9, 1e-7), (np.float32, 2e-5, 2e-3)])
+def test_oracle_pinned_against_reference_kernels(dtype, tol1, tol20):
+    """Pins the CPU oracle (and ours) against the REFERENCE's own kernels (oracle/_ref: the unmodified
+    multibody/gpu_mpm sources compiled for sm_100, precise build) on the reference smoke scene.
+    One warm step, then 20 steps of the cold scene (with sort=false the reference's
+    warp merge in P2G trusts keys computed BEFORE the FEM kernel moved the face particles, so on warm
+    scenes it occasionally deposits a merged contribution one cell off; the oracle restates the
+    kernel without the warp merge)."""
+    for warm, steps, tol in ((True, 1, tol1), (False, 20, tol20)):
+        sheet = scenes.cloth_sheet(100, 0.5, 0.25, 0.25, 0.75, dtype)
+        if warm:
+            rng = np.random.default_rng(5)
+            sheet = (sheet[0], rng.normal(0, 0.2, sheet[0].shape).astype(dtype), sheet[2])
+        ref = refgpu.RefMpm(dtype)
+        ref.AddQRCloth(*sheet)
+        ref.Finalize()
+        st, sv, orc = make_pair(dtype, [sheet])
+        N = st.n_particles()
+        sizes = {"positions": 3 * N, "velocities": 3 * N, "affine_matrices": 9 * N, "volumes": N}
+        for i in range(steps):
+            ref.substep(1e-3, -1, False)
+        ref.GpuSync()
+        run_both(st, sv, orc, steps, 1e-3)
+        refget = lambda name: ref.read(name, sizes[name])
+        assert_particles_close(orc.read, refget, tol, ("oracle vs reference", warm))
+        assert_particles_close(st.read, refget, tol, ("ours vs reference", warm))
+        # integer path: the reference's 16-bit stable sort
+        ref.RebuildMapping(True)
+        orc.RebuildMapping(True)
+        sv.RebuildMapping(st, True)
+        rk = ref.read("sort_keys", N, np.uint32)
+        if np.array_equal(np.sort(orc.read("sort_keys")), np.sort(rk)):
+            for name in ("sort_keys", "sort_ids"):
+                r = ref.read(name, N, np.uint32)
+                assert np.array_equal(orc.read(name), r), name
+                assert np.array_equal(st.read(name), r), name
+            for name in ("pids", "index_mappings"):
+                r = ref.read(name, N, np.int32)
+                assert np.array_equal(orc.read(name), r), name
+                assert np.array_equal(st.read(name), r), name
+        else:
+            assert not warm or steps > 1
+        ref.close()

@@ -1,0 +1,46 @@
+"""Quick per-kernel timing of the no-contact substep (development aid; bench.py is the contract)."""
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, ".")
+from drake_b200 import scenes
+from drake_b200.gpu_mpm import GpuMpmSolver, GpuMpmState
+
+
+def main():
+    dtype = np.float64 if "--f32" not in sys.argv else np.float32
+    n_sheets = 34
+    for a in sys.argv:
+        if a.startswith("--sheets="):
+            n_sheets = int(a.split("=")[1])
+    st = GpuMpmState(dtype)
+    for pos, vel, tri in scenes.stacked_sheets(n_sheets, dtype=dtype):
+        st.AddQRCloth(pos, vel, tri)
+    st.Finalize()
+    sv = GpuMpmSolver()
+    N = st.n_particles()
+    dt = 1e-3
+    sv.RunSubsteps(st, 10, dt, -1, 40)
+    sv.GpuSync(st)
+    for steps in (40, 200):
+        t0 = time.perf_counter()
+        sv.RunSubsteps(st, steps, dt, -1, 40)
+        sv.GpuSync(st)
+        t1 = time.perf_counter()
+        print("N=%d %s steps=%d: %.3f ms/step, %.3f G particle-steps/s (wall)" %
+              (N, np.dtype(dtype).name, steps, (t1 - t0) / steps * 1e3, N * steps / (t1 - t0) / 1e9))
+    print("pblocks, touched:", st.block_counts(), "device MB:", st.device_bytes() / 1e6)
+    st.set_profiling(True)
+    sv.RunSubsteps(st, 40, dt, -1, 40)
+    sv.GpuSync(st)
+    rep = st.profile_report()
+    tot = sum(v[0] for v in rep.values())
+    for k, v in sorted(rep.items(), key=lambda kv: -kv[1][0]):
+        print("  %-24s %9.3f ms total %6d launches %9.2f us/launch %5.1f%%" % (k, v[0], v[1], v[0] / v[1] * 1e3, 100 * v[0] / tot))
+    print("  profiled total %.3f ms over 40 steps = %.3f ms/step" % (tot, tot / 40))
+
+
+if __name__ == "__main__":
+    main()
