@@ -1,0 +1,366 @@
+#!/usr/bin/env python
+"""bench.py -- particle-steps/s of the MPM per-timestep hot path (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1]): 34 stacked 100x100 cloth sheets,
+N = 1 006 468 particles, fp64, dt = 1e-3, no rigid contact, 128^3 grid, the reference's own
+standalone loop (cuda_mpm_test.cc:63-72): RebuildMapping(sort = every 40th substep)
+CalcFemStateAndForce ParticleToGrid UpdateGrid GridToParticle.  One "step" = one substep.
+N > 1: one such scene per GPU (cloth shards by whole sheets; the path has no exchange step for
+cloth scenes, so there is no data-path collective) -> weak scaling.
+
+  value : device-timed (CUDA events on the library's stream), state resident in HBM.
+  e2e   : the DeformableDriver substep through the C ABI with HOST buffers
+          (deformable_driver.h:240-260): SyncParticleStateToCpu (D2H of all positions into pinned
+          host memory) + CopyContactPairs (H2D; empty in this config) + the five solver calls.
+  roofline : P2G tile kernel, algorithmic bytes / per-launch CUDA-event time (separate profiled pass).
+  cpu_baseline : the CPU oracle (oracle/, OpenMP) on this box's host cores, bounded sample.
+`--impl reference` times that CPU port alone (the reference has no CPU implementation of this path;
+oracle/_ref holds its CUDA kernels, reported by the `ours` arm as `reference_gpu`).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+N_SHEETS = 34
+DT = 1e-3
+SORT_EVERY = 40
+METRIC = "particle_steps_per_sec"
+UNIT = "particle-steps/s"
+WORKLOAD = "cfg-2: 34 stacked 100x100 cloth sheets, N=1006468, fp64, dt=1e-3, no contact, 128^3 grid"
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+def build_scene(cls_factory, dtype):
+    from drake_b200 import scenes
+    st = cls_factory()
+    for pos, vel, tri in scenes.stacked_sheets(N_SHEETS, dtype=dtype):
+        st.AddQRCloth(pos, vel, tri)
+    st.Finalize()
+    return st
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock / power / throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index, period=0.02):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples = []
+        self.stop_flag = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            uuid = None
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = index
+            if vis:
+                ids = [v.strip() for v in vis.split(",") if v.strip()]
+                if index < len(ids):
+                    if ids[index].isdigit():
+                        phys = int(ids[index])
+                    else:
+                        uuid = ids[index]
+            self.h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode()) if uuid else pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_sm = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # pragma: no cover
+            self.err = repr(e)
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self.stop_flag.is_set():
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                try:
+                    rs = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.samples.append((time.perf_counter(), sm, pw, rs))
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def summary(self, t0, t1):
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable: %s" % getattr(self, "err", "?")]}
+        nv = self.nv
+        sel = [s for s in self.samples if t0 <= s[0] <= t1] or self.samples
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4),
+                 "hw_power_brake": getattr(nv, "nvmlClocksThrottleReasonHwPowerBrakeSlowdown", 0x80)}
+        reasons = sorted({n for s in sel for n, bit in names.items() if s[3] & bit})
+        return {"sm_mhz": float(np.median([s[1] for s in sel])) if sel else None, "sm_max_mhz": float(self.max_sm),
+                "power_w_max": max([s[2] for s in sel]) if sel else None, "samples": len(sel), "reasons": reasons}
+
+
+def cpu_baseline(dtype, budget_s=12.0):
+    """The CPU oracle (OpenMP over particles/faces/cells, atomics for the scatters) on a bounded
+    sample of the same workload: the full 1M-particle scene, as many substeps as fit the budget."""
+    import oracle_py as O
+    from drake_b200 import scenes
+    cores = os.cpu_count() or 1
+    orc = O.OracleMpm(dtype)
+    for pos, vel, tri in scenes.stacked_sheets(N_SHEETS, dtype=dtype):
+        orc.AddQRCloth(pos, vel, tri)
+    orc.Finalize()
+    n = orc.n_particles
+    orc.substep_omp(DT, -1, cores)  # warm-up (page faults, first touched-block list)
+    t0 = time.perf_counter()
+    orc.substep_omp(DT, -1, cores)
+    one = time.perf_counter() - t0
+    steps = int(max(2, min(200, budget_s / max(one, 1e-6))))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        orc.substep_omp(DT, -1, cores)
+    el = time.perf_counter() - t0
+    orc.close()
+    return {"value": n * steps / el, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%d substeps of the full %d-particle scene, %.1f s, OpenMP x%d (oracle/gmpm_oracle.c)" % (steps, n, el, cores),
+            "ms_per_step": el / steps * 1e3}
+
+
+def run_reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    dtype = np.float64
+    t0 = time.perf_counter()
+    cb = cpu_baseline(dtype, budget_s=max(5.0, min(60.0, 0.5 * (args.steps + args.warmup))))
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "sort_every": SORT_EVERY,
+                       "note": "the reference ships this path only as CUDA; this arm is its CPU restatement "
+                               "(oracle/, pinned against the reference's own kernels) on the host cores"},
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
+    print(json.dumps(line), flush=True)
+
+
+def reference_gpu(dtype, steps):
+    """The reference's own kernels (oracle/_ref, as-shipped flags retargeted to sm_100) on this GPU."""
+    import refgpu
+    from drake_b200 import scenes
+    out = {}
+    for fast in (True, False):
+        if not refgpu.available(fast):
+            continue
+        ref = refgpu.RefMpm(dtype, fast=fast)
+        for pos, vel, tri in scenes.stacked_sheets(N_SHEETS, dtype=dtype):
+            ref.AddQRCloth(pos, vel, tri)
+        ref.Finalize()
+        n = ref.n_verts + ref.n_faces
+        for i in range(5):
+            ref.substep(DT, -1, i == 0)
+        ref.GpuSync()
+        t0 = time.perf_counter()
+        for i in range(steps):
+            ref.substep(DT, -1, i % SORT_EVERY == 0)
+        ref.GpuSync()
+        el = time.perf_counter() - t0
+        out["fast_math" if fast else "precise"] = {"value": n * steps / el, "ms_per_step": el / steps * 1e3}
+        ref.close()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=80)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--dtype", default="f64", choices=["f64", "f32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ref-gpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist = dist_mod
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    from drake_b200.gpu_mpm import GpuMpmSolver, GpuMpmState, MpmParticleContactPairs
+    dtype = np.float64 if args.dtype == "f64" else np.float32
+    T = np.dtype(dtype).itemsize
+    st = build_scene(lambda: GpuMpmState(dtype, device=local), dtype)
+    sv = GpuMpmSolver()
+    N = st.n_particles()
+    K, W = args.steps, args.warmup
+
+    sampler = ClockSampler(local)
+    sampler.start()
+
+    # ---- device-timed region -------------------------------------------------------------------
+    sv.RunSubsteps(st, W, DT, -1, SORT_EVERY)
+    sv.GpuSync(st)
+    barrier()
+    l0 = st.kernel_launches()
+    w0 = time.perf_counter()
+    st.timer_mark(0)
+    sv.RunSubsteps(st, K, DT, -1, SORT_EVERY)
+    st.timer_mark(1)
+    sv.GpuSync(st)
+    barrier()
+    w1 = time.perf_counter()
+    launches = st.kernel_launches() - l0
+    ms = st.timer_elapsed_ms(0, 1)
+    clocks = sampler.summary(w0, w1)
+
+    # ---- end-to-end region: the driver substep with host buffers ---------------------------------
+    pos_host = torch.empty((N, 3), dtype=torch.float64 if dtype == np.float64 else torch.float32).pin_memory()
+    pos_np = pos_host.numpy()
+    pairs = MpmParticleContactPairs(dtype)
+    contact_ok = True
+
+    def driver_substep(i):
+        nonlocal contact_ok
+        sv.SyncParticleStateToCpu(st, pos_np)              # D2H, blocking (deformable_driver.h:243)
+        sv.RebuildMapping(st, i % SORT_EVERY == 0)
+        sv.CalcFemStateAndForce(st, DT)
+        sv.ParticleToGrid(st, DT)
+        sv.UpdateGrid(st, -1)
+        if contact_ok:
+            try:
+                sv.CopyContactPairs(st, pairs)             # H2D (empty here), :250
+            except Exception:
+                contact_ok = False
+        sv.GridToParticle(st, DT)
+
+    Ke = max(3, min(K, 200))
+    for i in range(3):
+        driver_substep(i)
+    sv.GpuSync(st)
+    barrier()
+    e0 = time.perf_counter()
+    for i in range(Ke):
+        driver_substep(i)
+    sv.GpuSync(st)
+    barrier()
+    e_ms = (time.perf_counter() - e0) * 1e3
+
+    # ---- per-kernel pass (CUDA events between launches on the library's stream) ------------------
+    Kp = max(3, min(K, 200))
+    st.set_profiling(True)
+    sv.RunSubsteps(st, Kp, DT, -1, SORT_EVERY)
+    sv.GpuSync(st)
+    prof = st.profile_report()
+    st.set_profiling(False)
+    pblocks, touched = st.block_counts()
+    sampler.stop_flag.set()
+
+    # ---- reduce over ranks -----------------------------------------------------------------------
+    if dist is not None:
+        t = torch.tensor([ms, e_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e_ms = float(t[0]), float(t[1])
+        tot = torch.tensor([float(N), float(launches)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        N_all, launches_all = float(tot[0]), int(tot[1])
+    else:
+        N_all, launches_all = float(N), int(launches)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        peak_src = "MEASURED_PEAKS.json hbm_gbs (measured copy, burst)" if "hbm_gbs" in peaks else "fallback 6.65 TB/s"
+        c = touched * 64.0 / N
+        alg = {"p2g_tile": (28 * T + 4 + 8 * T * c) * N,     # P2G = 28T + 4 + 8T c per particle
+               "g2p": (18 * T + 3 * T * c) * N,              # G2P = 18T + 3T c
+               "fem": (28 + 83 * T) * st.n_faces()}          # FEM per face
+        kern = {}
+        tot_ms = sum(v[0] for v in prof.values())
+        for name, (tms, cnt) in prof.items():
+            per = tms / max(cnt, 1)
+            kern[name] = {"us_per_launch": per * 1e3, "launches_per_step": cnt / Kp, "share": tms / tot_ms}
+            if name in alg:
+                kern[name]["achieved_gbs"] = alg[name] / (per * 1e-3) / 1e9
+                kern[name]["frac_of_measured_peak"] = kern[name]["achieved_gbs"] / peak
+        dom = max(alg, key=lambda n: prof.get(n, (0, 1))[0])
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
+        except Exception:
+            pass
+        roofline = {"kernel": dom, "bound": "hbm", "achieved": kern[dom]["achieved_gbs"], "peak": peak, "unit": "GB/s",
+                    "frac": kern[dom]["achieved_gbs"] / peak, "traffic": traffic, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": alg[dom], "touched_cells_per_particle": c,
+                    "timing": "CUDA events between launches on the library stream, separate pass of %d steps" % Kp}
+        line = {"metric": METRIC, "value": N_all * K / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
+                "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": args.dtype, "data": "synthetic",
+                "config": {"workload": WORKLOAD, "sort_every": SORT_EVERY, "particles_per_gpu": N,
+                           "particle_blocks": pblocks, "touched_grid_blocks": touched,
+                           "l2": "inputs larger than L2 (particle state %.0f MB per step > 126 MB)" % (N * (44 * T + 8) / 1e6),
+                           "parallelism": "1 scene per GPU, no data-path collective"},
+                "clocks": clocks,
+                "e2e": {"value": N_all * Ke / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0,
+                        "d2h_bytes_per_step": int(3 * T * N), "steps": Ke, "ms_per_step": e_ms / Ke,
+                        "what": "DeformableDriver substep through the C ABI: SyncParticleStateToCpu (all positions "
+                                "to pinned host memory) + CopyContactPairs (0 pairs) + 5 solver calls"},
+                "gpu_launches": launches_all, "gpu_launches_per_step": launches_all / K / world,
+                "roofline": roofline, "kernels": kern}
+        if world == 1 and not args.no_cpu_baseline:
+            cb = cpu_baseline(dtype)
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            line["speedup_vs_cpu_port"] = {"device": line["value"] / cb["value"], "e2e": line["e2e"]["value"] / cb["value"]}
+        if world == 1 and not args.no_ref_gpu:
+            try:
+                line["reference_gpu"] = reference_gpu(dtype, 100)
+            except Exception as e:  # checker library missing or failed: not fatal for the product line
+                line["reference_gpu"] = {"unavailable": repr(e)}
+        print(json.dumps(line), flush=True)
+    st.Destroy()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

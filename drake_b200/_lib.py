@@ -34,7 +34,8 @@ TYPED_SYMBOLS = ["create", "destroy", "add_qr_cloth", "finalize", "rebuild_mappi
                  "update_contact", "reallocate_external_bodies", "external_body_force_to_host",
                  "dump_cpu_state", "n_verts", "n_faces", "n_particles", "n_cells", "num_contacts",
                  "grid_touched_cnt_host", "read", "run_substeps", "kernel_launches", "set_profiling",
-                 "kernel_time", "profile_report", "device_bytes", "block_counts"]
+                 "kernel_time", "profile_report", "timer_mark", "timer_elapsed_ms", "device_bytes",
+                 "block_counts"]
 
 _lib = None
 
@@ -98,6 +99,8 @@ def _declare(L):
         g("profile_report").argtypes = [vp, C.c_char_p, sz]
         g("profile_report").restype = sz
         g("block_counts").argtypes = [vp, u32p, u32p]
+        g("timer_mark").argtypes = [vp, C.c_int]
+        g("timer_elapsed_ms").argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_double)]
 
 
 def check(status):

@@ -213,6 +213,12 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
     }                                                                                                          \
     return r.size() + 1;                                                                                       \
   }                                                                                                            \
+  int gmpm_timer_mark_##SUF(gmpm_state_##SUF* s, int slot) {                                                   \
+    return guarded([&] { s->st.timer_mark(slot); });                                                           \
+  }                                                                                                            \
+  int gmpm_timer_elapsed_ms_##SUF(gmpm_state_##SUF* s, int a, int b, double* ms) {                             \
+    return guarded([&] { *ms = s->st.timer_elapsed_ms(a, b); });                                               \
+  }                                                                                                            \
   size_t gmpm_device_bytes_##SUF(const gmpm_state_##SUF* s) { return s->st.device_bytes; }                     \
   int gmpm_block_counts_##SUF(gmpm_state_##SUF* s, uint32_t* pb, uint32_t* tb) {                               \
     return guarded([&] {                                                                                       \

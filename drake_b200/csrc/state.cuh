@@ -199,6 +199,11 @@ struct State {
     io_buf = nullptr;
     h_pinned = nullptr;
     h_scalars = nullptr;
+    for (auto& t : timers)
+      if (t) {
+        cudaEventDestroy(t);
+        t = nullptr;
+      }
     if (stream) cudaStreamDestroy(stream);
     stream = nullptr;
   }
@@ -486,6 +491,22 @@ struct State {
     keys_valid = true;   // g2p wrote the key of every new slot
     bin_valid = false;
     fem_valid = false;
+  }
+
+  cudaEvent_t timers[16]{};
+  void timer_mark(int slot) {
+    if (slot < 0 || slot >= 16) throw std::invalid_argument("timer slot out of range");
+    bind_device();
+    if (!timers[slot]) GMPM_CUDA(cudaEventCreate(&timers[slot]));
+    GMPM_CUDA(cudaEventRecord(timers[slot], stream));
+  }
+  double timer_elapsed_ms(int a, int b) {
+    if (a < 0 || a >= 16 || b < 0 || b >= 16 || !timers[a] || !timers[b]) throw std::invalid_argument("timer slot not marked");
+    bind_device();
+    GMPM_CUDA(cudaEventSynchronize(timers[b]));
+    float ms = 0.f;
+    GMPM_CUDA(cudaEventElapsedTime(&ms, timers[a], timers[b]));
+    return (double)ms;
   }
 
   void sync() {

@@ -251,6 +251,14 @@ class GpuMpmState:
         check(self._f("kernel_time")(self._h, prefix.encode(), C.byref(ms), C.byref(n)))
         return ms.value, int(n.value)
 
+    def timer_mark(self, slot):
+        check(self._f("timer_mark")(self._h, int(slot)))
+
+    def timer_elapsed_ms(self, a, b):
+        ms = C.c_double()
+        check(self._f("timer_elapsed_ms")(self._h, int(a), int(b), C.byref(ms)))
+        return ms.value
+
     def profile_report(self):
         need = self._f("profile_report")(self._h, None, 0)
         buf = C.create_string_buffer(max(int(need), 1))

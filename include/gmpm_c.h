@@ -144,6 +144,10 @@ int gmpm_device_count(void);
                              uint64_t* launches);                                                   \
   /* writes "name ms launches\n" lines for every profiled kernel; returns bytes needed */          \
   size_t gmpm_profile_report_##SUF(gmpm_state_##SUF* s, char* buf, size_t cap);                     \
+  /* CUDA-event stopwatch on the state's stream: mark slot (0..15), then elapsed ms between two    */\
+  /* marks (synchronises on the later one).  Used by bench.py to time on the device.              */\
+  int gmpm_timer_mark_##SUF(gmpm_state_##SUF* s, int slot);                                         \
+  int gmpm_timer_elapsed_ms_##SUF(gmpm_state_##SUF* s, int slot_begin, int slot_end, double* ms);   \
   /* device bytes currently held by the state */                                                   \
   size_t gmpm_device_bytes_##SUF(const gmpm_state_##SUF* s);                                        \
   /* binning summary of the last RebuildMapping: particle blocks and touched grid blocks */        \

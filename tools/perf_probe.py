@@ -24,6 +24,11 @@ def main():
     dt = 1e-3
     sv.RunSubsteps(st, 10, dt, -1, 40)
     sv.GpuSync(st)
+    if "--quick" in sys.argv:
+        sv.RunSubsteps(st, 12, dt, -1, 40)
+        sv.GpuSync(st)
+        print("quick ok", N)
+        return
     for steps in (40, 200):
         t0 = time.perf_counter()
         sv.RunSubsteps(st, steps, dt, -1, 40)
