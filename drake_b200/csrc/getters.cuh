@@ -117,10 +117,12 @@ size_t State<T>::read(const char* name, void* out, size_t cap) {
   }
   if (n == "grid_touched_ids") return plain(touched_list[tl_cur], sizeof(uint32_t) * k.n_blocks);
   if (n == "grid_Hess" || n == "grid_Grad" || n == "grid_Dir") {
-    ensure_contact_grids();
     const int comps = n == "grid_Hess" ? 9 : 3;
     const T* src = n == "grid_Hess" ? g_Hess : (n == "grid_Grad" ? g_Grad : g_Dir);
-    return plain(src, sizeof(T) * comps * k.n_cells);
+    const size_t bytes = need(sizeof(T) * comps * k.n_cells);
+    const T* buf = contact_grid_dense(src, comps);
+    to_host(out, buf, bytes);
+    return bytes;
   }
   if (n == "contact_vel") return plain(c_vel, sizeof(T) * 3 * n_contacts);
   if (n == "contact_vel0") return plain(c_vel0, sizeof(T) * 3 * n_contacts);

@@ -64,6 +64,7 @@ struct Profiler {
 };
 
 enum class GridStage { kClean, kTiles, kMomentum, kVelocity };
+template <typename T> struct ContactScalars;  // contact.cuh
 
 template <typename T>
 struct State {
@@ -113,12 +114,20 @@ struct State {
   size_t n_contacts = 0, contact_cap = 0;
   uint32_t *c_pid = nullptr, *c_rigid_id = nullptr, *c_keys = nullptr;
   T *c_pos = nullptr, *c_vel = nullptr, *c_vel0 = nullptr, *c_dist = nullptr, *c_normal = nullptr,
-    *c_rigid_v = nullptr, *c_rigid_p = nullptr, *c_mass = nullptr, *c_v0p = nullptr;
+    *c_rigid_v = nullptr, *c_rigid_p = nullptr, *c_frame = nullptr;
+  // contact blocks (grid blocks a contact stencil reaches) and the compact Hess/Grad/Dir store
+  uint32_t *cb_epoch = nullptr, *cb_slot = nullptr, *cb_list = nullptr;
+  size_t cb_cap = 0;
+  uint32_t contact_epoch = 0;
+  bool cb_valid = false;
   T *g_Hess = nullptr, *g_Grad = nullptr, *g_Dir = nullptr;
   size_t n_bodies = 0, body_cap = 0;
   T *F_tau = nullptr, *F_f = nullptr;
-  T* d_scalars = nullptr;     // device reduction scalars of the contact solve
-  T* h_scalars = nullptr;     // pinned mirror
+  ContactScalars<T>* csc = nullptr;  // device scalars of the contact solve
+  void* h_csc = nullptr;             // pinned mirror (stats read-back)
+  void* h_stage = nullptr;           // pinned staging of CopyContactPairs
+  size_t h_stage_cap = 0;
+  int newton_ctas = 0;
   // io
   void* io_buf = nullptr;
   size_t io_cap = 0;
@@ -195,10 +204,12 @@ struct State {
     allocs.clear();
     if (io_buf) cudaFree(io_buf);
     if (h_pinned) cudaFreeHost(h_pinned);
-    if (h_scalars) cudaFreeHost(h_scalars);
+    if (h_csc) cudaFreeHost(h_csc);
+    if (h_stage) cudaFreeHost(h_stage);
     io_buf = nullptr;
     h_pinned = nullptr;
-    h_scalars = nullptr;
+    h_csc = nullptr;
+    h_stage = nullptr;
     for (auto& t : timers)
       if (t) {
         cudaEventDestroy(t);
@@ -263,8 +274,6 @@ struct State {
     g_vstar = dalloc<T>((size_t)k.n_cells * 3);
     touched_epoch = dalloc<uint32_t>(k.n_blocks);
     ctr = dalloc<DevCounters>(1);
-    d_scalars = dalloc<T>(16);
-    GMPM_CUDA(cudaMallocHost(&h_scalars, 16 * sizeof(T)));
 
     // upload: [faces | verts] (cuda_mpm_model.cu:40-45), planar
     std::vector<T> hp(3 * N, T(0)), hv(3 * N, T(0));
@@ -589,7 +598,9 @@ struct State {
   void update_contact(T dt, T mu, T stiffness, T damping, bool exact, int max_it, gmpm_contact_stats* stats);
   void reallocate_external_bodies(size_t n);
   void external_body_force_to_host(T* tau, T* f);
-  void ensure_contact_grids();
+  void reallocate_contacts(size_t n);
+  T* contact_grid_dense(const T* src, int comps);
+  void dfree(void* p);
 };
 
 }  // namespace gmpm

@@ -44,3 +44,26 @@ def stacked_sheets(n_sheets, res=100, side=0.5, z0=0.15, dz=0.02, domain_bits=7,
             vel = rng.normal(0.0, 0.1, size=pos.shape).astype(dtype)
         out.append((pos, vel, tri))
     return out
+
+
+def box_contacts(pos, lo, hi, rigid_id=1, rigid_v=(0.0, 0.0, 0.0), rigid_p_WB=None):
+    """Contact pairs of points against an axis-aligned rigid box [lo, hi], the way
+    DeformableDriver::CalcMpmContactPairs builds them (deformable_driver.h:120-194) from
+    ComputeSignedDistanceToPoint: every point strictly inside the box is one pair with
+    penetration_distance = signed distance (< 0), normal = -grad_W (grad_W = outward normal of the
+    nearest face), position = the point, rigid_v, rigid_p_WB (body origin).
+    Returns (particle_index, non_mpm_id, distance, normal, position, rigid_v, rigid_p_WB) arrays."""
+    pos = np.asarray(pos, np.float64).reshape(-1, 3)
+    lo, hi = np.asarray(lo, np.float64), np.asarray(hi, np.float64)
+    inside = np.all((pos > lo) & (pos < hi), axis=1)
+    idx = np.nonzero(inside)[0]
+    p = pos[idx]
+    d = np.concatenate([p - lo, hi - p], axis=1)          # distance to the 6 faces
+    face = np.argmin(d, axis=1)
+    dist = -d[np.arange(len(idx)), face]
+    grad = np.zeros((len(idx), 3))
+    grad[np.arange(len(idx)), face % 3] = np.where(face < 3, -1.0, 1.0)
+    center = 0.5 * (lo + hi) if rigid_p_WB is None else np.asarray(rigid_p_WB, np.float64)
+    n = len(idx)
+    return (idx.astype(np.uint32), np.full(n, rigid_id, np.uint32), dist, -grad, p,
+            np.tile(np.asarray(rigid_v, np.float64), (n, 1)), np.tile(center, (n, 1)))
