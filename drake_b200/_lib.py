@@ -27,7 +27,7 @@ class ContactStats(C.Structure):
 
 
 # every symbol include/gmpm_c.h declares (checked by tests/test_abi.py against the header text)
-PLAIN_SYMBOLS = ["gmpm_default_params", "gmpm_last_error", "gmpm_version", "gmpm_device_count",
+PLAIN_SYMBOLS = ["gmpm_default_params", "gmpm_last_error", "gmpm_version", "gmpm_device_count", "gmpm_device_sync",
                  "gmpm_morton_code", "gmpm_cell_index", "gmpm_inverse_cell_index", "gmpm_radix_sort_pairs"]
 TYPED_SYMBOLS = ["create", "destroy", "add_qr_cloth", "finalize", "rebuild_mapping", "calc_fem", "p2g",
                  "update_grid", "g2p", "sync", "sync_particle_state_to_cpu", "copy_contact_pairs",
@@ -62,6 +62,7 @@ def _declare(L):
     L.gmpm_last_error.restype = C.c_char_p
     L.gmpm_version.restype = C.c_char_p
     L.gmpm_device_count.restype = C.c_int
+    L.gmpm_device_sync.restype = C.c_int
     for n in ("gmpm_morton_code", "gmpm_cell_index"):
         getattr(L, n).argtypes = [C.c_uint32] * 3
         getattr(L, n).restype = C.c_uint32

@@ -73,7 +73,17 @@ size_t State<T>::read(const char* name, void* out, size_t cap) {
   if (n == "volumes") return particle_field(vol[cur], 1, false);
   if (n == "affine_matrices") return particle_field(C[cur], 9, false);
   if (n == "forces") return particle_field(forces, 3, false);
-  if (n == "taus") return particle_field(taus, 9, true);
+  if (n == "taus") {
+    const size_t bytes = need(sizeof(T) * 9 * N);
+    if (!N) return 0;
+    T* buf = static_cast<T*>(io(bytes));
+    launch("gather_taus");
+    gather_taus_kernel<T><<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, (uint32_t)n_faces, taus,
+                                                                 pid_of_vis[vis_cur], slot_of_pid, buf);
+    GMPM_CUDA(cudaGetLastError());
+    to_host(out, buf, bytes);
+    return bytes;
+  }
   if (n == "pids") return plain(pid_of_vis[vis_cur], sizeof(int) * N);
   if (n == "index_mappings") return plain(vis_of_pid, sizeof(int) * N);
   if (n == "sort_keys") {

@@ -61,6 +61,9 @@ int gmpm_device_count(void) {
   }
   return n;
 }
+int gmpm_device_sync(void) {
+  return guarded([&] { GMPM_CUDA(cudaDeviceSynchronize()); });
+}
 uint32_t gmpm_morton_code(uint32_t x, uint32_t y, uint32_t z) { return gmpm::morton3(x, y, z); }
 uint32_t gmpm_cell_index(uint32_t x, uint32_t y, uint32_t z) { return gmpm::cell_key(x, y, z); }
 void gmpm_inverse_cell_index(uint32_t index, uint32_t* xyz) { gmpm::inverse_cell_key(index, xyz[0], xyz[1], xyz[2]); }

@@ -2,7 +2,7 @@
 //
 // Data layout (DESIGN.md "Data layout in HBM"):
 //   particles : planar SoA by PHYSICAL slot: pos[3][N] vel[3][N] C[9][N] vol[N] pid[N], double
-//               buffered; forces[3][N], taus[9][N] by slot.  slot_of_pid[N] is the inverse of pid[].
+//               buffered; forces[3][N], taus[6][N] (the two factors of the rank-one stress) by slot.  slot_of_pid[N] is the inverse of pid[].
 //   faces     : planar by face id: tri[3][F] (original particle ids), F[9][F], Dm_inv[4][F].
 //   binning   : key[N] (block-major Morton cell key of every slot), order[N] = slots sorted by key,
 //               per-particle-block ranges pb_start/pb_end[n_blocks], compact list pb_list[].
@@ -18,6 +18,7 @@
 namespace gmpm {
 
 constexpr int kThreads = 256;
+constexpr int kChunk = 128;  // particles per unit of work (a particle block is split into chunks of <= kChunk)
 
 // Device-resident counters (no host round trips inside a substep).
 struct DevCounters {
@@ -27,8 +28,15 @@ struct DevCounters {
   uint32_t work_p2g;       // dynamic work queues of the persistent kernels
   uint32_t work_g2p;
   uint32_t work_grid;
-  uint32_t grid_dofs;      // contact solve
-  uint32_t pad;
+  uint32_t n_big;          // work records of blocks with more particles than the average (front of pb_work)
+  uint32_t n_small;        // ... the others (back of pb_work, growing down)
+  uint32_t n_tiles;        // P2G tiles handed out (one per work record)
+  uint32_t pad[3];
+};
+
+// One unit of work of the per-particle-block kernels: tile index, particle range, grid block id.
+struct alignas(16) WorkRec {
+  uint32_t tile, begin, end, block;
 };
 
 // Rolls the touched-block list and resets the P2G work queue (device side, no host round trip).
@@ -36,6 +44,13 @@ __global__ void p2g_prologue_kernel(DevCounters* ctr) {
   ctr->n_touched_prev = ctr->n_touched;
   ctr->n_touched = 0;
   ctr->work_p2g = 0;
+  ctr->work_g2p = 0;
+}
+__global__ void bin_reset_kernel(DevCounters* ctr) {
+  ctr->n_pblocks = 0;
+  ctr->n_big = 0;
+  ctr->n_small = 0;
+  ctr->n_tiles = 0;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -123,8 +138,8 @@ __global__ void permute_visible_kernel(uint32_t N, const uint32_t* __restrict__ 
 // ------------------------------------------------------------------------------------------------
 __global__ void build_pblocks_kernel(uint32_t N, const uint32_t* __restrict__ sorted_key, uint32_t epoch,
                                      uint32_t* __restrict__ pb_start, uint32_t* __restrict__ pb_end,
-                                     uint32_t* __restrict__ pb_epoch, uint32_t* __restrict__ pb_tile,
-                                     uint32_t* __restrict__ pb_list, DevCounters* ctr) {
+                                     uint32_t* __restrict__ pb_epoch, uint32_t* __restrict__ pb_list,
+                                     DevCounters* ctr) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   const bool in = i < N;
   uint32_t b = 0;
@@ -146,9 +161,33 @@ __global__ void build_pblocks_kernel(uint32_t N, const uint32_t* __restrict__ so
     if (head) {
       const uint32_t t = base + __popc(m & ((1u << lane) - 1u));
       pb_list[t] = b;
-      pb_tile[b] = t;
       pb_epoch[b] = epoch;
     }
+  }
+}
+
+// Work records: every particle block is cut into chunks of <= kChunk particles (bounded units keep the
+// persistent P2G / G2P kernels balanced whatever the block populations are), each with its own P2G
+// tile; the tiles of one block are consecutive (pb_tile[block] = {first, count}).  Full chunks are
+// appended at the front of pb_work, partial ones at the back (growing down); the kernels walk the
+// front, then the back (longest-processing-time-first keeps the tail short).
+__global__ void classify_pblocks_kernel(uint32_t cap, const uint32_t* __restrict__ pb_list,
+                                        const uint32_t* __restrict__ pb_start, const uint32_t* __restrict__ pb_end,
+                                        uint2* __restrict__ pb_tile, WorkRec* __restrict__ pb_work, DevCounters* ctr) {
+  const uint32_t n_pb = ctr->n_pblocks;
+  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_pb; t += gridDim.x * blockDim.x) {
+    const uint32_t blk = pb_list[t];
+    const uint32_t b = pb_start[blk], e = pb_end[blk];
+    const uint32_t n_full = (e - b) / kChunk, rest = (e - b) % kChunk;
+    const uint32_t n_chunks = n_full + (rest ? 1u : 0u);
+    const uint32_t tile0 = atomicAdd(&ctr->n_tiles, n_chunks);
+    pb_tile[blk] = make_uint2(tile0, n_chunks);
+    if (n_full) {
+      const uint32_t w0 = atomicAdd(&ctr->n_big, n_full);
+      for (uint32_t c = 0; c < n_full; ++c)
+        pb_work[w0 + c] = WorkRec{tile0 + c, b + c * kChunk, b + (c + 1) * kChunk, blk};
+    }
+    if (rest) pb_work[cap - 1u - atomicAdd(&ctr->n_small, 1u)] = WorkRec{tile0 + n_full, b + n_full * kChunk, e, blk};
   }
 }
 
@@ -214,11 +253,12 @@ fem_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ tri, const int*
   const T volume = vol[sf];
 #pragma unroll
   for (int e = 0; e < 9; ++e) VP[e] *= volume;
-  // tau = V * P[:,2] (x) F[:,2]
+  // tau = V * P[:,2] (x) F[:,2] is rank one: stored as its two factors, rows 0-2 and 3-5 of taus[6][N]
 #pragma unroll
-  for (int a = 0; a < 3; ++a)
-#pragma unroll
-    for (int b = 0; b < 3; ++b) taus[(a * 3 + b) * N + sf] = VP[a * 3 + 2] * ctF[b * 3 + 2];
+  for (int a = 0; a < 3; ++a) {
+    taus[(size_t)a * N + sf] = VP[a * 3 + 2];
+    taus[(size_t)(3 + a) * N + sf] = ctF[a * 3 + 2];
+  }
   // grad_N = Dm^-T * [-1 1 0; -1 0 1]
   T gN[6];
   gN[0] = Dmi[0] * T(-1) + Dmi[2] * T(-1);
@@ -242,120 +282,251 @@ fem_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ tri, const int*
 // One WARP per particle block (4^3 base cells).  The warp owns a private 6^3 x 4 shared-memory
 // tile, so there are no atomics and no barriers, and the summation order is fixed (run-to-run
 // reproducible).  Two alternating phases over batches of 32 particles of the block:
-//   (a) lanes = particles: coalesced loads through `order`, per-particle quantities to smem:
-//       the 9 one-dimensional B-spline weights, mass, a' = m v + m g dt + f dt - (B dx) fx, B dx;
-//   (b) lanes = the 27 stencil nodes: each lane accumulates its node's 4 channels in registers over
-//       a run of particles with the same base cell (the order is sorted by cell key), then adds
-//       the run total to the tile (distinct addresses across lanes -> plain read-modify-write).
+//   (a) lanes = particles: the raw particle record (prefetched into registers one batch ahead, so
+//       the global loads are in flight during phase (b) of the previous batch) is turned into a
+//       shared-memory row that makes the per-node work separable: for the 9 (i,j) stencil columns
+//       W_ij = wx_i wy_j and u_ij,d = a'_d + Bdx_d0 i + Bdx_d1 j, plus Bdx_d2, mass and wz_k;
+//   (b) lanes = the 27 stencil nodes (i,j,k): per particle 5 shared loads and 8 FMAs per lane:
+//       wt = W_ij wz_k;  mass += wt m;  mom_d += wt (u_ij,d + Bdx_d2 k); accumulated in registers
+//       over a run of particles with the same base cell (the order is sorted by cell key), then
+//       added to the tile (distinct addresses across lanes -> plain read-modify-write).
 // The tile is written to tiles[t][4][216]; grid_assemble_update sums the <= 8 tiles that overlap
 // each grid block.  Touched grid blocks are appended to a device list (epoch-stamped, no flags scan).
+// Work distribution: a device-side queue hands out blocks in two sweeps, blocks with more than the
+// average population first (longest-processing-time-first keeps the tail short); the next work item
+// and its first batch are fetched while the current block is still being processed.
 // ------------------------------------------------------------------------------------------------
-constexpr int kP2GWarps = 4;
-constexpr int kWStride = 10;  // 9 weights + pad (doubles/floats per particle)
-constexpr int kVStride = 14;  // m, a'[3], Bdx[9], pad -> 16-byte aligned rows
+constexpr int kP2GThreads = 32;  // one warp per CTA: nothing is shared between warps
+
+// Scalars per particle row: 9 x {A', G0, G1, G2} (per stencil column ij) + 3 x {z, zb0, zb1, zb2} (per k)
+// = 48, padded to an odd multiple of 16 bytes (conflict-free 128-bit row stores, 16-byte aligned rows).
+template <typename T> constexpr int kStageStride = 0;
+template <> constexpr int kStageStride<double> = 50;  // 400 B = 25 x 16
+template <> constexpr int kStageStride<float> = 52;   // 208 B = 13 x 16
 
 template <typename T>
 struct P2GSmem {
-  T tile[kP2GWarps][4][kTileNodes];
-  T sw[kP2GWarps][32][kWStride];
-  T sv[kP2GWarps][32][kVStride];
-  int scell[kP2GWarps][32];
+  T tile[4][kTileNodes];
+  T stage[32][kStageStride<T>];
 };
 
 template <typename T>
-__global__ void __launch_bounds__(kP2GWarps * 32)
+struct alignas(16) Vec4 {
+  T x, y, z, w;
+};
+
+// Raw record of one particle as P2G needs it (registers).
+template <typename T>
+struct P2GRaw {
+  T p[3], v[3], vol, C[9], ex[6];
+  bool face;
+};
+
+template <typename T>
+__device__ __forceinline__ void p2g_load(P2GRaw<T>& r, bool valid, uint32_t s, uint32_t N, uint32_t n_faces,
+                                         const T* __restrict__ pos, const T* __restrict__ vel,
+                                         const T* __restrict__ vol, const T* __restrict__ C,
+                                         const int* __restrict__ pid, const T* __restrict__ forces,
+                                         const T* __restrict__ taus) {
+  if (!valid) return;
+  r.face = (uint32_t)pid[s] < n_faces;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    r.p[d] = pos[(size_t)d * N + s];
+    r.v[d] = vel[(size_t)d * N + s];
+  }
+  r.vol = vol[s];
+#pragma unroll
+  for (int e = 0; e < 9; ++e) r.C[e] = C[(size_t)e * N + s];
+  if (r.face) {  // stress lives on face particles only: tau = ex[0:3] (x) ex[3:6]
+#pragma unroll
+    for (int e = 0; e < 6; ++e) r.ex[e] = taus[(size_t)e * N + s];
+  } else {       // nodal forces live on vertex particles only
+#pragma unroll
+    for (int d = 0; d < 3; ++d) r.ex[d] = forces[(size_t)d * N + s];
+  }
+}
+
+// Phase (a) of P2G for one particle: node (i,j,k) receives
+//   mass  += wx_i wy_j wz_k m                                   = A'_ij z_k
+//   mom_d += wx_i wy_j wz_k (a'_d + Bx_d i + By_d j + Bz_d k)    = G_ij,d z_k + A'_ij zb_k,d
+// with A'_ij = wx_i wy_j m, G_ij,d = wx_i wy_j (a'_d + Bx_d i + By_d j), z_k = wz_k,
+// zb_k,d = wz_k k Bz_d / m  (B. = (m C - dt D^-1 tau) dx, a' = m v + m g dt + f dt - B. fx).
+template <typename T>
+__device__ __forceinline__ uint32_t p2g_derive(const P2GRaw<T>& r, T* row, T dt, const Consts<T>& k) {
+  uint32_t b[3];
+  T fx[3], w[3][3];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    b[d] = base_node(r.p[d], k.dx_inv, k.domain_size);
+    fx[d] = r.p[d] * k.dx_inv - T(b[d]);
+    w[0][d] = T(0.5) * (T(1.5) - fx[d]) * (T(1.5) - fx[d]);
+    w[1][d] = T(0.75) - (fx[d] - T(1)) * (fx[d] - T(1));
+    w[2][d] = T(0.5) * (fx[d] - T(0.5)) * (fx[d] - T(0.5));
+  }
+  const T mass = r.vol * k.density;
+  const T inv_mass = mass > T(0) ? T(1) / mass : T(0);
+  T B[9];
+#pragma unroll
+  for (int e = 0; e < 9; ++e) B[e] = r.C[e] * mass;
+  T a[3] = {mass * r.v[0], mass * r.v[1], mass * r.v[2]};
+#pragma unroll
+  for (int d = 0; d < 3; ++d)
+    if (d == k.gravity_axis) a[d] += mass * k.gravity * dt;
+  if (r.face) {
+    const T cs = -dt * k.d_inv;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) B[i * 3 + j] += cs * (r.ex[i] * r.ex[3 + j]);
+  } else {
+#pragma unroll
+    for (int d = 0; d < 3; ++d) a[d] += r.ex[d] * dt;
+  }
+  T Bx[3], By[3], Bz[3], al[3];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    Bx[d] = B[d * 3 + 0] * k.dx;
+    By[d] = B[d * 3 + 1] * k.dx;
+    Bz[d] = B[d * 3 + 2] * k.dx;
+    al[d] = a[d] - (Bx[d] * fx[0] + By[d] * fx[1] + Bz[d] * fx[2]);
+  }
+  Vec4<T>* out = reinterpret_cast<Vec4<T>*>(row);
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const T A = w[i][0] * w[j][1];
+      Vec4<T> q;
+      q.x = A * mass;
+      q.y = A * (al[0] + Bx[0] * T(i) + By[0] * T(j));
+      q.z = A * (al[1] + Bx[1] * T(i) + By[1] * T(j));
+      q.w = A * (al[2] + Bx[2] * T(i) + By[2] * T(j));
+      out[i * 3 + j] = q;
+    }
+#pragma unroll
+  for (int kk = 0; kk < 3; ++kk) {
+    const T zk = w[kk][2] * T(kk) * inv_mass;
+    out[9 + kk] = Vec4<T>{w[kk][2], zk * Bz[0], zk * Bz[1], zk * Bz[2]};
+  }
+  // which neighbour blocks (+x,+y,+z combinations) does this stencil reach
+  uint32_t reach = 1u;  // bit (dx*4+dy*2+dz) per reached neighbour; delta = 0 always
+  if ((b[0] & 3u) >= 2u) reach |= reach << 4;
+  if ((b[1] & 3u) >= 2u) reach |= reach << 2;
+  if ((b[2] & 3u) >= 2u) reach |= reach << 1;
+  return reach;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kP2GThreads)
 p2g_tile_kernel(uint32_t N, uint32_t n_faces, const uint32_t* __restrict__ order,
-                const uint32_t* __restrict__ sorted_key, const uint32_t* __restrict__ pb_list,
-                const uint32_t* __restrict__ pb_start, const uint32_t* __restrict__ pb_end,
+                const uint32_t* __restrict__ sorted_key, const WorkRec* __restrict__ pb_work, uint32_t work_cap,
                 const T* __restrict__ pos, const T* __restrict__ vel, const T* __restrict__ vol,
                 const T* __restrict__ C, const int* __restrict__ pid, const T* __restrict__ forces,
                 const T* __restrict__ taus, T* __restrict__ tiles, uint32_t* __restrict__ touched_epoch,
                 uint32_t* __restrict__ touched_list, uint32_t epoch, DevCounters* ctr, T dt, Consts<T> k) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   P2GSmem<T>& sm = *reinterpret_cast<P2GSmem<T>*>(smem_raw);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  T* tile = &sm.tile[warp][0][0];
-  const uint32_t n_pb = ctr->n_pblocks;
+  const int lane = threadIdx.x;
+  T* tile = &sm.tile[0][0];
+  const uint32_t n_big = ctr->n_big, n_work = n_big + ctr->n_small;
+  if (n_work == 0) return;
   const int ni = lane / 9, nj = (lane / 3) % 3, nk = lane % 3;  // node of this lane (lane < 27)
   const bool node_lane = lane < 27;
-  const T fi = T(ni), fj = T(nj), fk = T(nk);
+  const int ij = node_lane ? ni * 3 + nj : 0, kz = node_lane ? nk : 0;
   const uint32_t blocks_per_axis = (uint32_t)k.domain_size >> 2;
 
-  for (;;) {
+  // work item pipeline: `cur` is being processed, `nxt` is resolved, one queue ticket is in flight
+  constexpr uint32_t kNone = 0xFFFFFFFFu;
+  using Item = WorkRec;
+  auto ticket = [&]() -> uint32_t {
     uint32_t t = 0;
     if (lane == 0) t = atomicAdd(&ctr->work_p2g, 1u);
-    t = __shfl_sync(kFullMask, t, 0);
-    if (t >= n_pb) break;
-    const uint32_t blk = pb_list[t];
-    const uint32_t begin = pb_start[blk], end = pb_end[blk];
+    return t;
+  };
+  auto resolve = [&](uint32_t t_lane0) -> Item {
+    const uint32_t t = __shfl_sync(kFullMask, t_lane0, 0);
+    if (t >= n_work) return Item{kNone, 0u, 0u, 0u};
+    return pb_work[t < n_big ? t : work_cap - 1u - (t - n_big)];
+  };
+  Item cur = resolve(ticket());
+  if (cur.tile == kNone) return;
+  Item nxt = resolve(ticket());
+  // two-level prefetch: the slot index and key two batches ahead, the particle record one batch ahead
+  // (a dependent load in program order would stall the warp for a full memory round trip)
+  uint32_t s_a = 0, key_a = 0, s_b = 0, key_b = 0;  // _a: next batch to load records for; _b: the one after
+  bool v_a = cur.begin + lane < cur.end;
+  if (v_a) {
+    s_a = order[cur.begin + lane];
+    key_a = sorted_key[cur.begin + lane];
+  }
+  auto batch_after = [&](const Item& c, const Item& n, uint32_t p0, uint32_t& s, uint32_t& key) -> bool {
+    // batch following the one that starts at p0 of item c (continuing into item n)
+    uint32_t i;
+    uint32_t end;
+    if (p0 + 32 < c.end) {
+      i = p0 + 32 + lane;
+      end = c.end;
+    } else if (n.tile != kNone) {
+      i = n.begin + lane;
+      end = n.end;
+    } else {
+      return false;
+    }
+    if (i >= end) return false;
+    s = order[i];
+    key = sorted_key[i];
+    return true;
+  };
+  bool v_b = batch_after(cur, nxt, cur.begin, s_b, key_b);
+  P2GRaw<T> raw;
+  p2g_load(raw, v_a, s_a, N, n_faces, pos, vel, vol, C, pid, forces, taus);
+  uint32_t key_cur = key_a;  // key of the particle whose record is in `raw`
+
+  for (;;) {
+    const uint32_t blk = cur.block;
     for (int i = lane; i < 4 * kTileNodes; i += 32) tile[i] = T(0);
     uint32_t reach = 0;
     T acc0 = T(0), acc1 = T(0), acc2 = T(0), acc3 = T(0);
-    int cur_cell = -1;
+    int run_cell = -1, last_cell = -1;
+    uint32_t t_pending = ticket();  // the item after `nxt`
+    Item nn{kNone, 0u, 0u, 0u};
     __syncwarp();
 
-    for (uint32_t p0 = begin; p0 < end; p0 += 32) {
+    for (uint32_t p0 = cur.begin; p0 < cur.end; p0 += 32) {
+      const bool last_batch = p0 + 32 >= cur.end;
       // ---- phase (a): lanes = particles
-      const uint32_t i = p0 + lane;
-      if (i < end) {
-        const uint32_t s = order[i];
-        const uint32_t key = sorted_key[i];
-        const T px = pos[s], py = pos[N + s], pz = pos[2 * N + s];
-        const uint32_t bx = base_node(px, k.dx_inv, k.domain_size);
-        const uint32_t by = base_node(py, k.dx_inv, k.domain_size);
-        const uint32_t bz = base_node(pz, k.dx_inv, k.domain_size);
-        const T fx[3] = {px * k.dx_inv - T(bx), py * k.dx_inv - T(by), pz * k.dx_inv - T(bz)};
-        T* w = &sm.sw[warp][lane][0];
-#pragma unroll
-        for (int d = 0; d < 3; ++d) {
-          w[0 * 3 + d] = T(0.5) * (T(1.5) - fx[d]) * (T(1.5) - fx[d]);
-          w[1 * 3 + d] = T(0.75) - (fx[d] - T(1)) * (fx[d] - T(1));
-          w[2 * 3 + d] = T(0.5) * (fx[d] - T(0.5)) * (fx[d] - T(0.5));
-        }
-        const T mass = vol[s] * k.density;
-        T B[9];
-        const bool is_face = (uint32_t)pid[s] < n_faces;
-#pragma unroll
-        for (int e = 0; e < 9; ++e) B[e] = C[e * N + s] * mass;
-        T a[3] = {mass * vel[s], mass * vel[N + s], mass * vel[2 * N + s]};
-#pragma unroll
-        for (int d = 0; d < 3; ++d)
-          if (d == k.gravity_axis) a[d] += mass * k.gravity * dt;
-        if (is_face) {  // stress lives on face particles only (taus of vertices are zero)
-          const T cs = -dt * k.d_inv;
-#pragma unroll
-          for (int e = 0; e < 9; ++e) B[e] += cs * taus[e * N + s];
-        } else {        // nodal forces live on vertex particles only
-#pragma unroll
-          for (int d = 0; d < 3; ++d) a[d] += forces[d * N + s] * dt;
-        }
-        T* v = &sm.sv[warp][lane][0];
-        v[0] = mass;
-#pragma unroll
-        for (int d = 0; d < 3; ++d) {
-          const T b0 = B[d * 3 + 0] * k.dx, b1 = B[d * 3 + 1] * k.dx, b2 = B[d * 3 + 2] * k.dx;
-          v[4 + d * 3 + 0] = b0;
-          v[4 + d * 3 + 1] = b1;
-          v[4 + d * 3 + 2] = b2;
-          v[1 + d] = a[d] - (b0 * fx[0] + b1 * fx[1] + b2 * fx[2]);
-        }
-        sm.scell[warp][lane] = (int)(key & 63u);
-        // which neighbour blocks (+x,+y,+z combinations) does this stencil reach
-        const uint32_t ox = (bx & 3u) >= 2u, oy = (by & 3u) >= 2u, oz = (bz & 3u) >= 2u;
-        uint32_t r = 1u;  // bit (dx*4+dy*2+dz) per reached neighbour; delta = 0 always
-        if (ox) r |= r << 4;
-        if (oy) r |= r << 2;
-        if (oz) r |= r << 1;
-        reach |= r;
-      }
+      const bool valid = p0 + lane < cur.end;
+      const int my_cell = (int)(key_cur & 63u);
+      if (valid) reach |= p2g_derive(raw, &sm.stage[lane][0], dt, k);
+      // run heads of this batch (the order is sorted by cell key inside a block)
+      int prev = __shfl_up_sync(kFullMask, my_cell, 1);
+      if (lane == 0) prev = last_cell;
+      const uint32_t heads = __ballot_sync(kFullMask, valid && my_cell != prev);
+      const int cnt = (int)min(32u, cur.end - p0);
+      last_cell = __shfl_sync(kFullMask, my_cell, cnt - 1);
       __syncwarp();
-      // ---- phase (b): lanes = stencil nodes
-      const int cnt = (int)min(32u, end - p0);
+      // ---- prefetch: records of the next batch, indices of the one after
+      if (last_batch && nxt.tile != kNone) nn = resolve(t_pending);  // needed to look two batches ahead
+      p2g_load(raw, v_b, s_b, N, n_faces, pos, vel, vol, C, pid, forces, taus);
+      key_cur = key_b;
+      {
+        // the batch after next: relative to the batch that `raw` now holds
+        const bool in_cur = !last_batch;
+        const Item& c2 = in_cur ? cur : nxt;
+        const Item& n2 = in_cur ? nxt : nn;
+        const uint32_t p2 = in_cur ? p0 + 32 : nxt.begin;
+        v_b = (in_cur || nxt.tile != kNone) ? batch_after(c2, n2, p2, s_b, key_b) : false;
+      }
+      // ---- phase (b): lanes = stencil nodes; the loads of particle q + 1 are issued before the math of q
+      auto row_of = [&](int q) { return reinterpret_cast<const Vec4<T>*>(&sm.stage[q][0]); };
+      Vec4<T> a4 = row_of(0)[ij], z4 = row_of(0)[9 + kz];
       for (int q = 0; q < cnt; ++q) {
-        const int c = sm.scell[warp][q];
-        if (c != cur_cell) {
-          if (cur_cell >= 0 && node_lane) {
-            const int n = (((cur_cell >> 4) & 3) + ni) * 36 + (((cur_cell >> 2) & 3) + nj) * 6 + ((cur_cell & 3) + nk);
+        const int qn = q + 1 < cnt ? q + 1 : q;
+        const Vec4<T> a4n = row_of(qn)[ij], z4n = row_of(qn)[9 + kz];
+        if ((heads >> q) & 1u) {
+          if (run_cell >= 0 && node_lane) {
+            const int n = (((run_cell >> 4) & 3) + ni) * 36 + (((run_cell >> 2) & 3) + nj) * 6 + ((run_cell & 3) + nk);
             tile[0 * kTileNodes + n] += acc0;
             tile[1 * kTileNodes + n] += acc1;
             tile[2 * kTileNodes + n] += acc2;
@@ -363,22 +534,19 @@ p2g_tile_kernel(uint32_t N, uint32_t n_faces, const uint32_t* __restrict__ order
           }
           __syncwarp();
           acc0 = acc1 = acc2 = acc3 = T(0);
-          cur_cell = c;
+          run_cell = __shfl_sync(kFullMask, my_cell, q);
         }
-        if (node_lane) {
-          const T* w = &sm.sw[warp][q][0];
-          const T* v = &sm.sv[warp][q][0];
-          const T wt = w[ni * 3 + 0] * w[nj * 3 + 1] * w[nk * 3 + 2];
-          acc0 += v[0] * wt;
-          acc1 += (v[1] + v[4] * fi + v[5] * fj + v[6] * fk) * wt;
-          acc2 += (v[2] + v[7] * fi + v[8] * fj + v[9] * fk) * wt;
-          acc3 += (v[3] + v[10] * fi + v[11] * fj + v[12] * fk) * wt;
-        }
+        acc0 += a4.x * z4.x;
+        acc1 += a4.y * z4.x + a4.x * z4.y;
+        acc2 += a4.z * z4.x + a4.x * z4.z;
+        acc3 += a4.w * z4.x + a4.x * z4.w;
+        a4 = a4n;
+        z4 = z4n;
       }
       __syncwarp();
     }
-    if (cur_cell >= 0 && node_lane) {
-      const int n = (((cur_cell >> 4) & 3) + ni) * 36 + (((cur_cell >> 2) & 3) + nj) * 6 + ((cur_cell & 3) + nk);
+    if (run_cell >= 0 && node_lane) {
+      const int n = (((run_cell >> 4) & 3) + ni) * 36 + (((run_cell >> 2) & 3) + nj) * 6 + ((run_cell & 3) + nk);
       tile[0 * kTileNodes + n] += acc0;
       tile[1 * kTileNodes + n] += acc1;
       tile[2 * kTileNodes + n] += acc2;
@@ -386,7 +554,7 @@ p2g_tile_kernel(uint32_t N, uint32_t n_faces, const uint32_t* __restrict__ order
     }
     __syncwarp();
     // ---- flush the tile (coalesced) and publish the touched grid blocks
-    T* out = tiles + (size_t)t * (4 * kTileNodes);
+    T* out = tiles + (size_t)cur.tile * (4 * kTileNodes);
     for (int i = lane; i < 4 * kTileNodes; i += 32) out[i] = tile[i];
     reach = __reduce_or_sync(kFullMask, reach);
     if (lane < 8 && ((reach >> lane) & 1u)) {
@@ -401,6 +569,9 @@ p2g_tile_kernel(uint32_t N, uint32_t n_faces, const uint32_t* __restrict__ order
       }
     }
     __syncwarp();
+    if (nxt.tile == kNone) break;
+    cur = nxt;
+    nxt = nn;
   }
 }
 
@@ -473,7 +644,7 @@ __device__ __forceinline__ void apply_boundary_and_colliders(const Consts<T>& k,
 template <typename T, bool ASSEMBLE, bool UPDATE>
 __global__ void __launch_bounds__(kThreads)
 grid_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __restrict__ ctr,
-            const T* __restrict__ tiles, const uint32_t* __restrict__ pb_tile, const uint32_t* __restrict__ pb_epoch,
+            const T* __restrict__ tiles, const uint2* __restrict__ pb_tile, const uint32_t* __restrict__ pb_epoch,
             uint32_t epoch, T* __restrict__ g_mass, T* __restrict__ g_vel, T* __restrict__ g_vstar, int bc,
             Consts<T> k) {
   const uint32_t n_touched = ctr->n_touched;
@@ -495,12 +666,15 @@ grid_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __rest
         if ((ddx && (lx >= 2u || gx == 0u)) || (ddy && (ly >= 2u || gy == 0u)) || (ddz && (lz >= 2u || gz == 0u))) continue;
         const uint32_t src = morton3(gx - ddx, gy - ddy, gz - ddz);
         if (pb_epoch[src] != epoch) continue;
-        const T* tl = tiles + (size_t)pb_tile[src] * (4 * kTileNodes);
+        const uint2 tr = pb_tile[src];
         const uint32_t n = (lx + 4u * ddx) * 36u + (ly + 4u * ddy) * 6u + (lz + 4u * ddz);
-        m += tl[n];
-        p[0] += tl[kTileNodes + n];
-        p[1] += tl[2 * kTileNodes + n];
-        p[2] += tl[3 * kTileNodes + n];
+        for (uint32_t c = 0; c < tr.y; ++c) {  // the chunks of particle block `src`, in chunk order
+          const T* tl = tiles + (size_t)(tr.x + c) * (4 * kTileNodes);
+          m += tl[n];
+          p[0] += tl[kTileNodes + n];
+          p[1] += tl[2 * kTileNodes + n];
+          p[2] += tl[3 * kTileNodes + n];
+        }
       }
       if (!UPDATE) {
         g_mass[cell] = m;
@@ -561,9 +735,8 @@ clean_stale_blocks_kernel(const uint32_t* __restrict__ prev_list, const DevCount
 constexpr int kG2PWarps = 4;
 
 template <typename T>
-__global__ void __launch_bounds__(kG2PWarps * 32)
-g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const uint32_t* __restrict__ pb_list,
-           const uint32_t* __restrict__ pb_start, const uint32_t* __restrict__ pb_end,
+__global__ void __launch_bounds__(kG2PWarps * 32, 6)
+g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __restrict__ pb_work, uint32_t work_cap,
            const T* __restrict__ g_vel, const T* __restrict__ pos, const T* __restrict__ vol,
            const int* __restrict__ pid, T* __restrict__ pos_out, T* __restrict__ vel_out, T* __restrict__ C_out,
            T* __restrict__ vol_out, int* __restrict__ pid_out, int* __restrict__ slot_of_pid,
@@ -571,17 +744,26 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const uint32_t* __res
   __shared__ T s_vel[kG2PWarps][3][kTileNodes];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   T* tv = &s_vel[warp][0][0];
-  const uint32_t n_pb = ctr->n_pblocks;
+  const uint32_t n_big = ctr->n_big, n_work = n_big + ctr->n_small;
   const uint32_t blocks_per_axis = (uint32_t)k.domain_size >> 2;
-  for (;;) {
-    uint32_t t = 0;
-    if (lane == 0) t = atomicAdd(&ctr->work_g2p, 1u);
-    t = __shfl_sync(kFullMask, t, 0);
-    if (t >= n_pb) break;
-    const uint32_t blk = pb_list[t];
-    const uint32_t begin = pb_start[blk], end = pb_end[blk];
+  const T scale = T(4) * k.dx_inv;
+  const T ca = (k.v_blend + T(1)) * T(.5), cb = (k.v_blend - T(1)) * T(.5);
+  uint32_t t = 0;
+  if (lane == 0) t = atomicAdd(&ctr->work_g2p, 1u);
+  t = __shfl_sync(kFullMask, t, 0);
+  while (t < n_work) {
+    const WorkRec w = pb_work[t < n_big ? t : work_cap - 1u - (t - n_big)];
+    uint32_t t_next = 0;
+    if (lane == 0) t_next = atomicAdd(&ctr->work_g2p, 1u);  // in flight while this chunk is processed
+    // slot indices of the whole chunk (<= kChunk = 4 batches) first: the position loads depend on them
+    uint32_t sidx[kChunk / 32];
+#pragma unroll
+    for (int b4 = 0; b4 < kChunk / 32; ++b4) {
+      const uint32_t ii = w.begin + b4 * 32 + lane;
+      sidx[b4] = ii < w.end ? order[ii] : 0u;
+    }
     uint32_t bx, by, bz;
-    block_coords(blk, bx, by, bz);
+    block_coords(w.block, bx, by, bz);
     // stage the reachable velocity nodes
     for (int n = lane; n < kTileNodes; n += 32) {
       const uint32_t tx = n / 36, ty = (n / 6) % 6, tz = n % 6;
@@ -597,64 +779,103 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const uint32_t* __res
       tv[kTileNodes + n] = v1;
       tv[2 * kTileNodes + n] = v2;
     }
+    uint32_t i = w.begin + lane;
+    uint32_t s = sidx[0];
+    T x[3] = {T(0), T(0), T(0)};
+    if (i < w.end) {
+      x[0] = pos[s];
+      x[1] = pos[(size_t)N + s];
+      x[2] = pos[(size_t)2 * N + s];
+    }
+    static_assert(kChunk == 128, "the slot-index rotation below assumes 4 batches per chunk");
+    uint32_t s1 = sidx[1], s2 = sidx[2], s3 = sidx[3];
     __syncwarp();
-    for (uint32_t i = begin + lane; i < end; i += 32) {
-      const uint32_t s = order[i];
-      T x[3] = {pos[s], pos[N + s], pos[2 * N + s]};
+    while (i < w.end) {
+      // prefetch the next batch (its slot index is already here)
+      const uint32_t i_n = i + 32;
+      const uint32_t s_n = s1;
+      s1 = s2;
+      s2 = s3;
+      T x_n[3] = {T(0), T(0), T(0)};
+      if (i_n < w.end) {
+        x_n[0] = pos[s_n];
+        x_n[1] = pos[(size_t)N + s_n];
+        x_n[2] = pos[(size_t)2 * N + s_n];
+      }
+      const T pvol = vol[s];
+      const int p = pid[s];
       uint32_t b[3];
-      T fx[3], w[3][3];
+      T fx[3], wt[3][3];
 #pragma unroll
       for (int d = 0; d < 3; ++d) {
         b[d] = base_node(x[d], k.dx_inv, k.domain_size);
         fx[d] = x[d] * k.dx_inv - T(b[d]);
-        w[0][d] = T(0.5) * (T(1.5) - fx[d]) * (T(1.5) - fx[d]);
-        w[1][d] = T(0.75) - (fx[d] - T(1)) * (fx[d] - T(1));
-        w[2][d] = T(0.5) * (fx[d] - T(0.5)) * (fx[d] - T(0.5));
+        wt[0][d] = T(0.5) * (T(1.5) - fx[d]) * (T(1.5) - fx[d]);
+        wt[1][d] = T(0.75) - (fx[d] - T(1)) * (fx[d] - T(1));
+        wt[2][d] = T(0.5) * (fx[d] - T(0.5)) * (fx[d] - T(0.5));
       }
       const int n0 = (int)((b[0] & 3u) * 36u + (b[1] & 3u) * 6u + (b[2] & 3u));
-      T nv[3] = {T(0), T(0), T(0)};
-      T S[9] = {T(0), T(0), T(0), T(0), T(0), T(0), T(0), T(0), T(0)};
+      // Separable accumulation of nv[a] = sum w v_a and the first moments M[a][c] = sum w v_a n_c
+      // (n = stencil offset 0..2 per axis); then sum w v_a (n_c - fx_c) = M[a][c] - fx_c nv[a].
+      const T wz2x2 = T(2) * wt[2][2];
+      T nv[3] = {T(0), T(0), T(0)}, Mx[3] = {T(0), T(0), T(0)}, My[3] = {T(0), T(0), T(0)}, Mz[3] = {T(0), T(0), T(0)};
 #pragma unroll
-      for (int ii = 0; ii < 3; ++ii)
+      for (int ii = 0; ii < 3; ++ii) {
+        T s00[3] = {T(0), T(0), T(0)}, s0y[3] = {T(0), T(0), T(0)}, s0z[3] = {T(0), T(0), T(0)};
 #pragma unroll
         for (int jj = 0; jj < 3; ++jj) {
-          const T wij = w[ii][0] * w[jj][1];
+          const int n = n0 + ii * 36 + jj * 6;
+          const T wy = wt[jj][1];
 #pragma unroll
-          for (int kk = 0; kk < 3; ++kk) {
-            const int n = n0 + ii * 36 + jj * 6 + kk;
-            const T wt = wij * w[kk][2];
-            const T xi[3] = {T(ii) - fx[0], T(jj) - fx[1], T(kk) - fx[2]};
-#pragma unroll
-            for (int a = 0; a < 3; ++a) {
-              const T wg = wt * tv[a * kTileNodes + n];
-              nv[a] += wg;
-              S[a * 3 + 0] += wg * xi[0];
-              S[a * 3 + 1] += wg * xi[1];
-              S[a * 3 + 2] += wg * xi[2];
-            }
+          for (int a = 0; a < 3; ++a) {
+            const T v0 = tv[a * kTileNodes + n], v1 = tv[a * kTileNodes + n + 1], v2 = tv[a * kTileNodes + n + 2];
+            const T t0 = wt[0][2] * v0 + wt[1][2] * v1 + wt[2][2] * v2;
+            const T t1 = wt[1][2] * v1 + wz2x2 * v2;
+            s00[a] += wy * t0;
+            s0z[a] += wy * t1;
+            if (jj) s0y[a] += (T(jj) * wy) * t0;
           }
         }
-      const T scale = T(4) * k.dx_inv;
-      const T ca = (k.v_blend + T(1)) * T(.5), cb = (k.v_blend - T(1)) * T(.5);
+        const T wx = wt[ii][0];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+          nv[a] += wx * s00[a];
+          My[a] += wx * s0y[a];
+          Mz[a] += wx * s0z[a];
+          if (ii) Mx[a] += (T(ii) * wx) * s00[a];
+        }
+      }
+      T S[9];
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        S[a * 3 + 0] = Mx[a] - fx[0] * nv[a];
+        S[a * 3 + 1] = My[a] - fx[1] * nv[a];
+        S[a * 3 + 2] = Mz[a] - fx[2] * nv[a];
+      }
 #pragma unroll
       for (int a = 0; a < 3; ++a)
 #pragma unroll
         for (int c = 0; c < 3; ++c)
-          C_out[(a * 3 + c) * N + i] = ca * (scale * S[a * 3 + c]) + cb * (scale * S[c * 3 + a]);
+          C_out[(size_t)(a * 3 + c) * N + i] = ca * (scale * S[a * 3 + c]) + cb * (scale * S[c * 3 + a]);
 #pragma unroll
       for (int d = 0; d < 3; ++d) {
         x[d] += nv[d] * dt;
-        vel_out[d * N + i] = nv[d];
-        pos_out[d * N + i] = x[d];
+        vel_out[(size_t)d * N + i] = nv[d];
+        pos_out[(size_t)d * N + i] = x[d];
       }
-      vol_out[i] = vol[s];
-      const int p = pid[s];
+      vol_out[i] = pvol;
       pid_out[i] = p;
       slot_of_pid[p] = (int)i;
       key_out[i] = cell_key(base_node(x[0], k.dx_inv, k.domain_size), base_node(x[1], k.dx_inv, k.domain_size),
                             base_node(x[2], k.dx_inv, k.domain_size));
+      i = i_n;
+      s = s_n;
+      x[0] = x_n[0];
+      x[1] = x_n[1];
+      x[2] = x_n[2];
     }
     __syncwarp();
+    t = __shfl_sync(kFullMask, t_next, 0);
   }
 }
 
@@ -669,6 +890,20 @@ __global__ void gather_particle_field_kernel(uint32_t N, int comps, const T* __r
   if (v >= N) return;
   const int s = slot_of_pid[pid_of_vis[v]];
   for (int c = 0; c < comps; ++c) out[(size_t)v * comps + c] = src[(size_t)c * N + s];
+}
+// Reference layout of taus (9 per particle, zero on vertex particles) from the two stored factors.
+template <typename T>
+__global__ void gather_taus_kernel(uint32_t N, uint32_t n_faces, const T* __restrict__ taus,
+                                   const int* __restrict__ pid_of_vis, const int* __restrict__ slot_of_pid,
+                                   T* __restrict__ out) {
+  const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= N) return;
+  const int p = pid_of_vis[v];
+  const int s = slot_of_pid[p];
+  const bool face = (uint32_t)p < n_faces;
+  for (int a = 0; a < 3; ++a)
+    for (int b = 0; b < 3; ++b)
+      out[(size_t)v * 9 + a * 3 + b] = face ? taus[(size_t)a * N + s] * taus[(size_t)(3 + b) * N + s] : T(0);
 }
 template <typename T>
 __global__ void transpose_planar_kernel(uint32_t n, int comps, const T* __restrict__ src, T* __restrict__ out) {

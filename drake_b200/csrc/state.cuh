@@ -100,7 +100,10 @@ struct State {
   uint32_t *skeys[2]{}, *svals[2]{};
   int sres = 0;
   uint32_t* sort_scratch = nullptr;
-  uint32_t *pb_start = nullptr, *pb_end = nullptr, *pb_epoch = nullptr, *pb_tile = nullptr, *pb_list = nullptr;
+  uint32_t *pb_start = nullptr, *pb_end = nullptr, *pb_epoch = nullptr, *pb_list = nullptr;
+  uint2* pb_tile = nullptr;
+  WorkRec* pb_work = nullptr;
+  size_t work_cap = 0;
   bool keys_valid = false, bin_valid = false, fem_valid = false;
   uint32_t bin_epoch = 0, p2g_epoch = 0;
   // grid
@@ -139,6 +142,8 @@ struct State {
   uint64_t launches = 0;
   Profiler prof;
   int sm_count = 148;
+  int p2g_ctas_per_sm = 1, g2p_ctas_per_sm = 1;
+  bool g2p_queue_ready = false;
 
   // ---------------------------------------------------------------------------------------------
   template <typename U>
@@ -254,7 +259,7 @@ struct State {
       touched_list[b] = dalloc<uint32_t>(k.n_blocks);
     }
     forces = dalloc<T>(3 * N);
-    taus = dalloc<T>(9 * N);
+    taus = dalloc<T>(6 * N);
     slot_of_pid = dalloc<int>(N);
     vis_of_pid = dalloc<int>(N);
     key = dalloc<uint32_t>(N);
@@ -265,9 +270,12 @@ struct State {
     pb_start = dalloc<uint32_t>(k.n_blocks);
     pb_end = dalloc<uint32_t>(k.n_blocks);
     pb_epoch = dalloc<uint32_t>(k.n_blocks);
-    pb_tile = dalloc<uint32_t>(k.n_blocks);
+    pb_tile = dalloc<uint2>(k.n_blocks);
     pb_list = dalloc<uint32_t>(k.n_blocks);
-    const size_t tile_cap = std::min<size_t>(k.n_blocks, std::max<size_t>(N, 1));
+    // one tile / work record per chunk: every block has at most one partial chunk
+    const size_t tile_cap = std::min<size_t>(k.n_blocks, std::max<size_t>(N, 1)) + N / kChunk + 1;
+    work_cap = tile_cap;
+    pb_work = dalloc<WorkRec>(work_cap);
     tiles = dalloc<T>(tile_cap * 4 * kTileNodes, false);
     g_mass = dalloc<T>(k.n_cells);
     g_vel = dalloc<T>((size_t)k.n_cells * 3);
@@ -299,6 +307,11 @@ struct State {
     }
     GMPM_CUDA(cudaFuncSetAttribute(p2g_tile_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)sizeof(P2GSmem<T>)));
+    GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p2g_ctas_per_sm, p2g_tile_kernel<T>, kP2GThreads,
+                                                            sizeof(P2GSmem<T>)));
+    if (p2g_ctas_per_sm < 1) throw CudaError(cudaErrorLaunchOutOfResources, "p2g_tile_kernel does not fit on an SM");
+    GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g2p_ctas_per_sm, g2p_kernel<T>, kG2PWarps * 32, 0));
+    g2p_ctas_per_sm = std::max(1, std::min(g2p_ctas_per_sm, 8));
     GMPM_CUDA(cudaStreamSynchronize(stream));  // host staging vectors go out of scope
     finalized = true;
     keys_valid = bin_valid = false;
@@ -330,12 +343,16 @@ struct State {
     // first pass reads `key` (by slot) and generates slot ids; later passes ping-pong skeys/svals
     sres = sort_from(key, skeys, svals, (uint32_t)N, key_bits());
     ++bin_epoch;
-    note("memset");
-    GMPM_CUDA(cudaMemsetAsync(&ctr->n_pblocks, 0, sizeof(uint32_t), stream));
+    launch("bin_reset");
+    bin_reset_kernel<<<1, 1, 0, stream>>>(ctr);
     launch("build_pblocks");
     build_pblocks_kernel<<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, skeys[sres], bin_epoch, pb_start,
-                                                                pb_end, pb_epoch, pb_tile, pb_list, ctr);
+                                                                pb_end, pb_epoch, pb_list, ctr);
+    launch("classify_pblocks");
+    classify_pblocks_kernel<<<std::min<uint32_t>(blocks_for(work_cap), 2u * sm_count), kThreads, 0, stream>>>(
+        (uint32_t)work_cap, pb_list, pb_start, pb_end, pb_tile, pb_work, ctr);
     GMPM_CUDA(cudaGetLastError());
+    g2p_queue_ready = false;
     bin_valid = true;
   }
 
@@ -446,9 +463,10 @@ struct State {
     launch("p2g_prologue");
     p2g_prologue_kernel<<<1, 1, 0, stream>>>(ctr);
     launch("p2g_tile");
-    p2g_tile_kernel<T><<<persistent_ctas(4), kP2GWarps * 32, sizeof(P2GSmem<T>), stream>>>(
-        (uint32_t)N, (uint32_t)n_faces, order(), sorted_keys(), pb_list, pb_start, pb_end, pos[cur], vel[cur],
+    p2g_tile_kernel<T><<<persistent_ctas(p2g_ctas_per_sm), kP2GThreads, sizeof(P2GSmem<T>), stream>>>(
+        (uint32_t)N, (uint32_t)n_faces, order(), sorted_keys(), pb_work, (uint32_t)work_cap, pos[cur], vel[cur],
         vol[cur], C[cur], pid[cur], forces, taus, tiles, touched_epoch, touched_list[tl_cur], p2g_epoch, ctr, dt, k);
+    g2p_queue_ready = true;  // the prologue reset both work queues
     launch("clean_stale_blocks");
     clean_stale_blocks_kernel<T><<<persistent_ctas(2), kThreads, 0, stream>>>(touched_list[tl_cur ^ 1], ctr,
                                                                              touched_epoch, p2g_epoch, g_mass, g_vel);
@@ -488,12 +506,15 @@ struct State {
     if (N == 0) return;
     assemble_momentum();  // only if UpdateGrid was skipped by the caller
     ensure_binning();
-    note("memset");
-    GMPM_CUDA(cudaMemsetAsync(&ctr->work_g2p, 0, sizeof(uint32_t), stream));
+    if (!g2p_queue_ready) {
+      note("memset");
+      GMPM_CUDA(cudaMemsetAsync(&ctr->work_g2p, 0, sizeof(uint32_t), stream));
+    }
+    g2p_queue_ready = false;
     launch("g2p");
     const int nx = cur ^ 1;
-    g2p_kernel<T><<<persistent_ctas(4), kG2PWarps * 32, 0, stream>>>(
-        (uint32_t)N, order(), pb_list, pb_start, pb_end, g_vel, pos[cur], vol[cur], pid[cur], pos[nx], vel[nx], C[nx],
+    g2p_kernel<T><<<persistent_ctas(g2p_ctas_per_sm), kG2PWarps * 32, 0, stream>>>(
+        (uint32_t)N, order(), pb_work, (uint32_t)work_cap, g_vel, pos[cur], vol[cur], pid[cur], pos[nx], vel[nx], C[nx],
         vol[nx], pid[nx], slot_of_pid, key, ctr, dt, k);
     GMPM_CUDA(cudaGetLastError());
     cur = nx;

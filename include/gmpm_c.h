@@ -74,6 +74,8 @@ const char* gmpm_last_error(void);
 const char* gmpm_version(void);
 /* Number of CUDA devices visible (0 -> every create fails). */
 int gmpm_device_count(void);
+/* GpuMpmSolver<T>::GpuSync, cuda_mpm_solver.cu:164-166: device-wide barrier (all states' streams). */
+int gmpm_device_sync(void);
 
 #define GMPM_DECLARE(SUF, T)                                                                        \
   typedef struct gmpm_state_##SUF gmpm_state_##SUF;                                                 \

@@ -1,0 +1,177 @@
+// Drop-in replacement header for the reference's multibody/gpu_mpm/cuda_mpm_model.cuh:20-260.
+// GpuMpmState<T> here is a value-semantic HANDLE to a state that lives inside libgmpm_b200.so
+// (gmpm_c.h): copies share the same device state, exactly like the reference's shallow copies of raw
+// device pointers (Drake copies the state by value into an AbstractValue, deformable_model.cc:428),
+// but the device memory is released when the last copy goes away or at an explicit Destroy().
+// Header-only, plain C++17 (no CUDA headers): link with -lgmpm_b200.
+#pragma once
+
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <tuple>
+#include <utility>
+#include <vector>
+
+#include "gmpm_c.h"
+#include "multibody/gpu_mpm/settings.h"
+
+namespace drake {
+namespace multibody {
+namespace gmpm {
+
+// cuda_mpm_model.cuh:20-35
+template <typename T>
+struct ExternalSpatialForce {
+  std::vector<Vec3<T>> p_BoBq_B, F_Bq_W_tau, F_Bq_W_f;
+  size_t size() const { return p_BoBq_B.size(); }
+  void resize(size_t n) {
+    p_BoBq_B.resize(n);
+    F_Bq_W_tau.resize(n);
+    F_Bq_W_f.resize(n);
+  }
+};
+
+namespace internal {
+inline void Check(int status, const char* what) {
+  if (status != GMPM_OK) throw std::runtime_error(std::string(what) + ": " + gmpm_last_error());
+}
+// Scalar -> entry points of the C ABI.
+template <typename T> struct Abi;
+#define GMPM_B200_ABI(SUF, T)                                                                        \
+  template <> struct Abi<T> {                                                                        \
+    using State = gmpm_state_##SUF;                                                                  \
+    static constexpr auto create = gmpm_create_##SUF;                                                \
+    static constexpr auto destroy = gmpm_destroy_##SUF;                                              \
+    static constexpr auto add_qr_cloth = gmpm_add_qr_cloth_##SUF;                                    \
+    static constexpr auto finalize = gmpm_finalize_##SUF;                                            \
+    static constexpr auto rebuild_mapping = gmpm_rebuild_mapping_##SUF;                              \
+    static constexpr auto calc_fem = gmpm_calc_fem_##SUF;                                            \
+    static constexpr auto p2g = gmpm_p2g_##SUF;                                                      \
+    static constexpr auto update_grid = gmpm_update_grid_##SUF;                                      \
+    static constexpr auto g2p = gmpm_g2p_##SUF;                                                      \
+    static constexpr auto sync = gmpm_sync_##SUF;                                                    \
+    static constexpr auto sync_particle_state_to_cpu = gmpm_sync_particle_state_to_cpu_##SUF;        \
+    static constexpr auto copy_contact_pairs = gmpm_copy_contact_pairs_##SUF;                        \
+    static constexpr auto update_contact = gmpm_update_contact_##SUF;                                \
+    static constexpr auto reallocate_external_bodies = gmpm_reallocate_external_bodies_##SUF;        \
+    static constexpr auto external_body_force_to_host = gmpm_external_body_force_to_host_##SUF;      \
+    static constexpr auto dump_cpu_state = gmpm_dump_cpu_state_##SUF;                                \
+    static constexpr auto n_verts = gmpm_n_verts_##SUF;                                              \
+    static constexpr auto n_faces = gmpm_n_faces_##SUF;                                              \
+    static constexpr auto n_particles = gmpm_n_particles_##SUF;                                      \
+    static constexpr auto num_contacts = gmpm_num_contacts_##SUF;                                    \
+    static constexpr auto grid_touched_cnt_host = gmpm_grid_touched_cnt_host_##SUF;                  \
+    static constexpr auto read = gmpm_read_##SUF;                                                    \
+    static constexpr auto run_substeps = gmpm_run_substeps_##SUF;                                    \
+  };
+GMPM_B200_ABI(f32, float)
+GMPM_B200_ABI(f64, double)
+#undef GMPM_B200_ABI
+}  // namespace internal
+
+template <typename T>
+struct GpuMpmState {
+  using Abi = internal::Abi<T>;
+
+  GpuMpmState() = default;
+  // Non-default runtime parameters (grid resolution, material, device); must precede AddQRCloth.
+  explicit GpuMpmState(const gmpm_params& params) { Create(&params); }
+
+  size_t n_verts() const { return h_ ? Abi::n_verts(h_.get()) : 0; }
+  size_t n_faces() const { return h_ ? Abi::n_faces(h_.get()) : 0; }
+  size_t n_particles() const { return h_ ? Abi::n_particles(h_.get()) : 0; }
+  size_t num_contacts() const { return h_ ? Abi::num_contacts(h_.get()) : 0; }
+  size_t num_external_bodies() const { return num_external_bodies_; }
+  uint32_t grid_touched_cnt_host() const {
+    uint32_t c = 0;
+    internal::Check(Abi::grid_touched_cnt_host(raw(), &c), "grid_touched_cnt_host");
+    return c;
+  }
+
+  // host mirrors (cuda_mpm_model.cuh:117-118, 141-143)
+  std::vector<Vec3<T>>& positions_host() { return host_->positions; }
+  const std::vector<Vec3<T>>& positions_host() const { return host_->positions; }
+  ExternalSpatialForce<T>& external_forces_host() { return host_->external_forces; }
+  const ExternalSpatialForce<T>& external_forces_host() const { return host_->external_forces; }
+
+  // cuda_mpm_model.cu:16-33
+  void AddQRCloth(const std::vector<Vec3<T>>& pos, const std::vector<Vec3<T>>& vel, const std::vector<int>& indices) {
+    if (!h_) Create(nullptr);
+    if (pos.size() != vel.size() || indices.size() % 3) throw std::invalid_argument("AddQRCloth: inconsistent sizes");
+    internal::Check(Abi::add_qr_cloth(raw(), reinterpret_cast<const T*>(pos.data()),
+                                      reinterpret_cast<const T*>(vel.data()), pos.size(), indices.data(),
+                                      indices.size() / 3),
+                    "AddQRCloth");
+  }
+  // cuda_mpm_model.cu:36-122: every device allocation happens here.
+  void Finalize() {
+    if (!h_) Create(nullptr);
+    internal::Check(Abi::finalize(raw()), "Finalize");
+  }
+  // cuda_mpm_model.cu:125-242.  Drops this handle's reference; the device memory is freed with the last copy.
+  void Destroy() {
+    if (h_) {
+      h_.reset();
+      host_ = std::make_shared<Host>();
+    }
+  }
+
+  // cuda_mpm_model.cu:245-265: (vertex positions, triangle indices) for visualisation.
+  using DumpT = std::tuple<std::vector<Vec3<T>>, std::vector<int>>;
+  DumpT DumpCpuState() const {
+    std::vector<Vec3<T>> pos(n_verts());
+    std::vector<int> tri(3 * n_faces());
+    internal::Check(Abi::dump_cpu_state(raw(), reinterpret_cast<T*>(pos.data()), tri.data()), "DumpCpuState");
+    return std::make_tuple(std::move(pos), std::move(tri));
+  }
+
+  // cuda_mpm_model.cu:320-345
+  void ReallocateExternelBodies(size_t n) {
+    internal::Check(Abi::reallocate_external_bodies(raw(), n), "ReallocateExternelBodies");
+    num_external_bodies_ = n;
+  }
+  void ExternelBodyForceToHost() {
+    auto& ext = host_->external_forces;
+    if (ext.size() != num_external_bodies_) ext.resize(num_external_bodies_);
+    internal::Check(Abi::external_body_force_to_host(raw(), reinterpret_cast<T*>(ext.F_Bq_W_tau.data()),
+                                                     reinterpret_cast<T*>(ext.F_Bq_W_f.data())),
+                    "ExternelBodyForceToHost");
+  }
+
+  // Replacement of the raw device-pointer accessors (cuda_mpm_model.cuh:43-143): a host copy of the
+  // named buffer in the reference's layout and particle order (names: gmpm_c.h, gmpm_read_*).
+  template <typename U>
+  std::vector<U> Read(const char* name, size_t count) const {
+    std::vector<U> out(count);
+    size_t written = 0;
+    internal::Check(Abi::read(raw(), name, out.data(), count * sizeof(U), &written), name);
+    out.resize(written / sizeof(U));
+    return out;
+  }
+
+  int total_contact_iteration_count = 0;  // cuda_mpm_model.cuh:175
+
+  typename Abi::State* raw() const {
+    if (!h_) throw std::runtime_error("GpuMpmState: no device state (call AddQRCloth / Finalize first)");
+    return h_.get();
+  }
+
+ private:
+  struct Host {
+    std::vector<Vec3<T>> positions;
+    ExternalSpatialForce<T> external_forces;
+  };
+  void Create(const gmpm_params* p) {
+    typename Abi::State* s = nullptr;
+    internal::Check(Abi::create(p, &s), "GpuMpmState");
+    h_ = std::shared_ptr<typename Abi::State>(s, [](typename Abi::State* q) { Abi::destroy(q); });
+  }
+  std::shared_ptr<typename Abi::State> h_;
+  std::shared_ptr<Host> host_ = std::make_shared<Host>();
+  size_t num_external_bodies_ = 0;
+};
+
+}  // namespace gmpm
+}  // namespace multibody
+}  // namespace drake

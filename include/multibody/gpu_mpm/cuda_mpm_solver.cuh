@@ -1,0 +1,96 @@
+// Drop-in replacement header for the reference's multibody/gpu_mpm/cuda_mpm_solver.cuh:19-35:
+// the stateless launch front end, same method names / argument meaning / const-ness, forwarding to
+// libgmpm_b200.so through the C ABI (gmpm_c.h).  Errors surface as std::runtime_error (the
+// reference's CUDA_SAFE_CALL throws the same type when DEBUG=1, settings.h:11-25).
+#pragma once
+
+#include <fstream>
+#include <string>
+
+#include "multibody/gpu_mpm/cpu_mpm_model.h"
+#include "multibody/gpu_mpm/cuda_mpm_model.cuh"
+#include "multibody/gpu_mpm/settings.h"
+
+namespace drake {
+namespace multibody {
+namespace gmpm {
+
+template <typename T>
+class GpuMpmSolver {
+  using Abi = internal::Abi<T>;
+
+ public:
+  void RebuildMapping(GpuMpmState<T>* state, bool sort) const {
+    internal::Check(Abi::rebuild_mapping(state->raw(), sort ? 1 : 0), "RebuildMapping");
+  }
+  void CalcFemStateAndForce(GpuMpmState<T>* state, const T& dt) const {
+    internal::Check(Abi::calc_fem(state->raw(), dt), "CalcFemStateAndForce");
+  }
+  void ParticleToGrid(GpuMpmState<T>* state, const T& dt) const {
+    internal::Check(Abi::p2g(state->raw(), dt), "ParticleToGrid");
+  }
+  void UpdateGrid(GpuMpmState<T>* state, int mpm_bc = -1) const {
+    internal::Check(Abi::update_grid(state->raw(), mpm_bc), "UpdateGrid");
+  }
+  void GridToParticle(GpuMpmState<T>* state, const T& dt) const {
+    internal::Check(Abi::g2p(state->raw(), dt), "GridToParticle");
+  }
+  // cuda_mpm_solver.cu:164-166: device-wide barrier.  Work is issued on per-state streams, so the
+  // one-argument form (this state's stream only) is the cheaper barrier.
+  void GpuSync() const { internal::Check(gmpm_device_sync(), "GpuSync"); }
+  void GpuSync(GpuMpmState<T>* state) const { internal::Check(Abi::sync(state->raw()), "GpuSync"); }
+
+  // cuda_mpm_solver.cu:187-191: positions_host() <- current particle positions.
+  void SyncParticleStateToCpu(GpuMpmState<T>* state) const {
+    auto& host = state->positions_host();
+    host.resize(state->n_particles());
+    internal::Check(Abi::sync_particle_state_to_cpu(state->raw(), reinterpret_cast<T*>(host.data())),
+                    "SyncParticleStateToCpu");
+  }
+
+  // cuda_mpm_solver.cu:169-183: Wavefront OBJ of the cloth.
+  void Dump(const GpuMpmState<T>& state, std::string filename) const {
+    const auto [pos, tri] = state.DumpCpuState();
+    std::ofstream obj(filename);
+    for (const auto& p : pos) obj << "v " << p[0] << " " << p[1] << " " << p[2] << "\n";
+    for (size_t f = 0; f + 2 < tri.size(); f += 3)
+      obj << "f " << tri[f] + 1 << " " << tri[f + 1] + 1 << " " << tri[f + 2] + 1 << "\n";
+  }
+
+  // cuda_mpm_solver.cu:194-212
+  void CopyContactPairs(GpuMpmState<T>* state, const MpmParticleContactPairs<T>& pairs) const {
+    auto flat = [](const std::vector<Vec3<T>>& v) { return reinterpret_cast<const T*>(v.data()); };
+    internal::Check(Abi::copy_contact_pairs(state->raw(), pairs.size(), pairs.particle_in_contact_index.data(),
+                                            pairs.non_mpm_id.data(), pairs.penetration_distance.data(),
+                                            flat(pairs.normal), flat(pairs.particle_in_contact_position),
+                                            flat(pairs.rigid_v), flat(pairs.rigid_p_WB)),
+                    "CopyContactPairs");
+  }
+
+  // cuda_mpm_solver.cu:215-621.  `dump` (per-iteration JSON to a developer path) is not reproduced.
+  void UpdateContact(GpuMpmState<T>* state, const int frame, const int substep, const T& dt, const T& friction_mu,
+                     const T& stiffness, const T& damping, const bool dump, const bool exact_line_search) const {
+    (void)frame;
+    (void)substep;
+    (void)dump;
+    gmpm_contact_stats stats{};
+    internal::Check(Abi::update_contact(state->raw(), dt, friction_mu, stiffness, damping, exact_line_search ? 1 : 0,
+                                        0, &stats),
+                    "UpdateContact");
+    state->total_contact_iteration_count += stats.iterations;
+    last_contact_stats_ = stats;
+  }
+  const gmpm_contact_stats& last_contact_stats() const { return last_contact_stats_; }
+
+  // Extension: n no-contact substeps in one call (cuda_mpm_test.cc:66-72 loop body).
+  void RunSubsteps(GpuMpmState<T>* state, int n, const T& dt, int mpm_bc = -1, int sort_every = 0) const {
+    internal::Check(Abi::run_substeps(state->raw(), n, dt, mpm_bc, sort_every), "RunSubsteps");
+  }
+
+ private:
+  mutable gmpm_contact_stats last_contact_stats_{};
+};
+
+}  // namespace gmpm
+}  // namespace multibody
+}  // namespace drake
