@@ -76,15 +76,31 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
       throw gmpm::CudaError(cudaErrorNoDevice, "no CUDA device available (libgmpm_b200 has no CPU fallback)");
     if (n == 0) return;
-    uint32_t *k[2], *v[2], *scratch;
+    uint32_t *k[2], *v[2], *kin, *vin, *scratch;
     for (int i = 0; i < 2; ++i) {
       GMPM_CUDA(cudaMalloc(&k[i], n * 4));
       GMPM_CUDA(cudaMalloc(&v[i], n * 4));
     }
+    GMPM_CUDA(cudaMalloc(&kin, n * 4));
+    GMPM_CUDA(cudaMalloc(&vin, n * 4));
     GMPM_CUDA(cudaMalloc(&scratch, gmpm::radix_sort_scratch_words(n) * 4));
-    GMPM_CUDA(cudaMemcpy(k[0], keys_in, n * 4, cudaMemcpyHostToDevice));
-    GMPM_CUDA(cudaMemcpy(v[0], ids_in, n * 4, cudaMemcpyHostToDevice));
-    const int r = gmpm::radix_sort_pairs(k, v, (uint32_t)n, num_bit, false, scratch, 0, [](const char*) {});
+    GMPM_CUDA(cudaMemcpy(kin, keys_in, n * 4, cudaMemcpyHostToDevice));
+    GMPM_CUDA(cudaMemcpy(vin, ids_in, n * 4, cudaMemcpyHostToDevice));
+    int r = 0;
+    if (num_bit == 0) {
+      GMPM_CUDA(cudaMemcpy(k[0], kin, n * 4, cudaMemcpyDeviceToDevice));
+      GMPM_CUDA(cudaMemcpy(v[0], vin, n * 4, cudaMemcpyDeviceToDevice));
+    } else {
+      int dev = 0, sms = 0;
+      GMPM_CUDA(cudaGetDevice(&dev));
+      GMPM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+      gmpm::SortArgs a = gmpm::make_sort_args(kin, vin, k, v, (uint32_t)n, num_bit, scratch);
+      const int ctas = gmpm::sort_grid_ctas(gmpm::radix_sort_kernel, sms, a.n_tiles);
+      void* kargs[] = {&a};
+      GMPM_CUDA(cudaLaunchCooperativeKernel((void*)gmpm::radix_sort_kernel, dim3(ctas), dim3(gmpm::kSortThreads), kargs,
+                                            gmpm::kSortSmemBytes, 0));
+      r = (a.n_passes - 1) & 1;
+    }
     GMPM_CUDA(cudaDeviceSynchronize());
     GMPM_CUDA(cudaMemcpy(keys_out, k[r], n * 4, cudaMemcpyDeviceToHost));
     GMPM_CUDA(cudaMemcpy(ids_out, v[r], n * 4, cudaMemcpyDeviceToHost));
@@ -92,6 +108,8 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
       cudaFree(k[i]);
       cudaFree(v[i]);
     }
+    cudaFree(kin);
+    cudaFree(vin);
     cudaFree(scratch);
   });
 }

@@ -14,6 +14,7 @@
 #pragma once
 #include "common.cuh"
 #include "math.cuh"
+#include "sort.cuh"
 
 namespace gmpm {
 
@@ -46,12 +47,7 @@ __global__ void p2g_prologue_kernel(DevCounters* ctr) {
   ctr->work_p2g = 0;
   ctr->work_g2p = 0;
 }
-__global__ void bin_reset_kernel(DevCounters* ctr) {
-  ctr->n_pblocks = 0;
-  ctr->n_big = 0;
-  ctr->n_small = 0;
-  ctr->n_tiles = 0;
-}
+
 
 // ------------------------------------------------------------------------------------------------
 // Setup: rest shape, F = Q, volumes (replaces initialize_fem_state_kernel, :13-70).
@@ -134,60 +130,73 @@ __global__ void permute_visible_kernel(uint32_t N, const uint32_t* __restrict__ 
 }
 
 // ------------------------------------------------------------------------------------------------
-// Binning: per-particle-block ranges of the key-sorted order + compact list of particle blocks.
+// Binning
 // ------------------------------------------------------------------------------------------------
-__global__ void build_pblocks_kernel(uint32_t N, const uint32_t* __restrict__ sorted_key, uint32_t epoch,
-                                     uint32_t* __restrict__ pb_start, uint32_t* __restrict__ pb_end,
-                                     uint32_t* __restrict__ pb_epoch, uint32_t* __restrict__ pb_list,
-                                     DevCounters* ctr) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool in = i < N;
-  uint32_t b = 0;
-  bool head = false;
-  if (in) {
-    b = sorted_key[i] >> 6;
-    head = (i == 0) || ((sorted_key[i - 1] >> 6) != b);
-    const bool tail = (i + 1 == N) || ((sorted_key[i + 1] >> 6) != b);
-    if (head) pb_start[b] = i;
-    if (tail) pb_end[b] = i + 1;
+// The whole particle binning in one cooperative launch: stable radix sort of (cell key, slot) on all
+// key bits, then the per-block ranges / block list (build_pblocks) and the chunked work records
+// (classify_pblocks), with grid barriers in between.  `sorted` = index of the result buffer pair.
+struct BinArgs {
+  SortArgs sort;
+  uint32_t N, epoch, work_cap;
+  uint32_t *pb_start, *pb_end, *pb_epoch, *pb_list;
+  uint2* pb_tile;
+  WorkRec* pb_work;
+  DevCounters* ctr;
+};
+
+__global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs a) {
+  extern __shared__ __align__(16) uint32_t sort_smem[];
+  cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    a.ctr->n_pblocks = 0;
+    a.ctr->n_big = 0;
+    a.ctr->n_small = 0;
+    a.ctr->n_tiles = 0;
   }
-  // warp-aggregated append of the heads
-  const uint32_t m = __ballot_sync(kFullMask, head);
-  if (m) {
-    const int lane = threadIdx.x & 31;
-    uint32_t base = 0;
-    if (lane == (__ffs(m) - 1)) base = atomicAdd(&ctr->n_pblocks, (uint32_t)__popc(m));
-    base = __shfl_sync(kFullMask, base, __ffs(m) - 1);
-    if (head) {
-      const uint32_t t = base + __popc(m & ((1u << lane) - 1u));
-      pb_list[t] = b;
-      pb_epoch[b] = epoch;
+  const int r = radix_sort_device(a.sort, sort_smem, grid);  // ends with a grid barrier
+  const uint32_t* sorted_key = a.sort.keys[r];
+  const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+  // ---- block ranges + list of particle blocks (uniform trip count: the warp-aggregated append needs all lanes)
+  for (uint32_t i0 = 0; i0 < a.N; i0 += nth) {
+    const uint32_t i = i0 + tid;
+    uint32_t b = 0;
+    bool head = false;
+    if (i < a.N) {
+      b = sorted_key[i] >> 6;
+      head = (i == 0) || ((sorted_key[i - 1] >> 6) != b);
+      const bool tail = (i + 1 == a.N) || ((sorted_key[i + 1] >> 6) != b);
+      if (head) a.pb_start[b] = i;
+      if (tail) a.pb_end[b] = i + 1;
+    }
+    const uint32_t m = __ballot_sync(kFullMask, head);
+    if (m) {
+      const int lane = threadIdx.x & 31;
+      uint32_t base = 0;
+      if (lane == (__ffs(m) - 1)) base = atomicAdd(&a.ctr->n_pblocks, (uint32_t)__popc(m));
+      base = __shfl_sync(kFullMask, base, __ffs(m) - 1);
+      if (head) {
+        a.pb_list[base + __popc(m & ((1u << lane) - 1u))] = b;
+        a.pb_epoch[b] = a.epoch;
+      }
     }
   }
-}
-
-// Work records: every particle block is cut into chunks of <= kChunk particles (bounded units keep the
-// persistent P2G / G2P kernels balanced whatever the block populations are), each with its own P2G
-// tile; the tiles of one block are consecutive (pb_tile[block] = {first, count}).  Full chunks are
-// appended at the front of pb_work, partial ones at the back (growing down); the kernels walk the
-// front, then the back (longest-processing-time-first keeps the tail short).
-__global__ void classify_pblocks_kernel(uint32_t cap, const uint32_t* __restrict__ pb_list,
-                                        const uint32_t* __restrict__ pb_start, const uint32_t* __restrict__ pb_end,
-                                        uint2* __restrict__ pb_tile, WorkRec* __restrict__ pb_work, DevCounters* ctr) {
-  const uint32_t n_pb = ctr->n_pblocks;
-  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_pb; t += gridDim.x * blockDim.x) {
-    const uint32_t blk = pb_list[t];
-    const uint32_t b = pb_start[blk], e = pb_end[blk];
+  grid.sync();
+  // ---- chunked work records
+  const uint32_t n_pb = a.ctr->n_pblocks;
+  for (uint32_t t = tid; t < n_pb; t += nth) {
+    const uint32_t blk = a.pb_list[t];
+    const uint32_t b = a.pb_start[blk], e = a.pb_end[blk];
     const uint32_t n_full = (e - b) / kChunk, rest = (e - b) % kChunk;
     const uint32_t n_chunks = n_full + (rest ? 1u : 0u);
-    const uint32_t tile0 = atomicAdd(&ctr->n_tiles, n_chunks);
-    pb_tile[blk] = make_uint2(tile0, n_chunks);
+    const uint32_t tile0 = atomicAdd(&a.ctr->n_tiles, n_chunks);
+    a.pb_tile[blk] = make_uint2(tile0, n_chunks);
     if (n_full) {
-      const uint32_t w0 = atomicAdd(&ctr->n_big, n_full);
+      const uint32_t w0 = atomicAdd(&a.ctr->n_big, n_full);
       for (uint32_t c = 0; c < n_full; ++c)
-        pb_work[w0 + c] = WorkRec{tile0 + c, b + c * kChunk, b + (c + 1) * kChunk, blk};
+        a.pb_work[w0 + c] = WorkRec{tile0 + c, b + c * kChunk, b + (c + 1) * kChunk, blk};
     }
-    if (rest) pb_work[cap - 1u - atomicAdd(&ctr->n_small, 1u)] = WorkRec{tile0 + n_full, b + n_full * kChunk, e, blk};
+    if (rest)
+      a.pb_work[a.work_cap - 1u - atomicAdd(&a.ctr->n_small, 1u)] = WorkRec{tile0 + n_full, b + n_full * kChunk, e, blk};
   }
 }
 

@@ -1,25 +1,34 @@
-// sort.cuh -- stable LSD radix sort of (key, value) uint32 pairs on key bits [0, num_bit).
+// sort.cuh -- stable LSD radix sort of (key, value) uint32 pairs on key bits [0, num_bit), and the
+// particle binning built on it, as ONE cooperative persistent kernel.
 //
 // Replaces the reference's radix_sort (radix_sort.cuh:202-286: 2-bit digits, Hillis-Steele block
-// scans, recursive Blelloch scan, ~5 global sweeps per digit, i.e. 8 digit passes for 16 bits).
-// Here: 8-bit digits, so 16 key bits = 2 passes and a full 21-bit cell key = 3 passes; each pass is
-//   (1) radix_hist   : per-tile digit histogram  -> hist[digit][tile], digit totals
-//   (2) radix_scan   : one CTA per digit: exclusive scan over tiles + digit base
-//   (3) radix_scatter: stable ranking inside the tile with warp match-any, scatter to global
-// Stability (ties keep input order) is what makes the result bit-identical to the reference's
-// permutation.  Traffic per pass: 4 B (hist) + 8 B read + 8 B write per element.
+// scans, recursive Blelloch scan: 8 digit passes x ~5 global sweeps x 3+ launches for its 16 key bits).
+// Here the digits are up to 11 bits wide, so the reference's 16 visible key bits are 2 passes and a
+// full 21-bit cell key is 2 passes (27 bits at 512^3: 3), and all passes run inside one launch with
+// grid-wide barriers between their phases:
+//   hist    : per-tile digit histogram (warp-aggregated shared-memory counting) -> hist[tile][digit]
+//   scan    : one warp per digit: exclusive scan over the tiles, digit totals
+//   scatter : stable ranking inside the tile with warp match-any, scatter to the other buffer
+// and, when the sort is the particle binning, two more phases (block ranges + work records, see
+// kernels.cuh).  Stability (ties keep input order) is what makes the result bit-identical to the
+// reference's permutation and the summation order of P2G reproducible.
+// Traffic per pass: 4 B (hist) + 8 B read + 8 B write per element; at the 1M-particle scene everything
+// is L2 resident and the cost is the 3 barriers per pass.
 #pragma once
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace gmpm {
 
-constexpr int kRadixBits = 8;
-constexpr int kRadix = 1 << kRadixBits;
+constexpr int kMaxRadixBits = 11;
+constexpr int kMaxRadix = 1 << kMaxRadixBits;
 constexpr int kSortThreads = 256;
 constexpr int kSortWarps = kSortThreads / 32;
 constexpr int kSortItemsPerLane = 16;                                  // per pass-through of a warp
 constexpr int kSortWarpChunk = 32 * kSortItemsPerLane;                 // 512 consecutive items / warp
 constexpr int kSortTile = kSortWarps * kSortWarpChunk;                 // 4096 items / CTA
+constexpr size_t kSortSmemBytes = sizeof(uint32_t) * (size_t)(kSortWarps + 1) * kMaxRadix + 64;
 
 __device__ __forceinline__ uint32_t lanemask_lt() {
   uint32_t m;
@@ -27,170 +36,248 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
   return m;
 }
 
-// hist[d * n_tiles + tile] = number of keys of the tile with digit d; totals[d] += same.
-__global__ void __launch_bounds__(kSortThreads)
-radix_hist_kernel(const uint32_t* __restrict__ keys, uint32_t n, int shift, uint32_t digit_mask,
-                  uint32_t n_tiles, uint32_t* __restrict__ hist, uint32_t* __restrict__ totals) {
-  __shared__ uint32_t sh[kRadix];
-  const uint32_t tile = blockIdx.x;
-  sh[threadIdx.x] = 0;
-  __syncthreads();
-  const uint32_t begin = tile * kSortTile;
-  const uint32_t end = min(begin + (uint32_t)kSortTile, n);
-  for (uint32_t i = begin + threadIdx.x; i < end; i += kSortThreads) {
-    const uint32_t d = (keys[i] >> shift) & digit_mask;
-    atomicAdd(&sh[d], 1u);
-  }
-  __syncthreads();
-  const uint32_t c = sh[threadIdx.x];
-  hist[threadIdx.x * n_tiles + tile] = c;
-  if (c) atomicAdd(&totals[threadIdx.x], c);
-}
+struct SortPass {
+  int shift, bits;
+};
 
-// One CTA per digit d: offsets[d][tile] = (sum of totals of digits < d) + exclusive scan over tiles.
-__global__ void __launch_bounds__(kSortThreads)
-radix_scan_kernel(uint32_t* __restrict__ hist, const uint32_t* __restrict__ totals, uint32_t n_tiles) {
-  __shared__ uint32_t sh[kSortThreads];
-  __shared__ uint32_t s_base;
-  const uint32_t d = blockIdx.x;
-  // digit base
-  sh[threadIdx.x] = threadIdx.x < d ? totals[threadIdx.x] : 0u;
-  __syncthreads();
-  for (int off = kSortThreads / 2; off > 0; off >>= 1) {
-    if (threadIdx.x < off) sh[threadIdx.x] += sh[threadIdx.x + off];
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) s_base = sh[0];
-  __syncthreads();
-  const uint32_t base = s_base;
-  // chunked exclusive scan of the row
-  uint32_t* row = hist + (size_t)d * n_tiles;
-  const uint32_t per = (n_tiles + kSortThreads - 1) / kSortThreads;
-  const uint32_t b = min(threadIdx.x * per, n_tiles), e = min(b + per, n_tiles);
-  uint32_t sum = 0;
-  for (uint32_t i = b; i < e; ++i) sum += row[i];
-  __syncthreads();
-  sh[threadIdx.x] = sum;
-  __syncthreads();
-  // Hillis-Steele inclusive scan over 256 partials
-  for (int off = 1; off < kSortThreads; off <<= 1) {
-    uint32_t v = threadIdx.x >= off ? sh[threadIdx.x - off] : 0u;
-    __syncthreads();
-    sh[threadIdx.x] += v;
-    __syncthreads();
-  }
-  uint32_t run = base + sh[threadIdx.x] - sum;
-  for (uint32_t i = b; i < e; ++i) {
-    const uint32_t c = row[i];
-    row[i] = run;
-    run += c;
-  }
-}
+struct SortArgs {
+  const uint32_t* keys_in;   // input keys (pass 0 reads them; never written)
+  const uint32_t* vals_in;   // input values, or nullptr: values of pass 0 are 0..n-1
+  uint32_t* keys[2];         // ping-pong buffers: pass p writes keys[p & 1]
+  uint32_t* vals[2];
+  uint32_t n, n_tiles;
+  int n_passes;
+  SortPass pass[4];
+  uint32_t* hist;            // [radix][n_tiles] scratch (digit-major: the scan reads contiguous rows)
+  uint32_t* totals;          // [radix] scratch
+};
 
-// Stable scatter.  Warp w of the CTA owns the 512 consecutive items [w*512, (w+1)*512) of the tile,
-// walked as 16 rounds of 32 lanes, so input order = (warp, round, lane).
-template <bool IOTA_VALUES>
-__global__ void __launch_bounds__(kSortThreads)
-radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n,
-                     int shift, uint32_t digit_mask, uint32_t n_tiles,
-                     const uint32_t* __restrict__ offsets) {
-  __shared__ uint32_t wh[kSortWarps][kRadix];
-  const uint32_t tile = blockIdx.x;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-#pragma unroll
-  for (int w = 0; w < kSortWarps; ++w) wh[w][threadIdx.x] = 0;
-  __syncthreads();
-  const uint32_t wbase = tile * kSortTile + warp * kSortWarpChunk;
-  uint32_t key[kSortItemsPerLane];
-  // phase 1: per-warp digit histogram
-#pragma unroll
-  for (int r = 0; r < kSortItemsPerLane; ++r) {
-    const uint32_t i = wbase + r * 32 + lane;
-    const bool valid = i < n;
-    key[r] = valid ? keys_in[i] : 0u;
-    const uint32_t d = valid ? ((key[r] >> shift) & digit_mask) : (uint32_t)(kRadix + lane);
-    const uint32_t peers = __match_any_sync(kFullMask, d);
-    if (valid && (peers & lanemask_lt()) == 0) wh[warp][d] += __popc(peers);
-    __syncwarp();
-  }
-  __syncthreads();
-  // phase 2: thread d turns the per-warp counts of digit d into global start offsets
-  {
-    const uint32_t d = threadIdx.x;
-    uint32_t run = offsets[d * n_tiles + tile];
-#pragma unroll
-    for (int w = 0; w < kSortWarps; ++w) {
-      const uint32_t c = wh[w][d];
-      wh[w][d] = run;
-      run += c;
-    }
-  }
-  __syncthreads();
-  // phase 3: same walk, rank inside the peer group, scatter
-#pragma unroll
-  for (int r = 0; r < kSortItemsPerLane; ++r) {
-    const uint32_t i = wbase + r * 32 + lane;
-    const bool valid = i < n;
-    const uint32_t d = valid ? ((key[r] >> shift) & digit_mask) : (uint32_t)(kRadix + lane);
-    const uint32_t peers = __match_any_sync(kFullMask, d);
-    const uint32_t rank = __popc(peers & lanemask_lt());
-    uint32_t dst = 0;
-    if (valid) dst = wh[warp][d] + rank;
-    __syncwarp();
-    if (valid && rank == 0) wh[warp][d] += __popc(peers);
-    __syncwarp();
-    if (valid) {
-      keys_out[dst] = key[r];
-      vals_out[dst] = IOTA_VALUES ? i : vals_in[i];
-    }
-  }
-}
-
-// Scratch needed by radix_sort_pairs for n elements (uint32 words).
 inline size_t radix_sort_scratch_words(size_t n) {
   const size_t n_tiles = (n + kSortTile - 1) / kSortTile;
-  return (size_t)kRadix * (n_tiles ? n_tiles : 1) + 4 * kRadix;
+  return (size_t)kMaxRadix * (n_tiles ? n_tiles : 1) + kMaxRadix;
 }
 
-struct LaunchCounter;  // fwd (gmpm.cu)
+// Splits num_bit key bits into the fewest passes of <= kMaxRadixBits, evenly.
+inline int plan_sort_passes(int num_bit, SortPass* pass) {
+  if (num_bit <= 0) return 0;
+  const int n = (num_bit + kMaxRadixBits - 1) / kMaxRadixBits;
+  int shift = 0;
+  for (int p = 0; p < n; ++p) {
+    const int bits = (num_bit - shift + (n - p) - 1) / (n - p);
+    pass[p] = SortPass{shift, bits};
+    shift += bits;
+  }
+  return n;
+}
 
-// Sorts (keys[0], vals[0]) using (keys[1], vals[1]) as the ping-pong partner.  Returns the index
-// (0 or 1) of the buffer pair holding the result.  If iota_first, the values of the first pass are
-// generated (0..n-1) instead of read.  `on_launch(name)` is called once per kernel launch.
-template <typename F>
-inline int radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], uint32_t n, int num_bit, bool iota_first,
-                            uint32_t* scratch, cudaStream_t stream, F&& on_launch) {
-  if (n == 0 || num_bit <= 0) {
-    return 0;
+// One full sort; every thread of the cooperative grid calls it.  `smem` = kSortSmemBytes.
+// Returns the index (0 or 1) of the buffer pair that holds the result.
+__device__ __forceinline__ int radix_sort_device(const SortArgs& a, uint32_t* smem,
+                                                 cooperative_groups::grid_group& grid) {
+  uint32_t* wh = smem;                                   // [kSortWarps][radix]
+  uint32_t* sbase = smem + (size_t)kSortWarps * kMaxRadix;  // [radix] digit bases
+  __shared__ uint32_t s_part[kSortWarps];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t* src_k = a.keys_in;
+  const uint32_t* src_v = a.vals_in;
+  for (int p = 0; p < a.n_passes; ++p) {
+    const int shift = a.pass[p].shift;
+    const uint32_t radix = 1u << a.pass[p].bits, mask = radix - 1u;
+    uint32_t* dst_k = a.keys[p & 1];
+    uint32_t* dst_v = a.vals[p & 1];
+    // ---- hist: hist[tile][d] = number of keys of the tile with digit d
+    for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+      for (uint32_t d = threadIdx.x; d < radix; d += kSortThreads) wh[d] = 0;
+      __syncthreads();
+      const uint32_t wbase = tile * kSortTile + warp * kSortWarpChunk;
+      uint32_t hk[kSortItemsPerLane];
+#pragma unroll
+      for (int r = 0; r < kSortItemsPerLane; ++r) {  // all loads first: one memory round trip
+        const uint32_t i = wbase + r * 32 + lane;
+        hk[r] = i < a.n ? __ldcg(src_k + i) : 0u;
+      }
+#pragma unroll
+      for (int r = 0; r < kSortItemsPerLane; ++r) {
+        const uint32_t i = wbase + r * 32 + lane;
+        const bool valid = i < a.n;
+        const uint32_t d = valid ? ((hk[r] >> shift) & mask) : (radix + (uint32_t)lane);
+        const uint32_t peers = __match_any_sync(kFullMask, d);
+        if (valid && (peers & lanemask_lt()) == 0) atomicAdd(&wh[d], (uint32_t)__popc(peers));
+      }
+      __syncthreads();
+      for (uint32_t d = threadIdx.x; d < radix; d += kSortThreads) a.hist[(size_t)d * a.n_tiles + tile] = wh[d];
+      __syncthreads();
+    }
+    grid.sync();
+    // ---- scan: one warp per digit, exclusive over the tiles (in place, rows are contiguous);
+    // totals[d] = digit count.  The row is read 8 x 32 tiles at a time before any of it is rewritten.
+    {
+      const uint32_t gw = (blockIdx.x * kSortThreads + threadIdx.x) >> 5, n_gw = (gridDim.x * kSortThreads) >> 5;
+      for (uint32_t d = gw; d < radix; d += n_gw) {
+        uint32_t* row = a.hist + (size_t)d * a.n_tiles;
+        uint32_t run = 0;
+        for (uint32_t t0 = 0; t0 < a.n_tiles; t0 += 256) {
+          uint32_t c[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const uint32_t t = t0 + u * 32 + lane;
+            c[u] = t < a.n_tiles ? __ldcg(row + t) : 0u;
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const uint32_t t = t0 + u * 32 + lane;
+            uint32_t inc = c[u];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+              const uint32_t v = __shfl_up_sync(kFullMask, inc, o);
+              if (lane >= o) inc += v;
+            }
+            if (t < a.n_tiles) row[t] = run + inc - c[u];
+            run += __shfl_sync(kFullMask, inc, 31);
+          }
+        }
+        if (lane == 0) a.totals[d] = run;
+      }
+    }
+    grid.sync();
+    // ---- scatter
+    if (blockIdx.x < a.n_tiles) {
+      // digit bases: exclusive scan of totals[] (every CTA computes its own copy)
+      const uint32_t per = radix / kSortThreads ? radix / kSortThreads : 1u;  // digits per thread (radix >= 256) or 1
+      const uint32_t d0 = threadIdx.x * per;
+      uint32_t loc[kMaxRadix / kSortThreads];
+      uint32_t sum = 0;
+#pragma unroll
+      for (uint32_t e = 0; e < kMaxRadix / kSortThreads; ++e) {
+        loc[e] = (e < per && d0 + e < radix) ? a.totals[d0 + e] : 0u;
+        sum += loc[e];
+      }
+      uint32_t inc = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(kFullMask, inc, o);
+        if (lane >= o) inc += v;
+      }
+      if (lane == 31) s_part[warp] = inc;
+      __syncthreads();
+      uint32_t wofs = 0;
+      for (int w = 0; w < warp; ++w) wofs += s_part[w];
+      uint32_t run = wofs + inc - sum;
+#pragma unroll
+      for (uint32_t e = 0; e < kMaxRadix / kSortThreads; ++e) {
+        if (e < per && d0 + e < radix) sbase[d0 + e] = run;
+        run += loc[e];
+      }
+      __syncthreads();
+    }
+    for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+      {
+        uint4* z = reinterpret_cast<uint4*>(wh);  // radix * kSortWarps is a multiple of 4
+        for (uint32_t d = threadIdx.x; d < radix * kSortWarps / 4; d += kSortThreads) z[d] = make_uint4(0u, 0u, 0u, 0u);
+      }
+      __syncthreads();
+      const uint32_t wbase = tile * kSortTile + warp * kSortWarpChunk;
+      uint32_t key[kSortItemsPerLane], val[kSortItemsPerLane];
+      uint32_t* mywh = wh + (size_t)warp * radix;
+#pragma unroll
+      for (int r = 0; r < kSortItemsPerLane; ++r) {  // all loads first: one memory round trip
+        const uint32_t i = wbase + r * 32 + lane;
+        key[r] = i < a.n ? __ldcg(src_k + i) : 0u;
+        val[r] = (src_v && i < a.n) ? __ldcg(src_v + i) : i;
+      }
+      // this tile's digit offsets (one more round trip, overlapped with phase 1)
+      uint32_t tofs[kMaxRadix / kSortThreads];
+#pragma unroll
+      for (uint32_t e = 0; e < kMaxRadix / kSortThreads; ++e) {
+        const uint32_t d = threadIdx.x + e * kSortThreads;
+        tofs[e] = d < radix ? __ldcg(a.hist + (size_t)d * a.n_tiles + tile) : 0u;
+      }
+      // phase 1: per-warp digit histogram (warp w owns the items [w*512, (w+1)*512) of the tile)
+#pragma unroll
+      for (int r = 0; r < kSortItemsPerLane; ++r) {
+        const uint32_t i = wbase + r * 32 + lane;
+        const bool valid = i < a.n;
+        const uint32_t d = valid ? ((key[r] >> shift) & mask) : (radix + (uint32_t)lane);
+        const uint32_t peers = __match_any_sync(kFullMask, d);
+        if (valid && (peers & lanemask_lt()) == 0) mywh[d] += __popc(peers);
+        __syncwarp();
+      }
+      __syncthreads();
+      // phase 2: per-warp counts of digit d -> global start offsets
+#pragma unroll
+      for (uint32_t e = 0; e < kMaxRadix / kSortThreads; ++e) {
+        const uint32_t d = threadIdx.x + e * kSortThreads;
+        if (d >= radix) break;
+        uint32_t run = tofs[e] + sbase[d];
+#pragma unroll
+        for (int w = 0; w < kSortWarps; ++w) {
+          const uint32_t c = wh[(size_t)w * radix + d];
+          wh[(size_t)w * radix + d] = run;
+          run += c;
+        }
+      }
+      __syncthreads();
+      // phase 3: same walk, rank inside the peer group, scatter
+#pragma unroll
+      for (int r = 0; r < kSortItemsPerLane; ++r) {
+        const uint32_t i = wbase + r * 32 + lane;
+        const bool valid = i < a.n;
+        const uint32_t d = valid ? ((key[r] >> shift) & mask) : (radix + (uint32_t)lane);
+        const uint32_t peers = __match_any_sync(kFullMask, d);
+        const uint32_t rank = __popc(peers & lanemask_lt());
+        uint32_t dst = 0;
+        if (valid) dst = mywh[d] + rank;
+        __syncwarp();
+        if (valid && rank == 0) mywh[d] += __popc(peers);
+        __syncwarp();
+        if (valid) {
+          dst_k[dst] = key[r];
+          dst_v[dst] = val[r];
+        }
+      }
+      __syncthreads();
+    }
+    grid.sync();
+    src_k = dst_k;
+    src_v = dst_v;
   }
-  const uint32_t n_tiles = (n + kSortTile - 1) / kSortTile;
-  uint32_t* hist = scratch;
-  uint32_t* totals = scratch + (size_t)kRadix * n_tiles;
-  const int passes = (num_bit + kRadixBits - 1) / kRadixBits;
-  GMPM_CUDA(cudaMemsetAsync(totals, 0, sizeof(uint32_t) * kRadix * 4, stream));
-  int cur = 0;
-  for (int p = 0; p < passes; ++p) {
-    const int shift = p * kRadixBits;
-    const int bits = (num_bit - shift) < kRadixBits ? (num_bit - shift) : kRadixBits;
-    const uint32_t mask = (1u << bits) - 1u;
-    uint32_t* tot = totals + (size_t)(p & 3) * kRadix;
-    if (p >= 4) GMPM_CUDA(cudaMemsetAsync(tot, 0, sizeof(uint32_t) * kRadix, stream));
-    on_launch("radix_hist");
-    radix_hist_kernel<<<n_tiles, kSortThreads, 0, stream>>>(keys[cur], n, shift, mask, n_tiles, hist, tot);
-    on_launch("radix_scan");
-    radix_scan_kernel<<<kRadix, kSortThreads, 0, stream>>>(hist, tot, n_tiles);
-    on_launch("radix_scatter");
-    if (p == 0 && iota_first)
-      radix_scatter_kernel<true><<<n_tiles, kSortThreads, 0, stream>>>(keys[cur], vals[cur], keys[cur ^ 1],
-                                                                       vals[cur ^ 1], n, shift, mask, n_tiles, hist);
-    else
-      radix_scatter_kernel<false><<<n_tiles, kSortThreads, 0, stream>>>(keys[cur], vals[cur], keys[cur ^ 1],
-                                                                        vals[cur ^ 1], n, shift, mask, n_tiles, hist);
-    GMPM_CUDA(cudaGetLastError());
-    cur ^= 1;
-  }
-  return cur;
+  return (a.n_passes - 1) & 1;
+}
+
+__global__ void __launch_bounds__(kSortThreads, 2) radix_sort_kernel(SortArgs a) {
+  extern __shared__ __align__(16) uint32_t sort_smem[];
+  cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  radix_sort_device(a, sort_smem, grid);
+}
+
+// Host helper: fills the pass plan and buffers of a SortArgs.
+inline SortArgs make_sort_args(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* keys[2], uint32_t* vals[2],
+                               uint32_t n, int num_bit, uint32_t* scratch) {
+  SortArgs a{};
+  a.keys_in = keys_in;
+  a.vals_in = vals_in;
+  a.keys[0] = keys[0];
+  a.keys[1] = keys[1];
+  a.vals[0] = vals[0];
+  a.vals[1] = vals[1];
+  a.n = n;
+  a.n_tiles = (n + kSortTile - 1) / kSortTile;
+  a.n_passes = plan_sort_passes(num_bit, a.pass);
+  a.hist = scratch;
+  a.totals = scratch + (size_t)kMaxRadix * (a.n_tiles ? a.n_tiles : 1);
+  return a;
+}
+
+// Cooperative-launch geometry of a kernel that embeds radix_sort_device.
+template <typename Kernel>
+inline int sort_grid_ctas(Kernel kernel, int sm_count, uint32_t n_tiles) {
+  int occ = 0;
+  GMPM_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSortSmemBytes));
+  GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kSortThreads, kSortSmemBytes));
+  if (occ < 1) throw CudaError(cudaErrorLaunchOutOfResources, "radix sort kernel does not fit on an SM");
+  const uint32_t max_ctas = (uint32_t)(sm_count * occ);
+  const uint32_t want = n_tiles > 64u ? n_tiles : 64u;  // the scan phase wants a few warps even for tiny inputs
+  return (int)(want < max_ctas ? want : max_ctas);
 }
 
 }  // namespace gmpm

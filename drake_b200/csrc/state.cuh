@@ -142,7 +142,7 @@ struct State {
   uint64_t launches = 0;
   Profiler prof;
   int sm_count = 148;
-  int p2g_ctas_per_sm = 1, g2p_ctas_per_sm = 1;
+  int p2g_ctas_per_sm = 1, g2p_ctas_per_sm = 1, bin_ctas = 0, sort_ctas = 0;
   bool g2p_queue_ready = false;
 
   // ---------------------------------------------------------------------------------------------
@@ -340,56 +340,39 @@ struct State {
   void ensure_binning() {
     ensure_keys();
     if (bin_valid || N == 0) return;
-    // first pass reads `key` (by slot) and generates slot ids; later passes ping-pong skeys/svals
-    sres = sort_from(key, skeys, svals, (uint32_t)N, key_bits());
+    // one cooperative launch: stable sort of (key, slot) on all key bits + block ranges + work records
     ++bin_epoch;
-    launch("bin_reset");
-    bin_reset_kernel<<<1, 1, 0, stream>>>(ctr);
-    launch("build_pblocks");
-    build_pblocks_kernel<<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, skeys[sres], bin_epoch, pb_start,
-                                                                pb_end, pb_epoch, pb_list, ctr);
-    launch("classify_pblocks");
-    classify_pblocks_kernel<<<std::min<uint32_t>(blocks_for(work_cap), 2u * sm_count), kThreads, 0, stream>>>(
-        (uint32_t)work_cap, pb_list, pb_start, pb_end, pb_tile, pb_work, ctr);
-    GMPM_CUDA(cudaGetLastError());
+    BinArgs a{};
+    a.sort = make_sort_args(key, nullptr, skeys, svals, (uint32_t)N, key_bits(), sort_scratch);
+    a.N = (uint32_t)N;
+    a.epoch = bin_epoch;
+    a.work_cap = (uint32_t)work_cap;
+    a.pb_start = pb_start;
+    a.pb_end = pb_end;
+    a.pb_epoch = pb_epoch;
+    a.pb_list = pb_list;
+    a.pb_tile = pb_tile;
+    a.pb_work = pb_work;
+    a.ctr = ctr;
+    sres = (a.sort.n_passes - 1) & 1;
+    if (bin_ctas == 0) bin_ctas = sort_grid_ctas(bin_particles_kernel, sm_count, a.sort.n_tiles);
+    void* kargs[] = {&a};
+    launch("bin_particles");
+    GMPM_CUDA(cudaLaunchCooperativeKernel((void*)bin_particles_kernel, dim3(bin_ctas), dim3(kSortThreads), kargs,
+                                          kSortSmemBytes, stream));
     g2p_queue_ready = false;
     bin_valid = true;
   }
 
-  // Sort (in_keys, iota) on `bits` key bits; result pair index in (ks, vs).
-  int sort_from(uint32_t* in_keys, uint32_t* ks[2], uint32_t* vs[2], uint32_t n, int bits) {
-    // pass 0: in_keys -> ks[0]; then ks[0] <-> ks[1]
-    const uint32_t n_tiles = (n + kSortTile - 1) / kSortTile;
-    uint32_t* hist = sort_scratch;
-    uint32_t* totals = sort_scratch + (size_t)kRadix * n_tiles;
-    const int passes = (bits + kRadixBits - 1) / kRadixBits;
-    note("memset");
-    GMPM_CUDA(cudaMemsetAsync(totals, 0, sizeof(uint32_t) * kRadix * 4, stream));
-    const uint32_t* src_k = in_keys;
-    const uint32_t* src_v = nullptr;
-    int dst = 0;
-    for (int p = 0; p < passes; ++p) {
-      const int shift = p * kRadixBits;
-      const int nb = std::min(bits - shift, kRadixBits);
-      const uint32_t mask = (1u << nb) - 1u;
-      uint32_t* tot = totals + (size_t)p * kRadix;
-      launch("radix_hist");
-      radix_hist_kernel<<<n_tiles, kSortThreads, 0, stream>>>(src_k, n, shift, mask, n_tiles, hist, tot);
-      launch("radix_scan");
-      radix_scan_kernel<<<kRadix, kSortThreads, 0, stream>>>(hist, tot, n_tiles);
-      launch("radix_scatter");
-      if (p == 0)
-        radix_scatter_kernel<true><<<n_tiles, kSortThreads, 0, stream>>>(src_k, nullptr, ks[dst], vs[dst], n, shift,
-                                                                         mask, n_tiles, hist);
-      else
-        radix_scatter_kernel<false><<<n_tiles, kSortThreads, 0, stream>>>(src_k, src_v, ks[dst], vs[dst], n, shift,
-                                                                          mask, n_tiles, hist);
-      GMPM_CUDA(cudaGetLastError());
-      src_k = ks[dst];
-      src_v = vs[dst];
-      dst ^= 1;
-    }
-    return dst ^ 1;
+  // Stable sort of (in_keys, 0..n-1) on `bits` key bits into (ks, vs); returns the result buffer index.
+  int sort_iota(const uint32_t* in_keys, uint32_t* ks[2], uint32_t* vs[2], uint32_t n, int bits) {
+    SortArgs a = make_sort_args(in_keys, nullptr, ks, vs, n, bits, sort_scratch);
+    if (sort_ctas == 0) sort_ctas = sort_grid_ctas(radix_sort_kernel, sm_count, a.n_tiles);
+    void* kargs[] = {&a};
+    launch("radix_sort");
+    GMPM_CUDA(cudaLaunchCooperativeKernel((void*)radix_sort_kernel, dim3(sort_ctas), dim3(kSortThreads), kargs,
+                                          kSortSmemBytes, stream));
+    return (a.n_passes - 1) & 1;
   }
 
   // ---- GpuMpmSolver<T>::RebuildMapping (cuda_mpm_solver.cu:18-70) -------------------------------
@@ -409,10 +392,10 @@ struct State {
                                                                       slot_of_pid, vis_keys[0], vis_ids[0]);
     GMPM_CUDA(cudaGetLastError());
     const int bits = std::min(key_bits(), 16);  // cuda_mpm_solver.cu:57
-    // sort_from reads vis_keys[0] as the input and would overwrite it in pass 0 -> stage through vis_keys[1]
+    // pass 0 reads vis_keys[0] and must not overwrite it -> it writes the pair [1] first
     uint32_t* ks[2] = {vis_keys[1], vis_keys[0]};
     uint32_t* vs[2] = {vis_ids[1], vis_ids[0]};
-    const int r = sort_from(vis_keys[0], ks, vs, (uint32_t)N, bits);
+    const int r = sort_iota(vis_keys[0], ks, vs, (uint32_t)N, bits);
     vis_res = (r == 0) ? 1 : 0;
     launch("permute_visible");
     permute_visible_kernel<<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, vis_ids[vis_res], pid_of_vis[vis_cur],
