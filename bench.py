@@ -8,13 +8,15 @@ Workload (BASELINE.json configs[1]): 34 stacked 100x100 cloth s
 N = 1 006 468 particles, fp64, dt = 1e-3, no rigid contact, 128^3 grid, the reference's own
 standalone loop (cuda_mpm_test.cc:63-72): RebuildMapping(sort = every 40th substep)
 CalcFemStateAndForce ParticleToGrid UpdateGrid GridToParticle.  One "step" = one substep.
-N > 1: one such scene per GPU (cloth shards by whole sheets; the path has no exchange step for
-cloth scenes, so there is no data-path collective) -> weak scaling.
+N > 1: weak scaling -- every rank owns one such stack (whole meshes) of one larger scene on a 256^3
+grid with the same dx; stacks are piled in pairs, and the grid blocks two ranks reach are summed
+between P2G and UpdateGrid every substep (drake_b200/slab.py: two NCCL all-reduces).
 
   value : device-timed (CUDA events on the library's stream), state resident in HBM.
   e2e   : the DeformableDriver substep through the C ABI with HOST buffers
-          (deformable_driver.h:240-260): SyncParticleStateToCpu (D2H of all positions into pinned
-          host memory) + CopyContactPairs (H2D; empty in this config) + the five solver calls.
+          (deformable_driver.h:240-260): SyncParticleStateToCpu (D2H of all positions into the pinned
+          host mirror, every substep) + positions_host() read + CopyContactPairs (H2D; empty in this
+          config) + the five solver calls.
   roofline : P2G tile kernel, algorithmic bytes / per-launch CUDA-event time (separate profiled pass).
   cpu_baseline : the CPU oracle (oracle/, OpenMP) on this box's host cores, bounded sample.
 `--impl reference` times that CPU port alone (the reference has no CPU implementation of this path;
@@ -39,7 +41,7 @@ DT = 1e-3
 SORT_EVERY = 40
 METRIC = "particle_steps_per_sec"
 UNIT = "particle-steps/s"
-WORKLOAD = "cfg-2: 34 stacked 100x100 cloth sheets, N=1006468, fp64, dt=1e-3, no contact, 128^3 grid"
+WORKLOAD = "cfg-2: 34 stacked 100x100 cloth sheets, N=1006468 per GPU, fp64, dt=1e-3, no contact, dx=1/128"
 
 
 def env_int(name, default):
@@ -49,13 +51,27 @@ def env_int(name, default):
         return default
 
 
-def build_scene(cls_factory, dtype):
+def build_scene(cls_factory, dtype, rank=0, world=1):
+    """N = 1: cfg-2 as the reference would run it (128^3 unit cube).  N > 1: every rank owns one such
+    34-sheet stack of ONE larger scene on a 256^3 grid with the same dx = 1/128 (domain [0,2]^3): ranks
+    2c and 2c+1 are stacked in z in column c (the upper stack rests on the lower one: their boundary
+    sheets reach common grid blocks, which the ranks sum every substep), columns sit 1.0 apart in x / y."""
     from drake_b200 import scenes
     st = cls_factory()
-    for pos, vel, tri in scenes.stacked_sheets(N_SHEETS, dtype=dtype):
-        st.AddQRCloth(pos, vel, tri)
+    col, lvl = rank // 2, rank % 2
+    ox, oy = (float(col % 2), float(col // 2)) if world > 1 else (0.0, 0.0)
+    z0 = 0.15 + lvl * N_SHEETS * 0.02
+    for pos, vel, tri in scenes.stacked_sheets(N_SHEETS, z0=z0, dtype=dtype, seed=scenes.SEED + rank):
+        pos = pos.astype(np.float64)
+        pos[:, 0] += ox
+        pos[:, 1] += oy
+        st.AddQRCloth(pos.astype(dtype), vel, tri)
     st.Finalize()
     return st
+
+
+def scene_params(world):
+    return {} if world == 1 else {"domain_bits": 8, "dx": 1.0 / 128}
 
 
 class ClockSampler(threading.Thread):
@@ -225,43 +241,64 @@ def main():
     from drake_b200.gpu_mpm import GpuMpmSolver, GpuMpmState, MpmParticleContactPairs
     dtype = np.float64 if args.dtype == "f64" else np.float32
     T = np.dtype(dtype).itemsize
-    st = build_scene(lambda: GpuMpmState(dtype, device=local), dtype)
+    st = build_scene(lambda: GpuMpmState(dtype, device=local, **scene_params(world)), dtype, rank, world)
     sv = GpuMpmSolver()
     N = st.n_particles()
     K, W = args.steps, args.warmup
+    ex = None
+    if world > 1:
+        from drake_b200 import slab
+        ex = slab.SlabExchange(slab.GpuHaloBackend(st))
+
+    def run_substeps(n, first=0):
+        if ex is None:
+            sv.RunSubsteps(st, n, DT, -1, SORT_EVERY)      # one ABI crossing, same calls inside
+            return
+        for i in range(first, first + n):                  # the exchange sits between P2G and UpdateGrid
+            slab.substep(sv, st, ex, DT, -1, i % SORT_EVERY == 0)
 
     sampler = ClockSampler(local)
     sampler.start()
 
     # ---- device-timed region -------------------------------------------------------------------
-    sv.RunSubsteps(st, W, DT, -1, SORT_EVERY)
+    run_substeps(W)
     sv.GpuSync(st)
     barrier()
     l0 = st.kernel_launches()
+    shared0 = ex.bytes_reduced if ex else 0
     w0 = time.perf_counter()
     st.timer_mark(0)
-    sv.RunSubsteps(st, K, DT, -1, SORT_EVERY)
+    run_substeps(K)
     st.timer_mark(1)
     sv.GpuSync(st)
     barrier()
     w1 = time.perf_counter()
     launches = st.kernel_launches() - l0
     ms = st.timer_elapsed_ms(0, 1)
+    halo_bytes_per_step = (ex.bytes_reduced - shared0) / K if ex else 0
+    halo_blocks = ex.last_n_shared if ex else 0
     clocks = sampler.summary(w0, w1)
 
     # ---- end-to-end region: the driver substep with host buffers ---------------------------------
-    pos_host = torch.empty((N, 3), dtype=torch.float64 if dtype == np.float64 else torch.float32).pin_memory()
-    pos_np = pos_host.numpy()
+    # deformable_driver.h:240-260 as the drop-in shim issues it: SyncParticleStateToCpu starts the
+    # snapshot of ALL positions (device gather + D2H into the library's pinned mirror), the four solver
+    # calls are enqueued, positions_host() -- which CalcMpmContactPairs reads (:120-194) -- waits for
+    # the copy and the result is read on the host, the contact pairs go up (H2D; none in this config).
     pairs = MpmParticleContactPairs(dtype)
     contact_ok = True
+    e2e_check = [0.0]
 
     def driver_substep(i):
         nonlocal contact_ok
-        sv.SyncParticleStateToCpu(st, pos_np)              # D2H, blocking (deformable_driver.h:243)
+        sv.SyncParticleStateToCpu(st)                      # deformable_driver.h:243
         sv.RebuildMapping(st, i % SORT_EVERY == 0)
         sv.CalcFemStateAndForce(st, DT)
         sv.ParticleToGrid(st, DT)
+        if ex is not None:
+            ex.exchange()
         sv.UpdateGrid(st, -1)
+        ph = st.positions_host()                           # host read of this step's particle positions
+        e2e_check[0] += float(ph[i % N, 2])
         if contact_ok:
             try:
                 sv.CopyContactPairs(st, pairs)             # H2D (empty here), :250
@@ -284,7 +321,7 @@ def main():
     # ---- per-kernel pass (CUDA events between launches on the library's stream) ------------------
     Kp = max(3, min(K, 200))
     st.set_profiling(True)
-    sv.RunSubsteps(st, Kp, DT, -1, SORT_EVERY)
+    run_substeps(Kp)
     sv.GpuSync(st)
     prof = st.profile_report()
     st.set_profiling(False)
@@ -338,12 +375,16 @@ def main():
                 "config": {"workload": WORKLOAD, "sort_every": SORT_EVERY, "particles_per_gpu": N,
                            "particle_blocks": pblocks, "touched_grid_blocks": touched,
                            "l2": "inputs larger than L2 (particle state %.0f MB per step > 126 MB)" % (N * (44 * T + 8) / 1e6),
-                           "parallelism": "1 scene per GPU, no data-path collective"},
+                           "parallelism": "single GPU" if world == 1 else
+                           "%d ranks, one 34-sheet stack each of one scene on a 256^3 grid (dx = 1/128); grid blocks "
+                           "reached by two ranks are summed every substep: all-reduce of block flags + all-reduce of "
+                           "%d shared blocks (%.0f KB/step) over NCCL" % (world, halo_blocks, halo_bytes_per_step / 1e3)},
                 "clocks": clocks,
                 "e2e": {"value": N_all * Ke / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0,
                         "d2h_bytes_per_step": int(3 * T * N), "steps": Ke, "ms_per_step": e_ms / Ke,
-                        "what": "DeformableDriver substep through the C ABI: SyncParticleStateToCpu (all positions "
-                                "to pinned host memory) + CopyContactPairs (0 pairs) + 5 solver calls"},
+                        "what": "DeformableDriver substep through the C ABI: SyncParticleStateToCpu (snapshot of all "
+                                "positions -> pinned host mirror, copy overlapped with the next 4 solver calls), "
+                                "positions_host() wait + host read, CopyContactPairs (0 pairs), 5 solver calls"},
                 "gpu_launches": launches_all, "gpu_launches_per_step": launches_all / K / world,
                 "roofline": roofline, "kernels": kern}
         if world == 1 and not args.no_cpu_baseline:

@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libgmpm_b200.so")
+LIB_PATH = os.environ.get("GMPM_B200_LIB") or os.path.join(HERE, "lib", "libgmpm_b200.so")  # override: build variants (tools/)
 
 
 class GmpmError(RuntimeError):
@@ -18,7 +18,7 @@ class Params(C.Structure):
     _fields_ = [("domain_bits", C.c_int), ("boundary_cells", C.c_int), ("gravity_axis", C.c_int),
                 ("device", C.c_int), ("youngs", C.c_double), ("poisson", C.c_double), ("density", C.c_double),
                 ("gamma", C.c_double), ("k_normal", C.c_double), ("v_blend", C.c_double), ("c_f", C.c_double),
-                ("sdf_friction", C.c_double), ("gravity", C.c_double), ("epsv", C.c_double)]
+                ("sdf_friction", C.c_double), ("gravity", C.c_double), ("epsv", C.c_double), ("dx", C.c_double)]
 
 
 class ContactStats(C.Structure):
@@ -30,7 +30,8 @@ class ContactStats(C.Structure):
 PLAIN_SYMBOLS = ["gmpm_default_params", "gmpm_last_error", "gmpm_version", "gmpm_device_count", "gmpm_device_sync",
                  "gmpm_morton_code", "gmpm_cell_index", "gmpm_inverse_cell_index", "gmpm_radix_sort_pairs"]
 TYPED_SYMBOLS = ["create", "destroy", "add_qr_cloth", "finalize", "rebuild_mapping", "calc_fem", "p2g",
-                 "update_grid", "g2p", "sync", "sync_particle_state_to_cpu", "copy_contact_pairs",
+                 "update_grid", "g2p", "sync", "sync_particle_state_to_cpu", "sync_particle_state_to_cpu_async",
+                 "positions_host", "halo_flags", "halo_plan", "halo_unpack", "stream", "copy_contact_pairs",
                  "update_contact", "reallocate_external_bodies", "external_body_force_to_host",
                  "dump_cpu_state", "n_verts", "n_faces", "n_particles", "n_cells", "num_contacts",
                  "grid_touched_cnt_host", "read", "run_substeps", "kernel_launches", "set_profiling",
@@ -82,6 +83,12 @@ def _declare(L):
         g("g2p").argtypes = [vp, ct]
         g("sync").argtypes = [vp]
         g("sync_particle_state_to_cpu").argtypes = [vp, vp]
+        g("sync_particle_state_to_cpu_async").argtypes = [vp]
+        g("positions_host").argtypes = [vp, C.POINTER(C.c_void_p)]
+        g("halo_flags").argtypes = [vp, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
+        g("halo_plan").argtypes = [vp, C.POINTER(C.c_uint32), C.POINTER(C.c_void_p)]
+        g("halo_unpack").argtypes = [vp]
+        g("stream").argtypes = [vp, C.POINTER(C.c_void_p)]
         g("copy_contact_pairs").argtypes = [vp, sz] + [vp] * 7
         g("update_contact").argtypes = [vp, ct, ct, ct, ct, C.c_int, C.c_int, C.POINTER(ContactStats)]
         g("reallocate_external_bodies").argtypes = [vp, sz]

@@ -72,6 +72,9 @@ size_t State<T>::read(const char* name, void* out, size_t cap) {
   if (n == "velocities") return particle_field(vel[cur], 3, false);
   if (n == "volumes") return particle_field(vol[cur], 1, false);
   if (n == "affine_matrices") return particle_field(C[cur], 9, false);
+  if ((n == "forces" || n == "taus") && !fem_valid)
+    throw std::invalid_argument("forces / taus are defined between CalcFemStateAndForce and GridToParticle only "
+                                "(the reference overwrites them in the next CalcFemStateAndForce)");
   if (n == "forces") return particle_field(forces, 3, false);
   if (n == "taus") {
     const size_t bytes = need(sizeof(T) * 9 * N);

@@ -50,6 +50,7 @@ void gmpm_default_params(gmpm_params* p) {
   p->sdf_friction = 0.3;
   p->gravity = -9.8;
   p->epsv = 1e-3;
+  p->dx = 0.;
 }
 const char* gmpm_last_error(void) { return g_last_error.c_str(); }
 const char* gmpm_version(void) { return "gmpm_b200 0.1 (sm_100a, CUDA " GMPM_STR(CUDART_VERSION) ")"; }
@@ -157,6 +158,15 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
   int gmpm_sync_particle_state_to_cpu_##SUF(gmpm_state_##SUF* s, T* out) {                                     \
     return guarded([&] { s->st.positions_to_host(out); });                                                     \
   }                                                                                                            \
+  int gmpm_sync_particle_state_to_cpu_async_##SUF(gmpm_state_##SUF* s) {                                       \
+    return guarded([&] { s->st.positions_async(); });                                                          \
+  }                                                                                                            \
+  int gmpm_positions_host_##SUF(gmpm_state_##SUF* s, const T** out) {                                          \
+    return guarded([&] {                                                                                       \
+      if (!out) throw std::invalid_argument("null out pointer");                                               \
+      *out = s->st.wait_positions();                                                                           \
+    });                                                                                                        \
+  }                                                                                                            \
   int gmpm_copy_contact_pairs_##SUF(gmpm_state_##SUF* s, size_t n, const uint32_t* mpm_id,                     \
                                     const uint32_t* rigid_id, const T* dist, const T* normal, const T* pos,    \
                                     const T* rigid_v, const T* rigid_p) {                                      \
@@ -187,6 +197,27 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
     return guarded([&] {                                                                                       \
       const size_t b = s->st.read(name, out, cap);                                                             \
       if (written) *written = b;                                                                               \
+    });                                                                                                        \
+  }                                                                                                            \
+  int gmpm_halo_flags_##SUF(gmpm_state_##SUF* s, void** flags_dev, size_t* n_blocks) {                         \
+    return guarded([&] {                                                                                       \
+      if (!flags_dev || !n_blocks) throw std::invalid_argument("null out pointer");                            \
+      *flags_dev = s->st.halo_flags();                                                                         \
+      *n_blocks = s->st.k.n_blocks;                                                                            \
+    });                                                                                                        \
+  }                                                                                                            \
+  int gmpm_halo_plan_##SUF(gmpm_state_##SUF* s, uint32_t* n_shared, void** packed_dev) {                       \
+    return guarded([&] {                                                                                       \
+      if (!n_shared || !packed_dev) throw std::invalid_argument("null out pointer");                           \
+      *n_shared = s->st.halo_plan();                                                                           \
+      *packed_dev = s->st.halo_packed;                                                                         \
+    });                                                                                                        \
+  }                                                                                                            \
+  int gmpm_halo_unpack_##SUF(gmpm_state_##SUF* s) { return guarded([&] { s->st.halo_unpack(); }); }            \
+  int gmpm_stream_##SUF(gmpm_state_##SUF* s, void** cuda_stream) {                                             \
+    return guarded([&] {                                                                                       \
+      if (!cuda_stream) throw std::invalid_argument("null out pointer");                                       \
+      *cuda_stream = (void*)s->st.stream;                                                                      \
     });                                                                                                        \
   }                                                                                                            \
   int gmpm_run_substeps_##SUF(gmpm_state_##SUF* s, int n, T dt, int bc, int sort_every) {                      \

@@ -1,0 +1,116 @@
+// halo.cuh -- shared-block exchange for scenes partitioned across GPUs (one process / state per GPU).
+//
+// The reference is single-GPU (settings.h:40 G_DEVICE_COUNT = 1, never used); this is the multi-GPU
+// extension SURVEY.md 8(e) plans.  Cloth particles are owned by MESH (a triangle gathers its three
+// vertices, so a mesh never straddles ranks); every rank addresses the same block-major grid.  The
+// only coupling between ranks is through grid blocks that particles of more than one rank reach, so
+// the exchange step sits between ParticleToGrid and UpdateGrid:
+//
+//   1. halo_flags   : flags[b] = 1 if this rank's P2G touched grid block b          (uint8[n_blocks])
+//      -- host: all-reduce SUM of flags over the ranks (NCCL, on this state's stream) --
+//   2. halo_plan    : shared blocks = {b : flags[b] > 1}, listed in ascending block id by a
+//                     deterministic two-kernel compaction (every rank derives the SAME list from the
+//                     same reduced flags); packed[i][4][64] = this rank's mass and momentum of shared
+//                     block i (zeros if this rank does not touch it); n_shared goes to the host
+//      -- host: all-reduce SUM of packed[0 : n_shared * 256] --
+//   3. halo_unpack  : the summed mass / momentum are written back into the blocks this rank touches.
+//
+// UpdateGrid then runs on each rank's own touched list: shared blocks are updated redundantly from
+// identical sums, so all owners see bit-identical grid velocities, and G2P stays local.  No particle
+// changes owner (ownership is by mesh), so there is no migration step for cloth scenes.
+#pragma once
+#include "kernels.cuh"
+
+namespace gmpm {
+
+constexpr int kHaloThreads = 256;
+constexpr int kHaloBlocksPerCta = 1024;  // grid blocks scanned by one CTA (4 per thread)
+
+__global__ void halo_flags_kernel(uint32_t n_blocks, const uint32_t* __restrict__ touched_epoch, uint32_t epoch,
+                                  uint8_t* __restrict__ flags) {
+  const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < n_blocks) flags[b] = touched_epoch[b] == epoch ? 1 : 0;
+}
+
+__device__ __forceinline__ uint32_t halo_shared_mask(const uint8_t* __restrict__ flags, uint32_t n_blocks,
+                                                     uint32_t b0) {
+  uint32_t m = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    if (b0 + j < n_blocks && flags[b0 + j] > 1) m |= 1u << j;
+  return m;
+}
+
+// Pass 1: number of shared blocks in each CTA's span.
+__global__ void __launch_bounds__(kHaloThreads)
+halo_count_kernel(uint32_t n_blocks, const uint8_t* __restrict__ flags, uint32_t* __restrict__ cta_counts) {
+  __shared__ uint32_t s_sum;
+  if (threadIdx.x == 0) s_sum = 0;
+  __syncthreads();
+  const uint32_t b0 = (blockIdx.x * kHaloThreads + threadIdx.x) * 4u;
+  uint32_t c = __popc(halo_shared_mask(flags, n_blocks, b0));
+  c = __reduce_add_sync(kFullMask, c);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_sum, c);
+  __syncthreads();
+  if (threadIdx.x == 0) cta_counts[blockIdx.x] = s_sum;
+}
+
+// Pass 2: ascending list of shared blocks (stable: CTA offset = sum of the preceding CTA counts,
+// in-CTA offset by an exclusive scan over the threads).
+__global__ void __launch_bounds__(kHaloThreads)
+halo_compact_kernel(uint32_t n_blocks, const uint8_t* __restrict__ flags, const uint32_t* __restrict__ cta_counts,
+                    uint32_t* __restrict__ list, uint32_t list_cap, uint32_t* __restrict__ n_shared) {
+  __shared__ uint32_t s_warp[kHaloThreads / 32];
+  __shared__ uint32_t s_base;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // offset of this CTA
+  uint32_t pre = 0;
+  for (uint32_t i = threadIdx.x; i < blockIdx.x; i += kHaloThreads) pre += cta_counts[i];
+  pre = __reduce_add_sync(kFullMask, pre);
+  if (threadIdx.x == 0) s_base = 0;
+  __syncthreads();
+  if (lane == 0 && pre) atomicAdd(&s_base, pre);
+  const uint32_t b0 = (blockIdx.x * kHaloThreads + threadIdx.x) * 4u;
+  const uint32_t m = halo_shared_mask(flags, n_blocks, b0);
+  const uint32_t c = __popc(m);
+  uint32_t incl = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(kFullMask, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  uint32_t off = s_base + incl - c;
+  for (int w = 0; w < warp; ++w) off += s_warp[w];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    if ((m >> j) & 1u) {
+      if (off < list_cap) list[off] = b0 + j;
+      ++off;
+    }
+  if (blockIdx.x == gridDim.x - 1 && threadIdx.x == kHaloThreads - 1) *n_shared = off;  // grand total
+}
+
+// packed[i][c][l], c = 0: mass, 1..3: momentum.  One CTA-quarter (64 threads) per (block, channel).
+template <typename T, bool UNPACK>
+__global__ void __launch_bounds__(kHaloThreads)
+halo_pack_kernel(const uint32_t* __restrict__ n_shared_p, uint32_t list_cap, const uint32_t* __restrict__ list,
+                 const uint32_t* __restrict__ touched_epoch, uint32_t epoch, T* __restrict__ g_mass,
+                 T* __restrict__ g_vel, T* __restrict__ packed) {
+  const uint32_t n = min(*n_shared_p, list_cap);
+  const uint32_t c = threadIdx.x >> 6, l = threadIdx.x & 63u;
+  for (uint32_t i = blockIdx.x; i < n; i += gridDim.x) {
+    const uint32_t g = list[i];
+    const bool own = touched_epoch[g] == epoch;
+    T* cell = c == 0 ? g_mass + (size_t)g * 64 + l : g_vel + (size_t)g * 192 + (size_t)(c - 1) * 64 + l;
+    T* slot = packed + (size_t)i * 256 + threadIdx.x;
+    if (UNPACK) {
+      if (own) *cell = *slot;
+    } else {
+      *slot = own ? *cell : T(0);
+    }
+  }
+}
+
+}  // namespace gmpm

@@ -138,6 +138,7 @@ __global__ void permute_visible_kernel(uint32_t N, const uint32_t* __restrict__ 
 struct BinArgs {
   SortArgs sort;
   uint32_t N, epoch, work_cap;
+  int roll_touched;  // binning on behalf of P2G: also do p2g_prologue_kernel's job (saves a launch)
   uint32_t *pb_start, *pb_end, *pb_epoch, *pb_list;
   uint2* pb_tile;
   WorkRec* pb_work;
@@ -152,6 +153,12 @@ __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs 
     a.ctr->n_big = 0;
     a.ctr->n_small = 0;
     a.ctr->n_tiles = 0;
+    if (a.roll_touched) {
+      a.ctr->n_touched_prev = a.ctr->n_touched;
+      a.ctr->n_touched = 0;
+      a.ctr->work_p2g = 0;
+      a.ctr->work_g2p = 0;
+    }
   }
   const int r = radix_sort_device(a.sort, sort_smem, grid);  // ends with a grid barrier
   const uint32_t* sorted_key = a.sort.keys[r];
@@ -203,85 +210,121 @@ __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs 
 // ------------------------------------------------------------------------------------------------
 // Constitutive update (replaces calc_fem_state_and_force_kernel, :183-294).  One thread per face.
 // ------------------------------------------------------------------------------------------------
+// Memory-latency design: the face record needs three dependent levels of loads (face -> particle ids ->
+// slots -> vertex state).  The kernel is persistent (grid-stride over faces) and software-pipelined:
+// the slot indices of the NEXT face of a thread are resolved while the current face is computed, and
+// every load of the current face (F, Dm^-1, C, volume, the three vertices' x and v) is issued before
+// the first use, so a face costs about one memory round trip instead of a dozen serialized ones.
+#ifndef GMPM_FEM_MIN_CTAS
+#define GMPM_FEM_MIN_CTAS 3
+#endif
+constexpr int kFemThreads = 128;
+
+struct FemIdx {
+  int sf, s0, s1, s2;
+};
+
 template <typename T>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(kFemThreads, GMPM_FEM_MIN_CTAS)
 fem_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ tri, const int* __restrict__ slot_of_pid,
            const T* __restrict__ vol, const T* __restrict__ C, const T* __restrict__ Dm_inv, T* __restrict__ pos,
            T* __restrict__ vel, T* __restrict__ Fd, T* __restrict__ forces, T* __restrict__ taus,
            uint32_t* __restrict__ key, T dt, Consts<T> k) {
-  const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
-  if (f >= n_faces) return;
-  const int sf = slot_of_pid[f];
-  const int s0 = slot_of_pid[tri[f]], s1 = slot_of_pid[tri[n_faces + f]], s2 = slot_of_pid[tri[2 * n_faces + f]];
-  T x0[3], x1[3], x2[3], xc[3];
+  const uint32_t stride = gridDim.x * blockDim.x;
+  uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+  auto resolve = [&](uint32_t ff) -> FemIdx {
+    FemIdx r{0, 0, 0, 0};
+    if (ff < n_faces) {
+      const int t0 = tri[ff], t1 = tri[n_faces + ff], t2 = tri[2 * n_faces + ff];
+      r.sf = slot_of_pid[ff];
+      r.s0 = slot_of_pid[t0];
+      r.s1 = slot_of_pid[t1];
+      r.s2 = slot_of_pid[t2];
+    }
+    return r;
+  };
+  FemIdx cur = resolve(f);
+  for (; f < n_faces; f += stride) {
+    const int sf = cur.sf, s0 = cur.s0, s1 = cur.s1, s2 = cur.s2;
+    // ---- every load of this face, before any use
+    T x0[3], x1[3], x2[3], v0[3], v1[3], v2[3], F[9], Cm[9], Dmi[4];
 #pragma unroll
-  for (int d = 0; d < 3; ++d) {
-    x0[d] = pos[d * N + s0];
-    x1[d] = pos[d * N + s1];
-    x2[d] = pos[d * N + s2];
-    xc[d] = (x0[d] + x1[d] + x2[d]) / T(3);
-    pos[d * N + sf] = xc[d];
-    vel[d * N + sf] = (vel[d * N + s0] + vel[d * N + s1] + vel[d * N + s2]) / T(3);
-  }
-  // the face particle moved: refresh its cell key (binning happens after this kernel)
-  key[sf] = cell_key(base_node(xc[0], k.dx_inv, k.domain_size), base_node(xc[1], k.dx_inv, k.domain_size),
-                     base_node(xc[2], k.dx_inv, k.domain_size));
-  T F[9], Cm[9];
+    for (int d = 0; d < 3; ++d) {
+      x0[d] = pos[(size_t)d * N + s0];
+      x1[d] = pos[(size_t)d * N + s1];
+      x2[d] = pos[(size_t)d * N + s2];
+      v0[d] = vel[(size_t)d * N + s0];
+      v1[d] = vel[(size_t)d * N + s1];
+      v2[d] = vel[(size_t)d * N + s2];
+    }
 #pragma unroll
-  for (int e = 0; e < 9; ++e) {
-    F[e] = Fd[e * n_faces + f];
-    Cm[e] = C[e * N + sf];
-  }
-  T ctF[9];
-  ctF[0] = F[0];
-  ctF[1] = F[1];
-  ctF[2] = (T(1) + dt * Cm[0]) * F[2] + dt * Cm[1] * F[5] + dt * Cm[2] * F[8];
-  ctF[3] = F[3];
-  ctF[4] = F[4];
-  ctF[5] = dt * Cm[3] * F[2] + (T(1) + dt * Cm[4]) * F[5] + dt * Cm[5] * F[8];
-  ctF[6] = F[6];
-  ctF[7] = F[7];
-  ctF[8] = dt * Cm[6] * F[2] + dt * Cm[7] * F[5] + (T(1) + dt * Cm[8]) * F[8];
-  cloth_project_strain(k, ctF);
+    for (int e = 0; e < 9; ++e) {
+      F[e] = Fd[(size_t)e * n_faces + f];
+      Cm[e] = C[(size_t)e * N + sf];
+    }
+#pragma unroll
+    for (int e = 0; e < 4; ++e) Dmi[e] = Dm_inv[(size_t)e * n_faces + f];
+    const T volume = vol[sf];
+    // ---- indices of this thread's next face (in flight during the math below)
+    cur = resolve(f + stride);
 
-  T Dmi[4];
+    T xc[3];
 #pragma unroll
-  for (int e = 0; e < 4; ++e) Dmi[e] = Dm_inv[e * n_faces + f];
-  // in-plane columns: ds * Dm^-1
-#pragma unroll
-  for (int d = 0; d < 3; ++d) {
-    const T a = x1[d] - x0[d], b = x2[d] - x0[d];
-    ctF[d * 3 + 0] = a * Dmi[0] + b * Dmi[2];
-    ctF[d * 3 + 1] = a * Dmi[1] + b * Dmi[3];
-  }
-#pragma unroll
-  for (int e = 0; e < 9; ++e) Fd[e * n_faces + f] = ctF[e];
+    for (int d = 0; d < 3; ++d) {
+      xc[d] = (x0[d] + x1[d] + x2[d]) / T(3);
+      pos[(size_t)d * N + sf] = xc[d];
+      vel[(size_t)d * N + sf] = (v0[d] + v1[d] + v2[d]) / T(3);
+    }
+    // the face particle moved: refresh its cell key (binning happens after this kernel)
+    key[sf] = cell_key(base_node(xc[0], k.dx_inv, k.domain_size), base_node(xc[1], k.dx_inv, k.domain_size),
+                       base_node(xc[2], k.dx_inv, k.domain_size));
+    T ctF[9];
+    ctF[0] = F[0];
+    ctF[1] = F[1];
+    ctF[2] = (T(1) + dt * Cm[0]) * F[2] + dt * Cm[1] * F[5] + dt * Cm[2] * F[8];
+    ctF[3] = F[3];
+    ctF[4] = F[4];
+    ctF[5] = dt * Cm[3] * F[2] + (T(1) + dt * Cm[4]) * F[5] + dt * Cm[5] * F[8];
+    ctF[6] = F[6];
+    ctF[7] = F[7];
+    ctF[8] = dt * Cm[6] * F[2] + dt * Cm[7] * F[5] + (T(1) + dt * Cm[8]) * F[8];
+    cloth_project_strain(k, ctF);
 
-  T VP[9];
-  cloth_pk1(k, ctF, VP);
-  const T volume = vol[sf];
+    // in-plane columns: ds * Dm^-1
 #pragma unroll
-  for (int e = 0; e < 9; ++e) VP[e] *= volume;
-  // tau = V * P[:,2] (x) F[:,2] is rank one: stored as its two factors, rows 0-2 and 3-5 of taus[6][N]
+    for (int d = 0; d < 3; ++d) {
+      const T a = x1[d] - x0[d], b = x2[d] - x0[d];
+      ctF[d * 3 + 0] = a * Dmi[0] + b * Dmi[2];
+      ctF[d * 3 + 1] = a * Dmi[1] + b * Dmi[3];
+    }
 #pragma unroll
-  for (int a = 0; a < 3; ++a) {
-    taus[(size_t)a * N + sf] = VP[a * 3 + 2];
-    taus[(size_t)(3 + a) * N + sf] = ctF[a * 3 + 2];
-  }
-  // grad_N = Dm^-T * [-1 1 0; -1 0 1]
-  T gN[6];
-  gN[0] = Dmi[0] * T(-1) + Dmi[2] * T(-1);
-  gN[1] = Dmi[0] * T(1) + Dmi[2] * T(0);
-  gN[2] = Dmi[0] * T(0) + Dmi[2] * T(1);
-  gN[3] = Dmi[1] * T(-1) + Dmi[3] * T(-1);
-  gN[4] = Dmi[1] * T(1) + Dmi[3] * T(0);
-  gN[5] = Dmi[1] * T(0) + Dmi[3] * T(1);
+    for (int e = 0; e < 9; ++e) Fd[(size_t)e * n_faces + f] = ctF[e];
+
+    T VP[9];
+    cloth_pk1(k, ctF, VP);
 #pragma unroll
-  for (int d = 0; d < 3; ++d) {
-    const T p0 = VP[d * 3 + 0], p1 = VP[d * 3 + 1];
-    atomicAdd(&forces[d * N + s0], -(p0 * gN[0] + p1 * gN[3]));
-    atomicAdd(&forces[d * N + s1], -(p0 * gN[1] + p1 * gN[4]));
-    atomicAdd(&forces[d * N + s2], -(p0 * gN[2] + p1 * gN[5]));
+    for (int e = 0; e < 9; ++e) VP[e] *= volume;
+    // tau = V * P[:,2] (x) F[:,2] is rank one: stored as its two factors, rows 0-2 and 3-5 of taus[6][N]
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      taus[(size_t)a * N + sf] = VP[a * 3 + 2];
+      taus[(size_t)(3 + a) * N + sf] = ctF[a * 3 + 2];
+    }
+    // grad_N = Dm^-T * [-1 1 0; -1 0 1]
+    T gN[6];
+    gN[0] = Dmi[0] * T(-1) + Dmi[2] * T(-1);
+    gN[1] = Dmi[0] * T(1) + Dmi[2] * T(0);
+    gN[2] = Dmi[0] * T(0) + Dmi[2] * T(1);
+    gN[3] = Dmi[1] * T(-1) + Dmi[3] * T(-1);
+    gN[4] = Dmi[1] * T(1) + Dmi[3] * T(0);
+    gN[5] = Dmi[1] * T(0) + Dmi[3] * T(1);
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      const T p0 = VP[d * 3 + 0], p1 = VP[d * 3 + 1];
+      atomicAdd(&forces[(size_t)d * N + s0], -(p0 * gN[0] + p1 * gN[3]));
+      atomicAdd(&forces[(size_t)d * N + s1], -(p0 * gN[1] + p1 * gN[4]));
+      atomicAdd(&forces[(size_t)d * N + s2], -(p0 * gN[2] + p1 * gN[5]));
+    }
   }
 }
 
@@ -668,21 +711,30 @@ grid_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __rest
     const size_t vbase = (size_t)g * 192 + l;
     if (ASSEMBLE) {
       m = T(0); p[0] = T(0); p[1] = T(0); p[2] = T(0);
+      // resolve the <= 8 source particle blocks first (independent loads in flight together) ...
+      uint2 tr[8];
+      uint32_t node[8];
 #pragma unroll
       for (int d = 0; d < 8; ++d) {
         const uint32_t ddx = (d >> 2) & 1u, ddy = (d >> 1) & 1u, ddz = d & 1u;
         // tile of particle block g - delta covers local cells [4 delta, 4 delta + 6): needs l < 2 where delta = 1
-        if ((ddx && (lx >= 2u || gx == 0u)) || (ddy && (ly >= 2u || gy == 0u)) || (ddz && (lz >= 2u || gz == 0u))) continue;
-        const uint32_t src = morton3(gx - ddx, gy - ddy, gz - ddz);
-        if (pb_epoch[src] != epoch) continue;
-        const uint2 tr = pb_tile[src];
-        const uint32_t n = (lx + 4u * ddx) * 36u + (ly + 4u * ddy) * 6u + (lz + 4u * ddz);
-        for (uint32_t c = 0; c < tr.y; ++c) {  // the chunks of particle block `src`, in chunk order
-          const T* tl = tiles + (size_t)(tr.x + c) * (4 * kTileNodes);
-          m += tl[n];
-          p[0] += tl[kTileNodes + n];
-          p[1] += tl[2 * kTileNodes + n];
-          p[2] += tl[3 * kTileNodes + n];
+        const bool skip = (ddx && (lx >= 2u || gx == 0u)) || (ddy && (ly >= 2u || gy == 0u)) || (ddz && (lz >= 2u || gz == 0u));
+        tr[d] = make_uint2(0u, 0u);
+        node[d] = (lx + 4u * ddx) * 36u + (ly + 4u * ddy) * 6u + (lz + 4u * ddz);
+        if (!skip) {
+          const uint32_t src = morton3(gx - ddx, gy - ddy, gz - ddz);
+          if (pb_epoch[src] == epoch) tr[d] = pb_tile[src];
+        }
+      }
+      // ... then sum their chunks' tiles in a fixed order (delta, then chunk): reproducible
+#pragma unroll
+      for (int d = 0; d < 8; ++d) {
+        const T* tl = tiles + (size_t)tr[d].x * (4 * kTileNodes) + node[d];
+        for (uint32_t c = 0; c < tr[d].y; ++c, tl += 4 * kTileNodes) {
+          m += tl[0];
+          p[0] += tl[kTileNodes];
+          p[1] += tl[2 * kTileNodes];
+          p[2] += tl[3 * kTileNodes];
         }
       }
       if (!UPDATE) {
@@ -749,7 +801,7 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __rest
            const T* __restrict__ g_vel, const T* __restrict__ pos, const T* __restrict__ vol,
            const int* __restrict__ pid, T* __restrict__ pos_out, T* __restrict__ vel_out, T* __restrict__ C_out,
            T* __restrict__ vol_out, int* __restrict__ pid_out, int* __restrict__ slot_of_pid,
-           uint32_t* __restrict__ key_out, DevCounters* ctr, T dt, Consts<T> k) {
+           uint32_t* __restrict__ key_out, T* __restrict__ forces_out, DevCounters* ctr, T dt, Consts<T> k) {
   __shared__ T s_vel[kG2PWarps][3][kTileNodes];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   T* tv = &s_vel[warp][0][0];
@@ -871,6 +923,7 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __rest
         x[d] += nv[d] * dt;
         vel_out[(size_t)d * N + i] = nv[d];
         pos_out[(size_t)d * N + i] = x[d];
+        forces_out[(size_t)d * N + i] = T(0);  // the next constitutive update accumulates into zeros
       }
       vol_out[i] = pvol;
       pid_out[i] = p;

@@ -10,6 +10,7 @@
 
 #include "../../include/gmpm_c.h"
 #include "common.cuh"
+#include "halo.cuh"
 #include "kernels.cuh"
 #include "sort.cuh"
 
@@ -136,14 +137,32 @@ struct State {
   size_t io_cap = 0;
   void* h_pinned = nullptr;
   size_t h_pinned_cap = 0;
+  // asynchronous positions_host() mirror: device staging (visible order, reference layout), pinned host
+  // mirror, a copy stream and two events (see positions_async)
+  T* pos_stage = nullptr;
+  T* h_pos_mirror = nullptr;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_gather = nullptr, ev_copy = nullptr;
+  bool copy_pending = false;
+
+  // shared-block exchange (halo.cuh)
+  uint8_t* halo_flags_d = nullptr;
+  uint32_t *halo_list = nullptr, *halo_cta_counts = nullptr, *halo_n_shared = nullptr;
+  uint32_t* h_halo_n = nullptr;  // pinned
+  T* halo_packed = nullptr;
+  size_t halo_cap = 0;           // shared blocks the list / packed buffers hold
+  uint32_t halo_n = 0;           // shared blocks of the current exchange (host copy)
+  int halo_stage = 0;            // 0 idle, 1 flags out, 2 planned
 
   std::vector<void*> allocs;
   size_t device_bytes = 0;
   uint64_t launches = 0;
   Profiler prof;
   int sm_count = 148;
-  int p2g_ctas_per_sm = 1, g2p_ctas_per_sm = 1, bin_ctas = 0, sort_ctas = 0;
+  int p2g_ctas_per_sm = 1, g2p_ctas_per_sm = 1, fem_ctas_per_sm = 1, bin_ctas = 0, sort_ctas = 0;
   bool g2p_queue_ready = false;
+  bool forces_zero = true;      // forces[] is all zeros (fresh allocation, or g2p just wrote the zeros)
+  bool prologue_done = false;   // the binning kernel already rolled the touched list for the coming P2G
 
   // ---------------------------------------------------------------------------------------------
   template <typename U>
@@ -187,8 +206,14 @@ struct State {
     k.n_blocks = 1u << (3 * (p.domain_bits - kBlockBits));
     k.boundary_cells = p.boundary_cells;
     k.gravity_axis = p.gravity_axis;
-    k.dx_inv = T(1) * T(1 << p.domain_bits);  // settings.h:50,57
-    k.dx = T(1) / k.dx_inv;
+    if (p.dx < 0) throw std::invalid_argument("dx must be >= 0");
+    if (p.dx > 0) {                           // cell size given: domain = [0, dx * 2^bits]^3
+      k.dx = T(p.dx);
+      k.dx_inv = T(1) / k.dx;
+    } else {
+      k.dx_inv = T(1) * T(1 << p.domain_bits);  // settings.h:50,57
+      k.dx = T(1) / k.dx_inv;
+    }
     k.d_inv = T(4) * k.dx_inv * k.dx_inv;     // settings.h:59
     const T E = T(p.youngs), nu = T(p.poisson);
     k.mu = E / (T(2) * (T(1) + nu));          // settings.h:114-115
@@ -211,6 +236,19 @@ struct State {
     if (h_pinned) cudaFreeHost(h_pinned);
     if (h_csc) cudaFreeHost(h_csc);
     if (h_stage) cudaFreeHost(h_stage);
+    if (h_halo_n) cudaFreeHost(h_halo_n);
+    h_halo_n = nullptr;
+    if (copy_stream) {
+      cudaStreamSynchronize(copy_stream);
+      cudaStreamDestroy(copy_stream);
+      copy_stream = nullptr;
+    }
+    if (h_pos_mirror) cudaFreeHost(h_pos_mirror);
+    h_pos_mirror = nullptr;
+    if (ev_gather) cudaEventDestroy(ev_gather);
+    if (ev_copy) cudaEventDestroy(ev_copy);
+    ev_gather = ev_copy = nullptr;
+    copy_pending = false;
     io_buf = nullptr;
     h_pinned = nullptr;
     h_csc = nullptr;
@@ -312,6 +350,8 @@ struct State {
     if (p2g_ctas_per_sm < 1) throw CudaError(cudaErrorLaunchOutOfResources, "p2g_tile_kernel does not fit on an SM");
     GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g2p_ctas_per_sm, g2p_kernel<T>, kG2PWarps * 32, 0));
     g2p_ctas_per_sm = std::max(1, std::min(g2p_ctas_per_sm, 8));
+    GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fem_ctas_per_sm, fem_kernel<T>, kFemThreads, 0));
+    fem_ctas_per_sm = std::max(1, fem_ctas_per_sm);
     GMPM_CUDA(cudaStreamSynchronize(stream));  // host staging vectors go out of scope
     finalized = true;
     keys_valid = bin_valid = false;
@@ -337,8 +377,9 @@ struct State {
   const uint32_t* order() const { return svals[sres]; }
   const uint32_t* sorted_keys() const { return skeys[sres]; }
 
-  void ensure_binning() {
+  void ensure_binning(bool for_p2g = false) {
     ensure_keys();
+    prologue_done = false;
     if (bin_valid || N == 0) return;
     // one cooperative launch: stable sort of (key, slot) on all key bits + block ranges + work records
     ++bin_epoch;
@@ -354,6 +395,8 @@ struct State {
     a.pb_tile = pb_tile;
     a.pb_work = pb_work;
     a.ctr = ctr;
+    a.roll_touched = for_p2g ? 1 : 0;
+    prologue_done = for_p2g;
     sres = (a.sort.n_passes - 1) & 1;
     if (bin_ctas == 0) bin_ctas = sort_grid_ctas(bin_particles_kernel, sm_count, a.sort.n_tiles);
     void* kargs[] = {&a};
@@ -421,13 +464,16 @@ struct State {
     require_finalized();
     if (N == 0) return;
     ensure_keys();
-    note("memset");
-    GMPM_CUDA(cudaMemsetAsync(forces, 0, sizeof(T) * 3 * N, stream));
+    if (!forces_zero) {
+      note("memset");
+      GMPM_CUDA(cudaMemsetAsync(forces, 0, sizeof(T) * 3 * N, stream));
+    }
+    forces_zero = n_faces == 0;
     if (n_faces) {
       launch("fem");
-      fem_kernel<T><<<blocks_for(n_faces, 128), 128, 0, stream>>>((uint32_t)n_faces, (uint32_t)N, tri, slot_of_pid,
-                                                                  vol[cur], C[cur], Dm_inv, pos[cur], vel[cur], Fd,
-                                                                  forces, taus, key, dt, k);
+      const uint32_t ctas = std::min<uint32_t>(blocks_for(n_faces, kFemThreads), persistent_ctas(fem_ctas_per_sm));
+      fem_kernel<T><<<ctas, kFemThreads, 0, stream>>>((uint32_t)n_faces, (uint32_t)N, tri, slot_of_pid, vol[cur], C[cur],
+                                                      Dm_inv, pos[cur], vel[cur], Fd, forces, taus, key, dt, k);
       GMPM_CUDA(cudaGetLastError());
       bin_valid = false;  // face particles moved to their centroids
     }
@@ -440,11 +486,14 @@ struct State {
   void p2g(T dt) {
     require_finalized();
     if (N == 0) return;
-    ensure_binning();
+    ensure_binning(true);
     ++p2g_epoch;
     tl_cur ^= 1;
-    launch("p2g_prologue");
-    p2g_prologue_kernel<<<1, 1, 0, stream>>>(ctr);
+    if (!prologue_done) {  // binning was still valid: roll the touched list in a launch of its own
+      launch("p2g_prologue");
+      p2g_prologue_kernel<<<1, 1, 0, stream>>>(ctr);
+    }
+    prologue_done = false;
     launch("p2g_tile");
     p2g_tile_kernel<T><<<persistent_ctas(p2g_ctas_per_sm), kP2GThreads, sizeof(P2GSmem<T>), stream>>>(
         (uint32_t)N, (uint32_t)n_faces, order(), sorted_keys(), pb_work, (uint32_t)work_cap, pos[cur], vel[cur],
@@ -498,12 +547,81 @@ struct State {
     const int nx = cur ^ 1;
     g2p_kernel<T><<<persistent_ctas(g2p_ctas_per_sm), kG2PWarps * 32, 0, stream>>>(
         (uint32_t)N, order(), pb_work, (uint32_t)work_cap, g_vel, pos[cur], vol[cur], pid[cur], pos[nx], vel[nx], C[nx],
-        vol[nx], pid[nx], slot_of_pid, key, ctr, dt, k);
+        vol[nx], pid[nx], slot_of_pid, key, forces, ctr, dt, k);
     GMPM_CUDA(cudaGetLastError());
+    forces_zero = true;
     cur = nx;
     keys_valid = true;   // g2p wrote the key of every new slot
     bin_valid = false;
     fem_valid = false;
+  }
+
+  // ---- multi-GPU shared-block exchange (halo.cuh); call order: flags -> [all-reduce] -> plan ->
+  // [all-reduce] -> unpack, between ParticleToGrid and UpdateGrid ------------------------------
+  void halo_reserve(size_t blocks) {
+    if (blocks <= halo_cap) return;
+    size_t cap = std::max<size_t>(1024, halo_cap * 2);
+    while (cap < blocks) cap *= 2;
+    cap = std::min<size_t>(cap, k.n_blocks);
+    GMPM_CUDA(cudaStreamSynchronize(stream));
+    if (halo_list) dfree(halo_list);
+    if (halo_packed) dfree(halo_packed);
+    halo_list = dalloc<uint32_t>(cap, false);
+    halo_packed = dalloc<T>(cap * 256, false);
+    halo_cap = cap;
+  }
+  uint8_t* halo_flags() {
+    require_finalized();
+    if (stage != GridStage::kTiles && stage != GridStage::kMomentum)
+      throw std::invalid_argument("halo exchange must follow ParticleToGrid and precede UpdateGrid");
+    assemble_momentum();
+    if (!halo_flags_d) {
+      halo_flags_d = dalloc<uint8_t>(k.n_blocks);
+      halo_cta_counts = dalloc<uint32_t>((k.n_blocks + kHaloBlocksPerCta - 1) / kHaloBlocksPerCta);
+      halo_n_shared = dalloc<uint32_t>(1);
+      GMPM_CUDA(cudaHostAlloc((void**)&h_halo_n, sizeof(uint32_t), cudaHostAllocDefault));
+      halo_reserve(1024);
+    }
+    launch("halo_flags");
+    halo_flags_kernel<<<blocks_for(k.n_blocks), kThreads, 0, stream>>>(k.n_blocks, touched_epoch, p2g_epoch, halo_flags_d);
+    GMPM_CUDA(cudaGetLastError());
+    halo_stage = 1;
+    return halo_flags_d;
+  }
+  // flags now hold the sum over ranks.  Returns the number of shared blocks (one blocking 4-byte read).
+  uint32_t halo_plan() {
+    require_finalized();
+    if (halo_stage != 1) throw std::invalid_argument("halo_plan without halo_flags");
+    const uint32_t ctas = (k.n_blocks + kHaloBlocksPerCta - 1) / kHaloBlocksPerCta;
+    for (;;) {
+      launch("halo_count");
+      halo_count_kernel<<<ctas, kHaloThreads, 0, stream>>>(k.n_blocks, halo_flags_d, halo_cta_counts);
+      launch("halo_compact");
+      halo_compact_kernel<<<ctas, kHaloThreads, 0, stream>>>(k.n_blocks, halo_flags_d, halo_cta_counts, halo_list,
+                                                            (uint32_t)halo_cap, halo_n_shared);
+      launch("halo_pack");
+      halo_pack_kernel<T, false><<<persistent_ctas(8), kHaloThreads, 0, stream>>>(
+          halo_n_shared, (uint32_t)halo_cap, halo_list, touched_epoch, p2g_epoch, g_mass, g_vel, halo_packed);
+      GMPM_CUDA(cudaGetLastError());
+      GMPM_CUDA(cudaMemcpyAsync(h_halo_n, halo_n_shared, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+      GMPM_CUDA(cudaStreamSynchronize(stream));
+      halo_n = *h_halo_n;
+      if (halo_n <= halo_cap) break;
+      halo_reserve(halo_n);  // grow and redo (rare: the shared set grows slowly)
+    }
+    halo_stage = 2;
+    return halo_n;
+  }
+  void halo_unpack() {
+    require_finalized();
+    if (halo_stage != 2) throw std::invalid_argument("halo_unpack without halo_plan");
+    if (halo_n) {
+      launch("halo_unpack");
+      halo_pack_kernel<T, true><<<persistent_ctas(8), kHaloThreads, 0, stream>>>(
+          halo_n_shared, (uint32_t)halo_cap, halo_list, touched_epoch, p2g_epoch, g_mass, g_vel, halo_packed);
+      GMPM_CUDA(cudaGetLastError());
+    }
+    halo_stage = 0;
   }
 
   cudaEvent_t timers[16]{};
@@ -566,6 +684,42 @@ struct State {
     GMPM_CUDA(cudaGetLastError());
     to_host(out, buf, sizeof(T) * 3 * N);
     if (prof.on) prof.flush(stream);
+  }
+
+  // Asynchronous form of SyncParticleStateToCpu.  The driver needs positions_host() only when it builds
+  // the contact pairs, four solver calls later (deformable_driver.h:243 vs :247), so the PCIe copy can
+  // run under FEM / P2G / UpdateGrid: the gather to the reference's layout and visible order runs in
+  // order on the compute stream (positions as of THIS call), the D2H runs on a copy stream into a
+  // library-owned pinned mirror, and wait_positions() blocks on that copy alone.
+  void positions_async() {
+    require_finalized();
+    if (N == 0) return;
+    if (!copy_stream) {
+      GMPM_CUDA(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
+      GMPM_CUDA(cudaEventCreateWithFlags(&ev_gather, cudaEventDisableTiming));
+      GMPM_CUDA(cudaEventCreateWithFlags(&ev_copy, cudaEventDisableTiming));
+      pos_stage = dalloc<T>(3 * N, false);
+      GMPM_CUDA(cudaHostAlloc((void**)&h_pos_mirror, sizeof(T) * 3 * N, cudaHostAllocDefault));
+    }
+    if (copy_pending) GMPM_CUDA(cudaStreamWaitEvent(stream, ev_copy, 0));  // staging buffer still being read
+    launch("gather_positions");
+    gather_particle_field_kernel<T><<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, 3, pos[cur],
+                                                                           pid_of_vis[vis_cur], slot_of_pid, pos_stage);
+    GMPM_CUDA(cudaGetLastError());
+    GMPM_CUDA(cudaEventRecord(ev_gather, stream));
+    GMPM_CUDA(cudaStreamWaitEvent(copy_stream, ev_gather, 0));
+    GMPM_CUDA(cudaMemcpyAsync(h_pos_mirror, pos_stage, sizeof(T) * 3 * N, cudaMemcpyDeviceToHost, copy_stream));
+    GMPM_CUDA(cudaEventRecord(ev_copy, copy_stream));
+    copy_pending = true;
+  }
+  // Blocks until the last positions_async() copy has landed; returns the pinned mirror (3N, visible order).
+  const T* wait_positions() {
+    require_finalized();
+    if (copy_pending) {
+      GMPM_CUDA(cudaEventSynchronize(ev_copy));
+      copy_pending = false;
+    }
+    return h_pos_mirror;
   }
 
   // GpuMpmState<T>::DumpCpuState (cuda_mpm_model.cu:245-265)

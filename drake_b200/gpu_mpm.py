@@ -146,6 +146,7 @@ class GpuMpmState:
         check(self._f("create")(C.byref(self.params), C.byref(h)))
         self._h = h
         self._positions_host = np.zeros((0, 3), self.dtype)
+        self._positions_pending = False
         self._external_forces_host = ExternalSpatialForce(self.dtype)
 
     def _f(self, name):
@@ -180,8 +181,40 @@ class GpuMpmState:
     def device_bytes(self):
         return self._f("device_bytes")(self._h)
 
+    # --- multi-GPU shared-block exchange (gmpm_c.h, "multi-GPU extension"); driven by drake_b200.slab
+    def stream_handle(self):
+        p = C.c_void_p()
+        check(self._f("stream")(self._h, C.byref(p)))
+        return p.value or 0
+
+    def halo_flags(self):
+        """-> (device pointer of uint8[n_blocks], n_blocks)"""
+        p, n = C.c_void_p(), C.c_size_t()
+        check(self._f("halo_flags")(self._h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def halo_plan(self):
+        """-> (n_shared, device pointer of T[n_shared][4][64])"""
+        n, p = C.c_uint32(), C.c_void_p()
+        check(self._f("halo_plan")(self._h, C.byref(n), C.byref(p)))
+        return n.value, p.value
+
+    def halo_unpack(self):
+        check(self._f("halo_unpack")(self._h))
+
     # --- host mirrors
     def positions_host(self):
+        """cuda_mpm_model.cuh:116-117.  Waits for the snapshot SyncParticleStateToCpu started and returns
+        a read-only (N, 3) view of the library's pinned mirror (or the caller's array of a blocking sync)."""
+        if self._positions_pending:
+            p = C.c_void_p()
+            check(self._f("positions_host")(self._h, C.byref(p)))
+            n = self.n_particles()
+            ctype = C.c_double if self.dtype == np.float64 else C.c_float
+            arr = np.ctypeslib.as_array(C.cast(p, C.POINTER(ctype)), shape=(n, 3)) if p.value and n else np.zeros((0, 3), self.dtype)
+            arr.flags.writeable = False
+            self._positions_host = arr
+            self._positions_pending = False
         return self._positions_host
 
     def external_forces_host(self):
@@ -294,15 +327,17 @@ class GpuMpmSolver:
             check(state._f("sync")(state._h))
 
     def SyncParticleStateToCpu(self, state, out=None):
-        """positions_host() <- current positions (3N, visible order).  `out` may be a caller-owned
-        (e.g. pinned) array of shape (N, 3)."""
-        n = state.n_particles()
+        """cuda_mpm_solver.cu:187-191: positions_host() <- current positions (3N, visible order).
+        Without `out` the snapshot is only STARTED here (device gather in stream order, D2H on a copy
+        stream into the library's pinned mirror) and `state.positions_host()` waits for it -- the driver
+        reads it four solver calls later (deformable_driver.h:243 vs :120-194).  With a caller-owned
+        `out` array of shape (N, 3) the call blocks and fills it, like the reference."""
         if out is None:
-            if state._positions_host.shape[0] != n:
-                state._positions_host = np.zeros((n, 3), state.dtype)
-            out = state._positions_host
-        else:
-            state._positions_host = out
+            check(state._f("sync_particle_state_to_cpu_async")(state._h))
+            state._positions_pending = True
+            return None
+        state._positions_pending = False
+        state._positions_host = out
         check(state._f("sync_particle_state_to_cpu")(state._h, C.c_void_p(out.ctypes.data)))
         return out
 

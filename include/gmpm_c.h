@@ -56,6 +56,9 @@ typedef struct gmpm_params {
   double sdf_friction; /* settings.h:109-111 0.3                                                    */
   double gravity;      /* settings.h:120-122 -9.8                                                   */
   double epsv;         /* settings.h:124-126 1e-3                                                   */
+  double dx;           /* settings.h:57 G_DX.  0 = 1 / 2^domain_bits (unit cube, the reference).  A positive */
+                       /* value decouples the cell size from the cell count: the domain is the cube        */
+                       /* [0, dx * 2^domain_bits]^3 (multi-GPU scenes keep dx = 1/128 on a 256^3 grid)     */
 } gmpm_params;
 
 /* Result of one UpdateContact call (the reference prints these, cuda_mpm_solver.cu:577-582). */
@@ -102,6 +105,13 @@ int gmpm_device_sync(void);
   int gmpm_sync_##SUF(gmpm_state_##SUF* s);                                                         \
   /* GpuMpmSolver<T>::SyncParticleStateToCpu, cuda_mpm_solver.cu:187-191: positions_host(), 3N */  \
   int gmpm_sync_particle_state_to_cpu_##SUF(gmpm_state_##SUF* s, T* positions_host);                \
+  /* Same snapshot, not blocking: positions as of THIS call are gathered in stream order and copied */\
+  /* on a copy stream into a library-owned PINNED mirror while later solver calls run (the driver   */\
+  /* reads positions_host() only when it builds the contact pairs, deformable_driver.h:243 vs :247).*/\
+  int gmpm_sync_particle_state_to_cpu_async_##SUF(gmpm_state_##SUF* s);                             \
+  /* positions_host(): waits for the last async snapshot; *out = pinned mirror, 3N scalars, visible */\
+  /* order, valid until the next snapshot or destroy (NULL before the first snapshot).              */\
+  int gmpm_positions_host_##SUF(gmpm_state_##SUF* s, const T** out);                                \
   /* GpuMpmSolver<T>::CopyContactPairs, cuda_mpm_solver.cu:194-212 (+ ReallocateContacts) */        \
   int gmpm_copy_contact_pairs_##SUF(gmpm_state_##SUF* s, size_t n, const uint32_t* mpm_id,          \
                                     const uint32_t* rigid_id, const T* dist, const T* normal,       \
@@ -131,10 +141,27 @@ int gmpm_device_sync(void);
   /* contact_vel contact_vel0 contact_sort_keys.  *bytes_written <- size; fails if cap too small. */\
   int gmpm_read_##SUF(gmpm_state_##SUF* s, const char* name, void* out, size_t cap_bytes,           \
                       size_t* bytes_written);                                                       \
+  /* ---- multi-GPU extension (not in the reference: settings.h:40 G_DEVICE_COUNT = 1 is unused). ---- */\
+  /* One process and one state per GPU; every rank holds whole cloth meshes and addresses the same    */\
+  /* grid.  Between ParticleToGrid and UpdateGrid the ranks sum the grid blocks more than one of them */\
+  /* touched (Multi-GPU).  The library does the device side; the host runs the two        */\
+  /* all-reduces (NCCL SUM) on the state's stream (gmpm_stream) between the calls:                    */\
+  /*   halo_flags : *flags_dev = uint8[*n_blocks] on the device, 1 where this rank's P2G touched the  */\
+  /*                block              -> host all-reduces flags_dev in place (ncclUint8, sum)        */\
+  /*   halo_plan  : shared blocks = flags > 1 in ascending block id (identical on every rank);        */\
+  /*                *packed_dev = T[*n_shared][4][64] = this rank's mass and momentum of them (zeros  */\
+  /*                where it has none); blocks on one 4-byte read-back                                */\
+  /*                                   -> host all-reduces packed_dev[0 : *n_shared * 256] (sum)      */\
+  /*   halo_unpack: the sums are written back into the blocks this rank touches; UpdateGrid follows.  */\
+  int gmpm_halo_flags_##SUF(gmpm_state_##SUF* s, void** flags_dev, size_t* n_blocks);               \
+  int gmpm_halo_plan_##SUF(gmpm_state_##SUF* s, uint32_t* n_shared, void** packed_dev);             \
+  int gmpm_halo_unpack_##SUF(gmpm_state_##SUF* s);                                                  \
+  /* The cudaStream_t all work of this state is issued on (for stream-ordered collectives). */      \
+  int gmpm_stream_##SUF(gmpm_state_##SUF* s, void** cuda_stream);                                   \
   /* One substep of the driver loop without contact (deformable_driver.h:240-260 /                */\
   /* cuda_mpm_test.cc:66-72): RebuildMapping(sort) CalcFemStateAndForce ParticleToGrid            */\
   /* UpdateGrid(mpm_bc) GridToParticle, n_substeps times; sort_every = k sorts at substeps        */\
-  /* 0,k,2k.. (0 = never).  Same results as the individual calls; replayed from a CUDA graph.     */\
+  /* 0,k,2k.. (0 = never).  Same results as the individual calls (one ABI crossing).              */\
   int gmpm_run_substeps_##SUF(gmpm_state_##SUF* s, int n_substeps, T dt, int mpm_bc,                \
                               int sort_every);                                                      \
   /* Instrumentation: number of kernels launched so far by this state, and per-kernel device time.*/\

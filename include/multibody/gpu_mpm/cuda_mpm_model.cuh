@@ -32,6 +32,29 @@ struct ExternalSpatialForce {
   }
 };
 
+// positions_host() of the reference is a std::vector<Vec3<T>> filled by a blocking cudaMemcpy
+// (cuda_mpm_model.cuh:116-117, cuda_mpm_solver.cu:187-191).  Here it is a read-only view of a pinned
+// mirror owned by the library: SyncParticleStateToCpu only *starts* the snapshot (device gather in
+// stream order + D2H on a copy stream) and the first access to positions_host() waits for it, so the
+// PCIe transfer runs under the solver calls the driver issues in between
+// (deformable_driver.h:243 -> :120-194).  Same members as the driver uses: operator[], size(), data().
+template <typename T>
+class HostPositions {
+ public:
+  HostPositions() = default;
+  HostPositions(const Vec3<T>* p, size_t n) : p_(p), n_(n) {}
+  const Vec3<T>& operator[](size_t i) const { return p_[i]; }
+  const Vec3<T>* data() const { return p_; }
+  const Vec3<T>* begin() const { return p_; }
+  const Vec3<T>* end() const { return p_ + n_; }
+  size_t size() const { return n_; }
+  bool empty() const { return n_ == 0; }
+
+ private:
+  const Vec3<T>* p_ = nullptr;
+  size_t n_ = 0;
+};
+
 namespace internal {
 inline void Check(int status, const char* what) {
   if (status != GMPM_OK) throw std::runtime_error(std::string(what) + ": " + gmpm_last_error());
@@ -52,6 +75,8 @@ template <typename T> struct Abi;
     static constexpr auto g2p = gmpm_g2p_##SUF;                                                      \
     static constexpr auto sync = gmpm_sync_##SUF;                                                    \
     static constexpr auto sync_particle_state_to_cpu = gmpm_sync_particle_state_to_cpu_##SUF;        \
+    static constexpr auto sync_particle_state_to_cpu_async = gmpm_sync_particle_state_to_cpu_async_##SUF; \
+    static constexpr auto positions_host = gmpm_positions_host_##SUF;                                \
     static constexpr auto copy_contact_pairs = gmpm_copy_contact_pairs_##SUF;                        \
     static constexpr auto update_contact = gmpm_update_contact_##SUF;                                \
     static constexpr auto reallocate_external_bodies = gmpm_reallocate_external_bodies_##SUF;        \
@@ -90,8 +115,12 @@ struct GpuMpmState {
   }
 
   // host mirrors (cuda_mpm_model.cuh:117-118, 141-143)
-  std::vector<Vec3<T>>& positions_host() { return host_->positions; }
-  const std::vector<Vec3<T>>& positions_host() const { return host_->positions; }
+  HostPositions<T> positions_host() const {
+    if (!h_) return HostPositions<T>();
+    const T* p = nullptr;
+    internal::Check(Abi::positions_host(h_.get(), &p), "positions_host");  // waits for the pending snapshot
+    return HostPositions<T>(reinterpret_cast<const Vec3<T>*>(p), p ? n_particles() : 0);
+  }
   ExternalSpatialForce<T>& external_forces_host() { return host_->external_forces; }
   const ExternalSpatialForce<T>& external_forces_host() const { return host_->external_forces; }
 
@@ -159,7 +188,6 @@ struct GpuMpmState {
 
  private:
   struct Host {
-    std::vector<Vec3<T>> positions;
     ExternalSpatialForce<T> external_forces;
   };
   void Create(const gmpm_params* p) {

@@ -40,12 +40,11 @@ class GpuMpmSolver {
   void GpuSync() const { internal::Check(gmpm_device_sync(), "GpuSync"); }
   void GpuSync(GpuMpmState<T>* state) const { internal::Check(Abi::sync(state->raw()), "GpuSync"); }
 
-  // cuda_mpm_solver.cu:187-191: positions_host() <- current particle positions.
+  // cuda_mpm_solver.cu:187-191: positions_host() <- current particle positions.  The snapshot is taken
+  // in stream order now; the copy to the host overlaps the following solver calls and the first
+  // positions_host() access waits for it (cuda_mpm_model.cuh, HostPositions).
   void SyncParticleStateToCpu(GpuMpmState<T>* state) const {
-    auto& host = state->positions_host();
-    host.resize(state->n_particles());
-    internal::Check(Abi::sync_particle_state_to_cpu(state->raw(), reinterpret_cast<T*>(host.data())),
-                    "SyncParticleStateToCpu");
+    internal::Check(Abi::sync_particle_state_to_cpu_async(state->raw()), "SyncParticleStateToCpu");
   }
 
   // cuda_mpm_solver.cu:169-183: Wavefront OBJ of the cloth.

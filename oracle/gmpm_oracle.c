@@ -25,6 +25,7 @@ void ogmpm_default_params(ogmpm_params* p) {
   p->sdf_friction = 0.3;
   p->gravity = -9.8;
   p->epsv = 1e-3;
+  p->dx = 0.;
 }
 
 /* ref: cuda_mpm_kernels.cuh:296-304 */

@@ -52,6 +52,7 @@ typedef struct ogmpm_params {
   double sdf_friction;  /* settings.h:109-111 0.3                                 */
   double gravity;       /* settings.h:120-122 -9.8                                */
   double epsv;          /* settings.h:124-126 1e-3                                */
+  double dx;            /* settings.h:57 G_DX; 0 = 1/2^domain_bits (the reference) */
 } ogmpm_params;
 
 void ogmpm_default_params(ogmpm_params* p);

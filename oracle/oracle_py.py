@@ -31,6 +31,7 @@ class OracleParams(C.Structure):
         ("sdf_friction", C.c_double),
         ("gravity", C.c_double),
         ("epsv", C.c_double),
+        ("dx", C.c_double),
     ]
 
 
@@ -206,6 +207,16 @@ class OracleMpm:
             return np.zeros((0,), dt)
         buf = (C.c_char * (n * comp * dt.itemsize)).from_address(p)
         return np.frombuffer(buf, dtype=dt).copy()
+
+    def view(self, name):
+        """Writable numpy array ALIASING the oracle's buffer (valid until the next call that reallocates)."""
+        kind, dim, comp = _VIEWS[name]
+        n = {"N": self.n_particles, "F": self.n_faces, "cells": self._f("n_cells")(self.h),
+             "blocks": self._f("n_cells")(self.h) // 64, "Nc": self.n_contacts}[dim]
+        dt = {"T": self.dtype, "i": np.dtype(np.int32), "u": np.dtype(np.uint32)}[kind]
+        p = self._f("view")(self.h, name.encode())
+        buf = (C.c_char * (n * comp * dt.itemsize)).from_address(p)
+        return np.frombuffer(buf, dtype=dt)
 
     # --- GpuMpmSolver
     def RebuildMapping(self, sort):

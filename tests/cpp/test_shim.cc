@@ -78,7 +78,7 @@ int main(int argc, char** argv) {
     ogmpm_update_grid_f64(orc, -1);
     // CalcMpmContactPairs stand-in: analytic box [0.2,0.8]^2 x [0.2,0.3]
     MpmParticleContactPairs<T> pairs;
-    const auto& ph = state.positions_host();  // host mirrors are shared between the copies as well
+    const auto ph = state.positions_host();  // host mirrors are shared between the copies as well
     for (size_t i = 0; i < ph.size(); ++i) {
       const T d = ph[i][2] - T(0.3);
       if (d < 0 && ph[i][2] > T(0.2))

@@ -55,7 +55,8 @@ class Pair:
         self.orc.ReallocateExternelBodies(n_bodies)
 
     def pre_contact(self):
-        pos = self.sv.SyncParticleStateToCpu(self.st).copy()
+        self.sv.SyncParticleStateToCpu(self.st)
+        pos = self.st.positions_host().copy()
         self.sv.RebuildMapping(self.st, False)
         self.sv.CalcFemStateAndForce(self.st, DT)
         self.sv.ParticleToGrid(self.st, DT)

@@ -233,8 +233,32 @@ def test_fp64_100_steps_reference_smoke_scene():
     ovp, otri = orc.DumpCpuState()
     assert rel(vp, ovp) <= 1e-6 and np.array_equal(tri.reshape(-1), otri.reshape(-1))
     # SyncParticleStateToCpu == positions in visible order
-    ph = sv.SyncParticleStateToCpu(st)
+    sv.SyncParticleStateToCpu(st)
+    ph = st.positions_host()
     assert np.array_equal(ph.reshape(-1), st.read("positions"))
+
+
+def test_async_position_snapshot_is_taken_at_the_call():
+    """SyncParticleStateToCpu only starts the copy; positions_host() must still show the positions as of
+    the call (cuda_mpm_solver.cu:187-191 semantics), not those after the solver calls issued since."""
+    dtype = np.float64
+    st, sv, orc = make_pair(dtype, small_scene(dtype, res=30, warm=True))
+    for it in range(3):
+        before = st.read("positions").copy()
+        sv.SyncParticleStateToCpu(st)
+        sv.RebuildMapping(st, it == 1)
+        sv.CalcFemStateAndForce(st, 1e-3)   # moves the face particles
+        sv.ParticleToGrid(st, 1e-3)
+        sv.UpdateGrid(st, -1)
+        ph = st.positions_host()
+        assert ph.shape == (st.n_particles(), 3)
+        assert np.array_equal(ph.reshape(-1), before)
+        sv.GridToParticle(st, 1e-3)          # advects everything
+        assert np.array_equal(st.positions_host().reshape(-1), before)  # mirror unchanged until the next Sync
+    out = np.zeros((st.n_particles(), 3), dtype)
+    assert sv.SyncParticleStateToCpu(st, out) is out          # blocking form, caller-owned buffer
+    assert np.array_equal(out.reshape(-1), st.read("positions"))
+    assert st.positions_host() is out
 
 
 def test_fp64_warm_folding_100_steps():

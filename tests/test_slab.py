@@ -1,0 +1,239 @@
+"""Multi-GPU path: host-side protocol on CPU (gloo, world_size 2, oracle backend) and the device side
+on one GPU (two states in one process) and on two GPUs (NCCL).  The pinned property everywhere:
+a scene split over R ranks gives the same particles as the same scene on one rank."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+for p in (ROOT, os.path.join(ROOT, "oracle"), HERE):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import oracle_py as O  # noqa: E402
+from drake_b200 import scenes, slab  # noqa: E402
+from oracle_halo import OracleHaloBackend, oracle_substep  # noqa: E402
+
+DT = 1e-3
+
+
+def sheets_scene(dtype, n_sheets=4, res=24):
+    """Warm wavy sheets 2.7 dx apart: neighbouring sheets reach common grid blocks."""
+    rng = np.random.default_rng(11)
+    out = []
+    for s in range(n_sheets):
+        pos, vel, tri = scenes.cloth_sheet(res, 0.2, 0.33 + 0.011 * s, 0.35, 0.45 + 0.021 * s, dtype)
+        pos = pos.astype(np.float64)
+        pos[:, 2] += 0.006 * np.sin(9 * pos[:, 0]) * np.cos(7 * pos[:, 1])
+        out.append((pos.astype(dtype), rng.normal(0, 0.3, pos.shape).astype(dtype), tri))
+    return out
+
+
+def make_oracle(dtype, sheets, **params):
+    orc = O.OracleMpm(dtype, O.default_params(**params))
+    for pos, vel, tri in sheets:
+        orc.AddQRCloth(pos, vel, tri)
+    orc.Finalize()
+    return orc
+
+
+def vert_range(sheets, part):
+    n = [s[0].shape[0] for s in sheets]
+    lo = sum(n[:part.start])
+    return lo, lo + sum(n[part.start:part.stop])
+
+
+def free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_partition_meshes():
+    assert [list(r) for r in slab.partition_meshes(5, 2)] == [[0, 1, 2], [3, 4]]
+    assert [len(r) for r in slab.partition_meshes(34 * 8, 8)] == [34] * 8
+    assert [list(r) for r in slab.partition_meshes(2, 3)] == [[0], [1], []]
+
+
+def test_oracle_two_parts_in_process_match_single():
+    dtype = np.float64
+    sheets = sheets_scene(dtype)
+    full = make_oracle(dtype, sheets)
+    parts = slab.partition_meshes(len(sheets), 2)
+    orcs = [make_oracle(dtype, [sheets[i] for i in p]) for p in parts]
+    backs = [OracleHaloBackend(o) for o in orcs]
+    shared_seen = 0
+    for it in range(8):
+        full.substep(DT, -1, it == 3)
+        for o in orcs:
+            o.RebuildMapping(it == 3)
+            o.CalcFemStateAndForce(DT)
+            o.ParticleToGrid(DT)
+        shared_seen += slab.exchange_in_process(backs)
+        for o in orcs:
+            o.UpdateGrid(-1)
+            o.GridToParticle(DT)
+    assert shared_seen > 0
+    ref, _ = full.DumpCpuState()
+    for o, p in zip(orcs, parts):
+        lo, hi = vert_range(sheets, p)
+        got, _ = o.DumpCpuState()
+        assert np.max(np.abs(got - ref[lo:hi])) <= 1e-12 * np.max(np.abs(ref))
+
+
+def _gloo_worker(rank, world, port, ret):
+    import torch.distributed as dist
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    try:
+        dtype = np.float64
+        sheets = sheets_scene(dtype)
+        part = slab.partition_meshes(len(sheets), world)[rank]
+        orc = make_oracle(dtype, [sheets[i] for i in part])
+        ex = slab.SlabExchange(OracleHaloBackend(orc))
+        shared = 0
+        for it in range(8):
+            oracle_substep(orc, lambda: ex.exchange(), DT, -1, it == 3)
+            shared += ex.last_n_shared
+        got, _ = orc.DumpCpuState()
+        full = make_oracle(dtype, sheets)
+        for it in range(8):
+            full.substep(DT, -1, it == 3)
+        ref, _ = full.DumpCpuState()
+        lo, hi = vert_range(sheets, part)
+        ret[rank] = (float(np.max(np.abs(got - ref[lo:hi])) / np.max(np.abs(ref))), shared, ex.bytes_reduced)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_world2_oracle_backend_matches_single():
+    import torch.multiprocessing as mp
+    world, port = 2, free_port()
+    with mp.Manager() as m:
+        ret = m.dict()
+        mp.spawn(_gloo_worker, args=(world, port, ret), nprocs=world, join=True)
+        assert len(ret) == world
+        for r in range(world):
+            err, shared, nbytes = ret[r]
+            assert err <= 1e-12, (r, err)
+            assert shared > 0 and nbytes > 0
+        assert ret[0][1] == ret[1][1]          # every rank planned the same shared-block lists
+
+
+# ---- device side ----------------------------------------------------------------------------------
+def make_state(dtype, sheets, **params):
+    from drake_b200.gpu_mpm import GpuMpmState
+    st = GpuMpmState(dtype, **params)
+    for pos, vel, tri in sheets:
+        st.AddQRCloth(pos, vel, tri)
+    st.Finalize()
+    return st
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-10), (np.float32, 2e-4)])
+def test_two_states_one_gpu_match_single_state_and_oracle(dtype, tol):
+    from drake_b200.gpu_mpm import GpuMpmSolver
+    sheets = sheets_scene(dtype)
+    sv = GpuMpmSolver()
+    full = make_state(dtype, sheets)
+    orc = make_oracle(dtype, sheets)
+    parts = slab.partition_meshes(len(sheets), 2)
+    sts = [make_state(dtype, [sheets[i] for i in p]) for p in parts]
+    backs = [slab.GpuHaloBackend(s) for s in sts]
+    shared_seen = 0
+    for it in range(12):
+        sort = it == 5
+        slab.substep(sv, full, None, DT, -1, sort)
+        orc.substep(DT, -1, sort)
+        for s in sts:
+            sv.RebuildMapping(s, sort)
+            sv.CalcFemStateAndForce(s, DT)
+            sv.ParticleToGrid(s, DT)
+        for s in sts:
+            sv.GpuSync(s)                      # two streams, explicit sums in between: order them by hand
+        shared_seen += slab.exchange_in_process(backs)
+        for s in sts:
+            sv.GpuSync(s)
+            sv.UpdateGrid(s, -1)
+            sv.GridToParticle(s, DT)
+    assert shared_seen > 0
+    ref, _ = full.DumpCpuState()
+    oref, _ = orc.DumpCpuState()
+    scale = np.max(np.abs(oref))
+    assert np.max(np.abs(ref - oref)) <= tol * scale
+    for s, p in zip(sts, parts):
+        lo, hi = vert_range(sheets, p)
+        got, _ = s.DumpCpuState()
+        assert np.max(np.abs(got - ref[lo:hi])) <= tol * scale
+        assert np.max(np.abs(got - oref[lo:hi])) <= tol * scale
+
+
+@pytest.mark.gpu
+def test_halo_call_order_is_checked():
+    from drake_b200.gpu_mpm import GmpmError, GpuMpmSolver
+    st = make_state(np.float64, sheets_scene(np.float64, n_sheets=1))
+    sv = GpuMpmSolver()
+    with pytest.raises(GmpmError):
+        st.halo_flags()                        # no P2G yet
+    sv.RebuildMapping(st, False)
+    sv.CalcFemStateAndForce(st, DT)
+    sv.ParticleToGrid(st, DT)
+    with pytest.raises(GmpmError):
+        st.halo_unpack()                       # not planned
+    ptr, n = st.halo_flags()
+    assert ptr and n == 32768
+    n_shared, _ = st.halo_plan()               # alone: nothing is shared
+    assert n_shared == 0
+    st.halo_unpack()
+    sv.UpdateGrid(st, -1)
+    sv.GridToParticle(st, DT)
+
+
+def _nccl_worker(rank, world, port, ret):
+    import torch
+    import torch.distributed as dist
+    from drake_b200.gpu_mpm import GpuMpmSolver
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world,
+                            device_id=torch.device("cuda", rank))
+    try:
+        dtype = np.float64
+        sheets = sheets_scene(dtype, n_sheets=6, res=40)
+        part = slab.partition_meshes(len(sheets), world)[rank]
+        st = make_state(dtype, [sheets[i] for i in part], device=rank)
+        sv = GpuMpmSolver()
+        ex = slab.SlabExchange(slab.GpuHaloBackend(st))
+        shared = 0
+        for it in range(20):
+            slab.substep(sv, st, ex, DT, -1, it == 7)
+            shared += ex.last_n_shared
+        got, _ = st.DumpCpuState()
+        full = make_oracle(dtype, sheets)
+        for it in range(20):
+            full.substep(DT, -1, it == 7)
+        ref, _ = full.DumpCpuState()
+        lo, hi = vert_range(sheets, part)
+        ret[rank] = (float(np.max(np.abs(got - ref[lo:hi])) / np.max(np.abs(ref))), shared)
+        st.Destroy()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_nccl_world2_matches_single_process_oracle():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    world, port = 2, free_port()
+    with mp.Manager() as m:
+        ret = m.dict()
+        mp.spawn(_nccl_worker, args=(world, port, ret), nprocs=world, join=True)
+        for r in range(world):
+            err, shared = ret[r]
+            assert err <= 1e-9, (r, err)
+            assert shared > 0
