@@ -48,7 +48,7 @@ size_t State<T>::read(const char* name, void* out, size_t cap) {
     if (!n_faces) return 0;
     T* buf = static_cast<T*>(io(bytes));
     launch("transpose_planar");
-    transpose_planar_kernel<T><<<blocks_for(n_faces), kThreads, 0, stream>>>((uint32_t)n_faces, comps, src, buf);
+    transpose_planar_kernel<T><<<blocks_for(n_faces), kThreads, 0, stream>>>((uint32_t)n_faces, comps, src, fid, buf);
     GMPM_CUDA(cudaGetLastError());
     to_host(out, buf, bytes);
     return bytes;
@@ -102,7 +102,7 @@ size_t State<T>::read(const char* name, void* out, size_t cap) {
     if (!n_faces) return 0;
     int* buf = static_cast<int*>(io(bytes));
     launch("transpose_planar");
-    transpose_planar_kernel<int><<<blocks_for(n_faces), kThreads, 0, stream>>>((uint32_t)n_faces, 3, tri, buf);
+    transpose_planar_kernel<int><<<blocks_for(n_faces), kThreads, 0, stream>>>((uint32_t)n_faces, 3, tri, fid, buf);
     GMPM_CUDA(cudaGetLastError());
     to_host(out, buf, bytes);
     return bytes;

@@ -210,6 +210,10 @@ __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs 
 // ------------------------------------------------------------------------------------------------
 // Constitutive update (replaces calc_fem_state_and_force_kernel, :183-294).  One thread per face.
 // ------------------------------------------------------------------------------------------------
+// Face records (tri, F, Dm^-1) are kept in the SPATIAL order of their face particles (refreshed every
+// few dozen substeps, State::refresh_face_order): record j belongs to face fid[j], consecutive
+// records sit in consecutive particle slots and their vertices in nearby ones, so the slot-indexed
+// loads, stores and atomics of a warp fall into a few 128-byte lines instead of ~16 each.
 // Memory-latency design: the face record needs three dependent levels of loads (face -> particle ids ->
 // slots -> vertex state).  The kernel is persistent (grid-stride over faces) and software-pipelined:
 // the slot indices of the NEXT face of a thread are resolved while the current face is computed, and
@@ -226,7 +230,8 @@ struct FemIdx {
 
 template <typename T>
 __global__ void __launch_bounds__(kFemThreads, GMPM_FEM_MIN_CTAS)
-fem_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ tri, const int* __restrict__ slot_of_pid,
+fem_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ fid, const int* __restrict__ tri,
+           const int* __restrict__ slot_of_pid,
            const T* __restrict__ vol, const T* __restrict__ C, const T* __restrict__ Dm_inv, T* __restrict__ pos,
            T* __restrict__ vel, T* __restrict__ Fd, T* __restrict__ forces, T* __restrict__ taus,
            uint32_t* __restrict__ key, T dt, Consts<T> k) {
@@ -236,7 +241,7 @@ fem_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ tri, const int*
     FemIdx r{0, 0, 0, 0};
     if (ff < n_faces) {
       const int t0 = tri[ff], t1 = tri[n_faces + ff], t2 = tri[2 * n_faces + ff];
-      r.sf = slot_of_pid[ff];
+      r.sf = slot_of_pid[fid[ff]];
       r.s0 = slot_of_pid[t0];
       r.s1 = slot_of_pid[t1];
       r.s2 = slot_of_pid[t2];
@@ -967,11 +972,38 @@ __global__ void gather_taus_kernel(uint32_t N, uint32_t n_faces, const T* __rest
     for (int b = 0; b < 3; ++b)
       out[(size_t)v * 9 + a * 3 + b] = face ? taus[(size_t)a * N + s] * taus[(size_t)(3 + b) * N + s] : T(0);
 }
+// Face getters: record j of the (spatially ordered) face arrays holds face id fid[j].
 template <typename T>
-__global__ void transpose_planar_kernel(uint32_t n, int comps, const T* __restrict__ src, T* __restrict__ out) {
+__global__ void transpose_planar_kernel(uint32_t n, int comps, const T* __restrict__ src,
+                                        const int* __restrict__ fid, T* __restrict__ out) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  for (int c = 0; c < comps; ++c) out[(size_t)i * comps + c] = src[(size_t)c * n + i];
+  const size_t o = fid ? (size_t)fid[i] : (size_t)i;
+  for (int c = 0; c < comps; ++c) out[o * comps + c] = src[(size_t)c * n + i];
+}
+
+// Face-record refresh: sort key of record j = current slot of its face particle ...
+__global__ void face_slot_keys_kernel(uint32_t n_faces, const int* __restrict__ fid,
+                                      const int* __restrict__ slot_of_pid, uint32_t* __restrict__ keys) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n_faces) keys[j] = (uint32_t)slot_of_pid[fid[j]];
+}
+// ... and the gather of the records into that order (perm[j] = old record index).
+template <typename T>
+__global__ void permute_faces_kernel(uint32_t n_faces, const uint32_t* __restrict__ perm,
+                                     const int* __restrict__ fid_in, const int* __restrict__ tri_in,
+                                     const T* __restrict__ F_in, const T* __restrict__ Dm_in, int* __restrict__ fid_out,
+                                     int* __restrict__ tri_out, T* __restrict__ F_out, T* __restrict__ Dm_out) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n_faces) return;
+  const uint32_t s = perm[j];
+  fid_out[j] = fid_in[s];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) tri_out[(size_t)c * n_faces + j] = tri_in[(size_t)c * n_faces + s];
+#pragma unroll
+  for (int e = 0; e < 9; ++e) F_out[(size_t)e * n_faces + j] = F_in[(size_t)e * n_faces + s];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) Dm_out[(size_t)e * n_faces + j] = Dm_in[(size_t)e * n_faces + s];
 }
 template <typename T>
 __global__ void grid_vec_to_reference_kernel(uint32_t n_cells, const T* __restrict__ src, T* __restrict__ out) {

@@ -87,8 +87,11 @@ struct State {
   T *forces = nullptr, *taus = nullptr;
   int* slot_of_pid = nullptr;
   // faces
-  int* tri = nullptr;
-  T *Fd = nullptr, *Dm_inv = nullptr;
+  // face records, double buffered for the spatial re-ordering (fid[j] = face id of record j)
+  int *tri = nullptr, *fid = nullptr, *tri_alt = nullptr, *fid_alt = nullptr;
+  T *Fd = nullptr, *Dm_inv = nullptr, *Fd_alt = nullptr, *Dm_inv_alt = nullptr;
+  uint32_t* face_keys = nullptr;
+  uint64_t fem_calls = 0;
   // visible order (reference semantics: current_pids / index_mappings / sort_keys / sort_ids)
   int* pid_of_vis[2]{};
   int vis_cur = 0;
@@ -304,6 +307,12 @@ struct State {
     tri = dalloc<int>(3 * F);
     Fd = dalloc<T>(9 * F);
     Dm_inv = dalloc<T>(4 * F);
+    tri_alt = dalloc<int>(3 * F);
+    Fd_alt = dalloc<T>(9 * F);
+    Dm_inv_alt = dalloc<T>(4 * F);
+    fid = dalloc<int>(F);
+    fid_alt = dalloc<int>(F);
+    face_keys = dalloc<uint32_t>(F);
     sort_scratch = dalloc<uint32_t>(radix_sort_scratch_words(N));
     pb_start = dalloc<uint32_t>(k.n_blocks);
     pb_end = dalloc<uint32_t>(k.n_blocks);
@@ -337,6 +346,7 @@ struct State {
     GMPM_CUDA(cudaMemcpyAsync(tri, ht.data(), sizeof(int) * 3 * F, cudaMemcpyHostToDevice, stream));
     for (int* dst : {pid[0], slot_of_pid, pid_of_vis[0], vis_of_pid})
       GMPM_CUDA(cudaMemcpyAsync(dst, iota.data(), sizeof(int) * N, cudaMemcpyHostToDevice, stream));
+    if (F) GMPM_CUDA(cudaMemcpyAsync(fid, iota.data(), sizeof(int) * F, cudaMemcpyHostToDevice, stream));
     if (F) {
       launch("init_fem_state");
       init_fem_state_kernel<T><<<blocks_for(F), kThreads, 0, stream>>>((uint32_t)F, (uint32_t)N, tri, pos[0], vel[0],
@@ -410,10 +420,11 @@ struct State {
   // Stable sort of (in_keys, 0..n-1) on `bits` key bits into (ks, vs); returns the result buffer index.
   int sort_iota(const uint32_t* in_keys, uint32_t* ks[2], uint32_t* vs[2], uint32_t n, int bits) {
     SortArgs a = make_sort_args(in_keys, nullptr, ks, vs, n, bits, sort_scratch);
-    if (sort_ctas == 0) sort_ctas = sort_grid_ctas(radix_sort_kernel, sm_count, a.n_tiles);
+    if (sort_ctas == 0) sort_ctas = sort_grid_ctas(radix_sort_kernel, sm_count, 0xFFFFFFFFu);  // co-resident maximum
+    const int ctas = (int)std::min<uint32_t>((uint32_t)sort_ctas, std::max<uint32_t>(a.n_tiles, 64u));
     void* kargs[] = {&a};
     launch("radix_sort");
-    GMPM_CUDA(cudaLaunchCooperativeKernel((void*)radix_sort_kernel, dim3(sort_ctas), dim3(kSortThreads), kargs,
+    GMPM_CUDA(cudaLaunchCooperativeKernel((void*)radix_sort_kernel, dim3(ctas), dim3(kSortThreads), kargs,
                                           kSortSmemBytes, stream));
     return (a.n_passes - 1) & 1;
   }
@@ -459,6 +470,29 @@ struct State {
     vis_keys_valid = true;
   }
 
+  // Re-orders the face records by the current slot of their face particles (stable sort + gather).
+  // Purely a memory-locality measure: no observable result depends on the record order.
+  static constexpr int kFaceRefreshEvery = 32;
+  void refresh_face_order() {
+    const uint32_t F = (uint32_t)n_faces;
+    if (F < 2) return;
+    launch("face_slot_keys");
+    face_slot_keys_kernel<<<blocks_for(F), kThreads, 0, stream>>>(F, fid, slot_of_pid, face_keys);
+    GMPM_CUDA(cudaGetLastError());
+    int bits = 1;
+    while (((size_t)1 << bits) < N) ++bits;
+    const int r = sort_iota(face_keys, skeys, svals, F, bits);  // binning scratch: rebuilt after FEM anyway
+    bin_valid = false;
+    launch("permute_faces");
+    permute_faces_kernel<T><<<blocks_for(F), kThreads, 0, stream>>>(F, svals[r], fid, tri, Fd, Dm_inv, fid_alt, tri_alt,
+                                                                   Fd_alt, Dm_inv_alt);
+    GMPM_CUDA(cudaGetLastError());
+    std::swap(fid, fid_alt);
+    std::swap(tri, tri_alt);
+    std::swap(Fd, Fd_alt);
+    std::swap(Dm_inv, Dm_inv_alt);
+  }
+
   // ---- GpuMpmSolver<T>::CalcFemStateAndForce (cuda_mpm_solver.cu:73-84) -------------------------
   void calc_fem(T dt) {
     require_finalized();
@@ -470,9 +504,12 @@ struct State {
     }
     forces_zero = n_faces == 0;
     if (n_faces) {
+      // the particles are in spatial order from the first G2P on: refresh after it, then periodically
+      if (fem_calls % kFaceRefreshEvery == 1) refresh_face_order();
+      ++fem_calls;
       launch("fem");
       const uint32_t ctas = std::min<uint32_t>(blocks_for(n_faces, kFemThreads), persistent_ctas(fem_ctas_per_sm));
-      fem_kernel<T><<<ctas, kFemThreads, 0, stream>>>((uint32_t)n_faces, (uint32_t)N, tri, slot_of_pid, vol[cur], C[cur],
+      fem_kernel<T><<<ctas, kFemThreads, 0, stream>>>((uint32_t)n_faces, (uint32_t)N, fid, tri, slot_of_pid, vol[cur], C[cur],
                                                       Dm_inv, pos[cur], vel[cur], Fd, forces, taus, key, dt, k);
       GMPM_CUDA(cudaGetLastError());
       bin_valid = false;  // face particles moved to their centroids
