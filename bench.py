@@ -176,7 +176,7 @@ def run_reference_arm(args, rank, world):
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def reference_gpu(dtype, steps):
@@ -205,7 +205,20 @@ def reference_gpu(dtype, steps):
     return out
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the real stdout; everything else any library prints (NCCL's version
+    banner, torchrun notices) was diverted to stderr by main()."""
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (json.dumps(line) + "\n").encode())
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=2000)
@@ -396,7 +409,7 @@ def main():
                 line["reference_gpu"] = reference_gpu(dtype, 100)
             except Exception as e:  # checker library missing or failed: not fatal for the product line
                 line["reference_gpu"] = {"unavailable": repr(e)}
-        print(json.dumps(line), flush=True)
+        emit(line)
     st.Destroy()
     if dist is not None:
         dist.barrier()

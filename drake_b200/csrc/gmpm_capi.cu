@@ -206,10 +206,11 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
       *n_blocks = s->st.k.n_blocks;                                                                            \
     });                                                                                                        \
   }                                                                                                            \
-  int gmpm_halo_plan_##SUF(gmpm_state_##SUF* s, uint32_t* n_shared, void** packed_dev) {                       \
+  int gmpm_halo_plan_async_##SUF(gmpm_state_##SUF* s) { return guarded([&] { s->st.halo_plan_async(); }); }      \
+  int gmpm_halo_pack_##SUF(gmpm_state_##SUF* s, uint32_t* n_shared, void** packed_dev) {                       \
     return guarded([&] {                                                                                       \
       if (!n_shared || !packed_dev) throw std::invalid_argument("null out pointer");                           \
-      *n_shared = s->st.halo_plan();                                                                           \
+      *n_shared = s->st.halo_pack();                                                                           \
       *packed_dev = s->st.halo_packed;                                                                         \
     });                                                                                                        \
   }                                                                                                            \
@@ -218,6 +219,14 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
     return guarded([&] {                                                                                       \
       if (!cuda_stream) throw std::invalid_argument("null out pointer");                                       \
       *cuda_stream = (void*)s->st.stream;                                                                      \
+    });                                                                                                        \
+  }                                                                                                            \
+  int gmpm_halo_stream_##SUF(gmpm_state_##SUF* s, void** cuda_stream) {                                        \
+    return guarded([&] {                                                                                       \
+      if (!cuda_stream) throw std::invalid_argument("null out pointer");                                       \
+      s->st.require_finalized();                                                                               \
+      s->st.halo_init();                                                                                       \
+      *cuda_stream = (void*)s->st.halo_stream;                                                                 \
     });                                                                                                        \
   }                                                                                                            \
   int gmpm_run_substeps_##SUF(gmpm_state_##SUF* s, int n, T dt, int bc, int sort_every) {                      \

@@ -6,14 +6,21 @@
 // only coupling between ranks is through grid blocks that particles of more than one rank reach, so
 // the exchange step sits between ParticleToGrid and UpdateGrid:
 //
-//   1. halo_flags   : flags[b] = 1 if this rank's P2G touched grid block b          (uint8[n_blocks])
-//      -- host: all-reduce SUM of flags over the ranks (NCCL, on this state's stream) --
+//   plan (for the NEXT substep, off the critical path, on a side stream):
+//   1. halo_flags   : flags[b] = 1 if block b is within one block (3x3x3 neighbourhood) of a block this
+//                     rank's P2G touched NOW.  A particle moves less than a block per substep (CFL), so
+//                     the dilated set contains everything the rank can touch in the next substep.
+//      -- host: all-reduce SUM of flags over the ranks (NCCL) --
 //   2. halo_plan    : shared blocks = {b : flags[b] > 1}, listed in ascending block id by a
 //                     deterministic two-kernel compaction (every rank derives the SAME list from the
-//                     same reduced flags); packed[i][4][64] = this rank's mass and momentum of shared
-//                     block i (zeros if this rank does not touch it); n_shared goes to the host
+//                     same reduced flags); the count goes to a pinned host word, asynchronously
+//   exchange (this substep, between ParticleToGrid and UpdateGrid, with the list planned one substep ago):
+//   3. halo_pack    : packed[i][4][64] = this rank's mass and momentum of shared block i (zeros where
+//                     its P2G did not touch it); the host already knows the count -> no read-back
 //      -- host: all-reduce SUM of packed[0 : n_shared * 256] --
-//   3. halo_unpack  : the summed mass / momentum are written back into the blocks this rank touches.
+//   4. halo_unpack  : the summed mass / momentum are written back into the blocks this rank touched.
+//   The containment assumption is CHECKED on the device: a touched block outside the previous dilated
+//   set bumps an error counter that the next halo_pack turns into an error.
 //
 // UpdateGrid then runs on each rank's own touched list: shared blocks are updated redundantly from
 // identical sums, so all owners see bit-identical grid velocities, and G2P stays local.  No particle
@@ -26,10 +33,20 @@ namespace gmpm {
 constexpr int kHaloThreads = 256;
 constexpr int kHaloBlocksPerCta = 1024;  // grid blocks scanned by one CTA (4 per thread)
 
-__global__ void halo_flags_kernel(uint32_t n_blocks, const uint32_t* __restrict__ touched_epoch, uint32_t epoch,
-                                  uint8_t* __restrict__ flags) {
-  const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b < n_blocks) flags[b] = touched_epoch[b] == epoch ? 1 : 0;
+// One thread per (touched block, neighbour): flags[neighbour] = 1 (flags were zeroed).  The centre thread
+// also checks the block against the previous dilated set `own_prev` (containment / CFL check).
+__global__ void halo_flags_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __restrict__ ctr,
+                                  uint32_t blocks_per_axis, const uint8_t* __restrict__ own_prev,
+                                  uint8_t* __restrict__ flags, uint32_t* __restrict__ err) {
+  const uint32_t n = ctr->n_touched * 27u;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t g = touched_list[i / 27u], d = i % 27u;
+    uint32_t bx, by, bz;
+    block_coords(g, bx, by, bz);
+    const uint32_t nx = bx + d / 9u - 1u, ny = by + (d / 3u) % 3u - 1u, nz = bz + d % 3u - 1u;  // wraps below 0
+    if (nx < blocks_per_axis && ny < blocks_per_axis && nz < blocks_per_axis) flags[morton3(nx, ny, nz)] = 1;
+    if (d == 13u && own_prev && own_prev[g] == 0) atomicAdd(err, 1u);
+  }
 }
 
 __device__ __forceinline__ uint32_t halo_shared_mask(const uint8_t* __restrict__ flags, uint32_t n_blocks,
@@ -95,10 +112,8 @@ halo_compact_kernel(uint32_t n_blocks, const uint8_t* __restrict__ flags, const 
 // packed[i][c][l], c = 0: mass, 1..3: momentum.  One CTA-quarter (64 threads) per (block, channel).
 template <typename T, bool UNPACK>
 __global__ void __launch_bounds__(kHaloThreads)
-halo_pack_kernel(const uint32_t* __restrict__ n_shared_p, uint32_t list_cap, const uint32_t* __restrict__ list,
-                 const uint32_t* __restrict__ touched_epoch, uint32_t epoch, T* __restrict__ g_mass,
-                 T* __restrict__ g_vel, T* __restrict__ packed) {
-  const uint32_t n = min(*n_shared_p, list_cap);
+halo_pack_kernel(uint32_t n, const uint32_t* __restrict__ list, const uint32_t* __restrict__ touched_epoch,
+                 uint32_t epoch, T* __restrict__ g_mass, T* __restrict__ g_vel, T* __restrict__ packed) {
   const uint32_t c = threadIdx.x >> 6, l = threadIdx.x & 63u;
   for (uint32_t i = blockIdx.x; i < n; i += gridDim.x) {
     const uint32_t g = list[i];

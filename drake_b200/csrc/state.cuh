@@ -149,13 +149,16 @@ struct State {
   bool copy_pending = false;
 
   // shared-block exchange (halo.cuh)
-  uint8_t* halo_flags_d = nullptr;
-  uint32_t *halo_list = nullptr, *halo_cta_counts = nullptr, *halo_n_shared = nullptr;
-  uint32_t* h_halo_n = nullptr;  // pinned
+  uint8_t *halo_flags_d = nullptr, *halo_own = nullptr;
+  uint32_t *halo_list[2]{}, *halo_cta_counts = nullptr, *halo_dev_words = nullptr;  // [0..1] counts, [2] error
+  uint32_t* h_halo_words = nullptr;  // pinned mirror of halo_dev_words (per plan slot: count, error)
   T* halo_packed = nullptr;
-  size_t halo_cap = 0;           // shared blocks the list / packed buffers hold
-  uint32_t halo_n = 0;           // shared blocks of the current exchange (host copy)
-  int halo_stage = 0;            // 0 idle, 1 flags out, 2 planned
+  size_t halo_cap = 0;            // shared blocks the lists / packed buffer hold
+  uint32_t halo_n = 0;            // shared blocks of the current exchange
+  int halo_cur = 0;               // list used by the current exchange; the next plan goes to halo_cur ^ 1
+  bool halo_planned = false, halo_flags_out = false, halo_own_valid = false, halo_packed_out = false;
+  cudaStream_t halo_stream = nullptr;
+  cudaEvent_t ev_halo_flags = nullptr, ev_halo_plan = nullptr;
 
   std::vector<void*> allocs;
   size_t device_bytes = 0;
@@ -239,8 +242,16 @@ struct State {
     if (h_pinned) cudaFreeHost(h_pinned);
     if (h_csc) cudaFreeHost(h_csc);
     if (h_stage) cudaFreeHost(h_stage);
-    if (h_halo_n) cudaFreeHost(h_halo_n);
-    h_halo_n = nullptr;
+    if (halo_stream) {
+      cudaStreamSynchronize(halo_stream);
+      cudaStreamDestroy(halo_stream);
+      halo_stream = nullptr;
+    }
+    if (h_halo_words) cudaFreeHost(h_halo_words);
+    h_halo_words = nullptr;
+    if (ev_halo_flags) cudaEventDestroy(ev_halo_flags);
+    if (ev_halo_plan) cudaEventDestroy(ev_halo_plan);
+    ev_halo_flags = ev_halo_plan = nullptr;
     if (copy_stream) {
       cudaStreamSynchronize(copy_stream);
       cudaStreamDestroy(copy_stream);
@@ -593,72 +604,135 @@ struct State {
     fem_valid = false;
   }
 
-  // ---- multi-GPU shared-block exchange (halo.cuh); call order: flags -> [all-reduce] -> plan ->
-  // [all-reduce] -> unpack, between ParticleToGrid and UpdateGrid ------------------------------
+  // ---- multi-GPU shared-block exchange (halo.cuh) ---------------------------------------------------
+  // plan:      halo_flags -> [all-reduce on halo_stream] -> halo_plan_async      (for the NEXT exchange)
+  // exchange:  halo_pack  -> [all-reduce on stream]      -> halo_unpack          (between P2G and UpdateGrid)
+  void halo_init() {
+    if (halo_flags_d) return;
+    halo_flags_d = dalloc<uint8_t>(k.n_blocks);
+    halo_own = dalloc<uint8_t>(k.n_blocks);
+    halo_cta_counts = dalloc<uint32_t>((k.n_blocks + kHaloBlocksPerCta - 1) / kHaloBlocksPerCta);
+    halo_dev_words = dalloc<uint32_t>(4);
+    GMPM_CUDA(cudaHostAlloc((void**)&h_halo_words, 4 * sizeof(uint32_t), cudaHostAllocDefault));
+    memset(h_halo_words, 0, 4 * sizeof(uint32_t));
+    GMPM_CUDA(cudaStreamCreateWithFlags(&halo_stream, cudaStreamNonBlocking));
+    GMPM_CUDA(cudaEventCreateWithFlags(&ev_halo_flags, cudaEventDisableTiming));
+    GMPM_CUDA(cudaEventCreateWithFlags(&ev_halo_plan, cudaEventDisableTiming));
+    halo_reserve(2048);
+  }
   void halo_reserve(size_t blocks) {
     if (blocks <= halo_cap) return;
-    size_t cap = std::max<size_t>(1024, halo_cap * 2);
+    size_t cap = std::max<size_t>(2048, halo_cap * 2);
     while (cap < blocks) cap *= 2;
     cap = std::min<size_t>(cap, k.n_blocks);
     GMPM_CUDA(cudaStreamSynchronize(stream));
-    if (halo_list) dfree(halo_list);
+    GMPM_CUDA(cudaStreamSynchronize(halo_stream));
+    for (int i = 0; i < 2; ++i) {
+      uint32_t* old = halo_list[i];
+      halo_list[i] = dalloc<uint32_t>(cap, false);
+      if (old) {
+        GMPM_CUDA(cudaMemcpyAsync(halo_list[i], old, sizeof(uint32_t) * halo_cap, cudaMemcpyDeviceToDevice, stream));
+        GMPM_CUDA(cudaStreamSynchronize(stream));
+        dfree(old);
+      }
+    }
     if (halo_packed) dfree(halo_packed);
-    halo_list = dalloc<uint32_t>(cap, false);
     halo_packed = dalloc<T>(cap * 256, false);
     halo_cap = cap;
   }
+  void require_after_p2g(const char* what) const {
+    if (stage != GridStage::kTiles && stage != GridStage::kMomentum)
+      throw std::invalid_argument(std::string(what) + " must follow ParticleToGrid and precede UpdateGrid");
+  }
+  // Dilated touched flags of the current P2G.  The host all-reduces them on halo_stream.
   uint8_t* halo_flags() {
     require_finalized();
-    if (stage != GridStage::kTiles && stage != GridStage::kMomentum)
-      throw std::invalid_argument("halo exchange must follow ParticleToGrid and precede UpdateGrid");
-    assemble_momentum();
-    if (!halo_flags_d) {
-      halo_flags_d = dalloc<uint8_t>(k.n_blocks);
-      halo_cta_counts = dalloc<uint32_t>((k.n_blocks + kHaloBlocksPerCta - 1) / kHaloBlocksPerCta);
-      halo_n_shared = dalloc<uint32_t>(1);
-      GMPM_CUDA(cudaHostAlloc((void**)&h_halo_n, sizeof(uint32_t), cudaHostAllocDefault));
-      halo_reserve(1024);
-    }
+    require_after_p2g("halo_flags");
+    halo_init();
+    // the previous plan chain (side stream) still reads the flag buffers
+    GMPM_CUDA(cudaStreamWaitEvent(stream, ev_halo_plan, 0));
+    note("memset");
+    GMPM_CUDA(cudaMemsetAsync(halo_flags_d, 0, k.n_blocks, stream));
     launch("halo_flags");
-    halo_flags_kernel<<<blocks_for(k.n_blocks), kThreads, 0, stream>>>(k.n_blocks, touched_epoch, p2g_epoch, halo_flags_d);
+    halo_flags_kernel<<<persistent_ctas(2), kThreads, 0, stream>>>(touched_list[tl_cur], ctr,
+                                                                  (uint32_t)k.domain_size >> 2,
+                                                                  halo_own_valid ? halo_own : nullptr, halo_flags_d,
+                                                                  halo_dev_words + 2);
     GMPM_CUDA(cudaGetLastError());
-    halo_stage = 1;
+    GMPM_CUDA(cudaMemcpyAsync(halo_own, halo_flags_d, k.n_blocks, cudaMemcpyDeviceToDevice, stream));
+    halo_own_valid = true;
+    GMPM_CUDA(cudaEventRecord(ev_halo_flags, stream));
+    GMPM_CUDA(cudaStreamWaitEvent(halo_stream, ev_halo_flags, 0));
+    halo_flags_out = true;
     return halo_flags_d;
   }
-  // flags now hold the sum over ranks.  Returns the number of shared blocks (one blocking 4-byte read).
-  uint32_t halo_plan() {
-    require_finalized();
-    if (halo_stage != 1) throw std::invalid_argument("halo_plan without halo_flags");
+  void halo_compact_into(int slot, cudaStream_t st) {
     const uint32_t ctas = (k.n_blocks + kHaloBlocksPerCta - 1) / kHaloBlocksPerCta;
-    for (;;) {
-      launch("halo_count");
-      halo_count_kernel<<<ctas, kHaloThreads, 0, stream>>>(k.n_blocks, halo_flags_d, halo_cta_counts);
-      launch("halo_compact");
-      halo_compact_kernel<<<ctas, kHaloThreads, 0, stream>>>(k.n_blocks, halo_flags_d, halo_cta_counts, halo_list,
-                                                            (uint32_t)halo_cap, halo_n_shared);
-      launch("halo_pack");
-      halo_pack_kernel<T, false><<<persistent_ctas(8), kHaloThreads, 0, stream>>>(
-          halo_n_shared, (uint32_t)halo_cap, halo_list, touched_epoch, p2g_epoch, g_mass, g_vel, halo_packed);
-      GMPM_CUDA(cudaGetLastError());
-      GMPM_CUDA(cudaMemcpyAsync(h_halo_n, halo_n_shared, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+    halo_count_kernel<<<ctas, kHaloThreads, 0, st>>>(k.n_blocks, halo_flags_d, halo_cta_counts);
+    halo_compact_kernel<<<ctas, kHaloThreads, 0, st>>>(k.n_blocks, halo_flags_d, halo_cta_counts, halo_list[slot],
+                                                      (uint32_t)halo_cap, halo_dev_words + slot);
+    GMPM_CUDA(cudaGetLastError());
+    launches += 2;
+  }
+  // flags now hold the sum over the ranks: build the shared-block list of the next exchange on the side
+  // stream; its count lands in pinned memory and is picked up by the next halo_pack.
+  void halo_plan_async() {
+    require_finalized();
+    if (!halo_flags_out) throw std::invalid_argument("halo_plan without halo_flags");
+    const int slot = halo_planned ? halo_cur ^ 1 : halo_cur;
+    halo_compact_into(slot, halo_stream);
+    GMPM_CUDA(cudaMemcpyAsync(h_halo_words + 2 * slot, halo_dev_words + slot, sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                              halo_stream));
+    GMPM_CUDA(cudaMemcpyAsync(h_halo_words + 2 * slot + 1, halo_dev_words + 2, sizeof(uint32_t),
+                              cudaMemcpyDeviceToHost, halo_stream));
+    GMPM_CUDA(cudaEventRecord(ev_halo_plan, halo_stream));
+    halo_flags_out = false;
+    halo_next_slot = slot;
+    halo_plan_pending = true;
+  }
+  int halo_next_slot = 0;
+  bool halo_plan_pending = false;
+  // Packs this rank's share of the planned shared blocks; returns their number (known on the host).
+  uint32_t halo_pack() {
+    require_finalized();
+    require_after_p2g("halo_pack");
+    if (!halo_plan_pending) throw std::invalid_argument("halo_pack without a plan (halo_flags / halo_plan first)");
+    GMPM_CUDA(cudaEventSynchronize(ev_halo_plan));  // issued a whole substep ago (or just now at start-up)
+    const int slot = halo_next_slot;
+    if (h_halo_words[2 * slot + 1] != 0)
+      throw std::runtime_error("halo exchange: a particle block appeared outside the dilated block set planned one "
+                               "substep earlier (a particle moved more than one grid block in a substep)");
+    uint32_t n = h_halo_words[2 * slot];
+    if (n > halo_cap) {  // rare: the lists were too short; grow and redo the compaction (flags still hold the sums)
+      halo_reserve(n);
+      halo_compact_into(slot, stream);
       GMPM_CUDA(cudaStreamSynchronize(stream));
-      halo_n = *h_halo_n;
-      if (halo_n <= halo_cap) break;
-      halo_reserve(halo_n);  // grow and redo (rare: the shared set grows slowly)
     }
-    halo_stage = 2;
-    return halo_n;
+    halo_cur = slot;
+    halo_planned = true;
+    halo_plan_pending = false;
+    halo_n = n;
+    GMPM_CUDA(cudaStreamWaitEvent(stream, ev_halo_plan, 0));
+    assemble_momentum();
+    if (n) {
+      launch("halo_pack");
+      halo_pack_kernel<T, false><<<std::min<uint32_t>(n, persistent_ctas(8)), kHaloThreads, 0, stream>>>(
+          n, halo_list[slot], touched_epoch, p2g_epoch, g_mass, g_vel, halo_packed);
+      GMPM_CUDA(cudaGetLastError());
+    }
+    halo_packed_out = true;
+    return n;
   }
   void halo_unpack() {
     require_finalized();
-    if (halo_stage != 2) throw std::invalid_argument("halo_unpack without halo_plan");
+    if (!halo_packed_out) throw std::invalid_argument("halo_unpack without halo_pack");
     if (halo_n) {
       launch("halo_unpack");
-      halo_pack_kernel<T, true><<<persistent_ctas(8), kHaloThreads, 0, stream>>>(
-          halo_n_shared, (uint32_t)halo_cap, halo_list, touched_epoch, p2g_epoch, g_mass, g_vel, halo_packed);
+      halo_pack_kernel<T, true><<<std::min<uint32_t>(halo_n, persistent_ctas(8)), kHaloThreads, 0, stream>>>(
+          halo_n, halo_list[halo_cur], touched_epoch, p2g_epoch, g_mass, g_vel, halo_packed);
       GMPM_CUDA(cudaGetLastError());
     }
-    halo_stage = 0;
+    halo_packed_out = false;
   }
 
   cudaEvent_t timers[16]{};

@@ -193,10 +193,18 @@ class GpuMpmState:
         check(self._f("halo_flags")(self._h, C.byref(p), C.byref(n)))
         return p.value, n.value
 
-    def halo_plan(self):
+    def halo_stream_handle(self):
+        p = C.c_void_p()
+        check(self._f("halo_stream")(self._h, C.byref(p)))
+        return p.value or 0
+
+    def halo_plan_async(self):
+        check(self._f("halo_plan_async")(self._h))
+
+    def halo_pack(self):
         """-> (n_shared, device pointer of T[n_shared][4][64])"""
         n, p = C.c_uint32(), C.c_void_p()
-        check(self._f("halo_plan")(self._h, C.byref(n), C.byref(p)))
+        check(self._f("halo_pack")(self._h, C.byref(n), C.byref(p)))
         return n.value, p.value
 
     def halo_unpack(self):

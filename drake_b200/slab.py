@@ -3,19 +3,25 @@ whole cloth meshes, grid blocks reached by several ranks summed between Particle
 
 The reference is single-GPU (multibody/gpu_mpm/settings.h:40: G_DEVICE_COUNT = 1, never read); this is
 the extension SURVEY.md 8(e) plans.  The device side lives in libgmpm_b200.so (csrc/halo.cuh, entry
-points gmpm_halo_flags / gmpm_halo_plan / gmpm_halo_unpack); this module is the host plumbing: it owns
-no arithmetic, it only orders the two collectives between those calls:
+points gmpm_halo_flags / halo_plan_async / halo_pack / halo_unpack); this module is the host plumbing:
+it owns no arithmetic, it only orders the two collectives per substep between those calls.
 
-    flags  = backend.halo_flags()          # uint8[n_blocks], 1 = this rank's P2G touched the block
-    all_reduce(flags, SUM)                 # NCCL over NVLink (gloo in the CPU tests)
-    packed = backend.halo_plan()           # T[n_shared * 256]: own mass + momentum of blocks with flags > 1
-    all_reduce(packed, SUM)
-    backend.halo_unpack()                  # sums written back where this rank touches the block
+    exchange (critical path, between P2G and UpdateGrid; list planned one substep earlier):
+        packed = backend.halo_pack()       # T[n_shared * 256]: own mass + momentum of the shared blocks
+        all_reduce(packed, SUM)            # NCCL over NVLink (gloo in the CPU tests)
+        backend.halo_unpack()              # sums written back where this rank touched the block
+    plan for the next substep (side stream, overlaps UpdateGrid / G2P / FEM / binning / P2G):
+        flags = backend.halo_flags()       # uint8[n_blocks]: 1 within one block of a touched block
+        all_reduce(flags, SUM)
+        backend.halo_plan_async()          # shared = flags > 1, ascending ids, same list on every rank
 
-`backend` is anything with those three methods returning torch tensors that alias its buffers: the GPU
+A particle moves less than one grid block per substep, so the dilated set planned at substep k covers
+everything substep k+1 can touch (checked on the device; halo_pack raises otherwise).  Nothing in the
+substep blocks the host: the count of shared blocks travels through pinned memory one substep ahead.
+
+`backend` is anything with those four methods returning torch tensors that alias its buffers: the GPU
 backend below wraps a GpuMpmState (tensors alias device memory, collectives are enqueued on the state's
-own CUDA stream, so the whole substep stays stream-ordered with a single 4-byte read-back in
-halo_plan); the CPU tests drive the same protocol class with a backend built on the oracle.
+own CUDA streams); the CPU tests drive the same protocol class with a backend built on the oracle.
 """
 import numpy as np
 
@@ -41,7 +47,7 @@ class _DevArray:
 
 
 class GpuHaloBackend:
-    """The three device steps of one GpuMpmState as torch tensors aliasing the library's buffers."""
+    """The four device steps of one GpuMpmState as torch tensors aliasing the library's buffers."""
 
     def __init__(self, state):
         import torch
@@ -49,21 +55,31 @@ class GpuHaloBackend:
         self.torch = torch
         self.device = torch.device("cuda", state.params.device if state.params.device >= 0 else torch.cuda.current_device())
         self.stream = torch.cuda.ExternalStream(state.stream_handle(), device=self.device)
+        self.plan_stream = torch.cuda.ExternalStream(state.halo_stream_handle(), device=self.device)
         self._typestr = "<f8" if state.dtype == np.float64 else "<f4"
-        self.n_shared = 0
+        self._views = {}
 
     def _view(self, ptr, n, typestr):
-        return self.torch.as_tensor(_DevArray(ptr, n, typestr), device=self.device)
+        key = (ptr, n, typestr)
+        t = self._views.get(key)
+        if t is None:
+            if len(self._views) > 64:
+                self._views.clear()
+            t = self._views[key] = self.torch.as_tensor(_DevArray(ptr, n, typestr), device=self.device)
+        return t
 
     def halo_flags(self):
         ptr, n = self.state.halo_flags()
         return self._view(ptr, n, "|u1")
 
-    def halo_plan(self):
-        self.n_shared, ptr = self.state.halo_plan()
-        if self.n_shared == 0:
+    def halo_plan_async(self):
+        self.state.halo_plan_async()
+
+    def halo_pack(self):
+        n_shared, ptr = self.state.halo_pack()
+        if n_shared == 0:
             return None
-        return self._view(ptr, self.n_shared * 256, self._typestr)
+        return self._view(ptr, n_shared * 256, self._typestr)
 
     def halo_unpack(self):
         self.state.halo_unpack()
@@ -78,49 +94,78 @@ class SlabExchange:
         self.dist = dist
         self.group = group
         self.stream = getattr(backend, "stream", None)
+        self.plan_stream = getattr(backend, "plan_stream", None)
+        self.planned = False
         self.last_n_shared = 0
         self.bytes_reduced = 0
 
-    def _all_reduce(self, t):
-        if self.stream is not None:
+    def _all_reduce(self, t, stream):
+        if stream is not None:
             import torch
-            with torch.cuda.stream(self.stream):   # ordered after the state's kernels, before its next ones
+            with torch.cuda.stream(stream):        # ordered with the state's kernels on that stream
                 self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
         else:
             self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
         self.bytes_reduced += t.numel() * t.element_size()
 
+    def _plan(self):
+        flags = self.backend.halo_flags()
+        self._all_reduce(flags, self.plan_stream)
+        self.backend.halo_plan_async()
+        self.planned = True
+
     def exchange(self):
         """Call between ParticleToGrid and UpdateGrid, on every rank."""
-        flags = self.backend.halo_flags()
-        self._all_reduce(flags)
-        packed = self.backend.halo_plan()     # every rank derives the same shared-block list
+        if not self.planned:
+            self._plan()                          # start-up: plan from the current (dilated) touched set
+        packed = self.backend.halo_pack()         # every rank holds the same shared-block list
         self.last_n_shared = 0 if packed is None else packed.numel() // 256
         if packed is not None:
-            self._all_reduce(packed)
+            self._all_reduce(packed, self.stream)
         self.backend.halo_unpack()
+        self._plan()                              # for the next substep, off the critical path
         return self.last_n_shared
 
 
-def exchange_in_process(backends):
-    """The same protocol for several states living in ONE process (tests: two states on one GPU, or
-    two oracles on the CPU): the all-reduces become explicit sums over the backends' tensors."""
-    flags = [b.halo_flags() for b in backends]
-    total = flags[0].clone()
-    for f in flags[1:]:
-        total += f
-    for f in flags:
-        f.copy_(total)
-    packed = [b.halo_plan() for b in backends]
-    if packed[0] is not None:
-        total = packed[0].clone()
-        for p in packed[1:]:
-            total += p
-        for p in packed:
-            p.copy_(total)
-    for b in backends:
-        b.halo_unpack()
-    return 0 if packed[0] is None else packed[0].numel() // 256
+class InProcessExchange:
+    """The same protocol for several states living in ONE process (tests: two states on one GPU, or two
+    oracles on the CPU): the all-reduces become explicit sums over the backends' tensors."""
+
+    def __init__(self, backends, sync=None):
+        self.backends = backends
+        self.sync = sync or (lambda: None)        # GPU states use several streams: order them by hand
+        self.planned = False
+
+    @staticmethod
+    def _sum(ts):
+        total = ts[0].clone()
+        for t in ts[1:]:
+            total += t
+        for t in ts:
+            t.copy_(total)
+
+    def _plan(self):
+        flags = [b.halo_flags() for b in self.backends]
+        self.sync()
+        self._sum(flags)
+        self.sync()
+        for b in self.backends:
+            b.halo_plan_async()
+        self.planned = True
+
+    def exchange(self):
+        if not self.planned:
+            self._plan()
+        packed = [b.halo_pack() for b in self.backends]
+        n = 0 if packed[0] is None else packed[0].numel() // 256
+        self.sync()
+        if n:
+            self._sum(packed)
+        self.sync()
+        for b in self.backends:
+            b.halo_unpack()
+        self._plan()
+        return n
 
 
 def substep(solver, state, exchange, dt, mpm_bc=-1, sort=False):

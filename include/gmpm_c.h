@@ -144,20 +144,27 @@ int gmpm_device_sync(void);
   /* ---- multi-GPU extension (not in the reference: settings.h:40 G_DEVICE_COUNT = 1 is unused). ---- */\
   /* One process and one state per GPU; every rank holds whole cloth meshes and addresses the same    */\
   /* grid.  Between ParticleToGrid and UpdateGrid the ranks sum the grid blocks more than one of them */\
-  /* touched (Multi-GPU).  The library does the device side; the host runs the two        */\
-  /* all-reduces (NCCL SUM) on the state's stream (gmpm_stream) between the calls:                    */\
-  /*   halo_flags : *flags_dev = uint8[*n_blocks] on the device, 1 where this rank's P2G touched the  */\
-  /*                block              -> host all-reduces flags_dev in place (ncclUint8, sum)        */\
-  /*   halo_plan  : shared blocks = flags > 1 in ascending block id (identical on every rank);        */\
-  /*                *packed_dev = T[*n_shared][4][64] = this rank's mass and momentum of them (zeros  */\
-  /*                where it has none); blocks on one 4-byte read-back                                */\
-  /*                                   -> host all-reduces packed_dev[0 : *n_shared * 256] (sum)      */\
-  /*   halo_unpack: the sums are written back into the blocks this rank touches; UpdateGrid follows.  */\
+  /* reaches (Multi-GPU).  The library does the device side; the host runs two all-reduces */\
+  /* (NCCL SUM) per substep between the calls.  PLAN, for the next substep, off the critical path:    */\
+  /*   halo_flags      : *flags_dev = uint8[*n_blocks], 1 within one block of a block this rank's P2G */\
+  /*                     touched   -> host all-reduces flags_dev in place on gmpm_halo_stream         */\
+  /*   halo_plan_async : shared blocks = flags > 1 in ascending block id (identical on every rank),   */\
+  /*                     built on the halo stream; nothing is returned and nothing blocks             */\
+  /* EXCHANGE, with the list planned one substep earlier (the first one: plan, then exchange):        */\
+  /*   halo_pack       : *packed_dev = T[*n_shared][4][64] = this rank's mass and momentum of the     */\
+  /*                     shared blocks (zeros where it has none)                                      */\
+  /*                               -> host all-reduces packed_dev[0 : *n_shared * 256] on gmpm_stream */\
+  /*   halo_unpack     : the sums are written back into the blocks this rank touched; UpdateGrid next */\
+  /* halo_pack fails if a block was touched outside the set planned for it (a particle moved more     */\
+  /* than one grid block in one substep).                                                             */\
   int gmpm_halo_flags_##SUF(gmpm_state_##SUF* s, void** flags_dev, size_t* n_blocks);               \
-  int gmpm_halo_plan_##SUF(gmpm_state_##SUF* s, uint32_t* n_shared, void** packed_dev);             \
+  int gmpm_halo_plan_async_##SUF(gmpm_state_##SUF* s);                                              \
+  int gmpm_halo_pack_##SUF(gmpm_state_##SUF* s, uint32_t* n_shared, void** packed_dev);             \
   int gmpm_halo_unpack_##SUF(gmpm_state_##SUF* s);                                                  \
-  /* The cudaStream_t all work of this state is issued on (for stream-ordered collectives). */      \
+  /* The cudaStream_t all work of this state is issued on, and the side stream of the halo planning  */\
+  /* (for stream-ordered collectives). */                                                           \
   int gmpm_stream_##SUF(gmpm_state_##SUF* s, void** cuda_stream);                                   \
+  int gmpm_halo_stream_##SUF(gmpm_state_##SUF* s, void** cuda_stream);                              \
   /* One substep of the driver loop without contact (deformable_driver.h:240-260 /                */\
   /* cuda_mpm_test.cc:66-72): RebuildMapping(sort) CalcFemStateAndForce ParticleToGrid            */\
   /* UpdateGrid(mpm_bc) GridToParticle, n_substeps times; sort_every = k sorts at substeps        */\

@@ -5,21 +5,57 @@ import numpy as np
 import torch
 
 
+def _contract(v):
+    v = v & 0x09249249
+    v = (v ^ (v >> 2)) & 0x030C30C3
+    v = (v ^ (v >> 4)) & 0x0300F00F
+    v = (v ^ (v >> 8)) & 0xFF0000FF
+    v = (v ^ (v >> 16)) & 0x000003FF
+    return v
+
+
+def dilate_blocks(flags):
+    """flags[n_blocks] (Morton block ids, x most significant) -> flags of the 3x3x3 block neighbourhood."""
+    n = flags.size
+    side = round(n ** (1.0 / 3.0))
+    ids = np.arange(n, dtype=np.uint32)
+    bx, by, bz = _contract(ids >> 2), _contract(ids >> 1), _contract(ids)
+    dense = np.zeros((side + 2,) * 3, bool)
+    dense[bx + 1, by + 1, bz + 1] = flags
+    out = np.zeros_like(dense)
+    for dx in (-1, 0, 1):
+        for dy in (-1, 0, 1):
+            for dz in (-1, 0, 1):
+                out |= np.roll(dense, (dx, dy, dz), axis=(0, 1, 2))
+    return out[bx + 1, by + 1, bz + 1]
+
+
 class OracleHaloBackend:
     def __init__(self, orc):
         self.orc = orc
-        self.own = None
+        self.planned_own = None     # own dilated flags of the previous plan (containment check)
+        self.next_shared = None
         self.shared = None
         self._flags = None
         self._packed = None
 
+    def _touched(self):
+        return self.orc.view("grid_touched_flags") != 0
+
     def halo_flags(self):
-        self.own = self.orc.view("grid_touched_flags") != 0
-        self._flags = torch.from_numpy(self.own.astype(np.uint8))
+        touched = self._touched()
+        if self.planned_own is not None:
+            assert not np.any(touched & ~self.planned_own), "touched block outside the planned dilated set"
+        self.planned_own = dilate_blocks(touched)
+        self._flags = torch.from_numpy(self.planned_own.astype(np.uint8))
         return self._flags
 
-    def halo_plan(self):
-        self.shared = np.nonzero(self._flags.numpy() > 1)[0]          # ascending block ids
+    def halo_plan_async(self):
+        self.next_shared = np.nonzero(self._flags.numpy() > 1)[0]     # ascending block ids
+
+    def halo_pack(self):
+        self.shared = self.next_shared
+        self.own = self._touched()
         if self.shared.size == 0:
             self._packed = None
             return None

@@ -65,7 +65,7 @@ def test_oracle_two_parts_in_process_match_single():
     full = make_oracle(dtype, sheets)
     parts = slab.partition_meshes(len(sheets), 2)
     orcs = [make_oracle(dtype, [sheets[i] for i in p]) for p in parts]
-    backs = [OracleHaloBackend(o) for o in orcs]
+    ex = slab.InProcessExchange([OracleHaloBackend(o) for o in orcs])
     shared_seen = 0
     for it in range(8):
         full.substep(DT, -1, it == 3)
@@ -73,7 +73,7 @@ def test_oracle_two_parts_in_process_match_single():
             o.RebuildMapping(it == 3)
             o.CalcFemStateAndForce(DT)
             o.ParticleToGrid(DT)
-        shared_seen += slab.exchange_in_process(backs)
+        shared_seen += ex.exchange()
         for o in orcs:
             o.UpdateGrid(-1)
             o.GridToParticle(DT)
@@ -143,7 +143,13 @@ def test_two_states_one_gpu_match_single_state_and_oracle(dtype, tol):
     orc = make_oracle(dtype, sheets)
     parts = slab.partition_meshes(len(sheets), 2)
     sts = [make_state(dtype, [sheets[i] for i in p]) for p in parts]
-    backs = [slab.GpuHaloBackend(s) for s in sts]
+    def sync_all():
+        for s in sts:
+            sv.GpuSync(s)
+        import torch
+        torch.cuda.synchronize()
+
+    ex = slab.InProcessExchange([slab.GpuHaloBackend(s) for s in sts], sync=sync_all)
     shared_seen = 0
     for it in range(12):
         sort = it == 5
@@ -153,11 +159,8 @@ def test_two_states_one_gpu_match_single_state_and_oracle(dtype, tol):
             sv.RebuildMapping(s, sort)
             sv.CalcFemStateAndForce(s, DT)
             sv.ParticleToGrid(s, DT)
+        shared_seen += ex.exchange()
         for s in sts:
-            sv.GpuSync(s)                      # two streams, explicit sums in between: order them by hand
-        shared_seen += slab.exchange_in_process(backs)
-        for s in sts:
-            sv.GpuSync(s)
             sv.UpdateGrid(s, -1)
             sv.GridToParticle(s, DT)
     assert shared_seen > 0
@@ -183,10 +186,13 @@ def test_halo_call_order_is_checked():
     sv.CalcFemStateAndForce(st, DT)
     sv.ParticleToGrid(st, DT)
     with pytest.raises(GmpmError):
-        st.halo_unpack()                       # not planned
+        st.halo_unpack()                       # nothing packed
+    with pytest.raises(GmpmError):
+        st.halo_pack()                         # nothing planned
     ptr, n = st.halo_flags()
     assert ptr and n == 32768
-    n_shared, _ = st.halo_plan()               # alone: nothing is shared
+    st.halo_plan_async()
+    n_shared, _ = st.halo_pack()               # alone: no block has flags > 1
     assert n_shared == 0
     st.halo_unpack()
     sv.UpdateGrid(st, -1)
