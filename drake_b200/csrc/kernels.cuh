@@ -237,18 +237,23 @@ fem_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ fid, const int*
            uint32_t* __restrict__ key, T dt, Consts<T> k) {
   const uint32_t stride = gridDim.x * blockDim.x;
   uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
-  auto resolve = [&](uint32_t ff) -> FemIdx {
+  // two index levels, each resolved one iteration ahead of its use (an in-order warp stalls at the first
+  // instruction whose operand is still in flight, so a dependent pair of loads must not share an iteration)
+  auto level1 = [&](uint32_t ff) -> FemIdx {  // particle ids of the record: face particle, three vertices
     FemIdx r{0, 0, 0, 0};
     if (ff < n_faces) {
-      const int t0 = tri[ff], t1 = tri[n_faces + ff], t2 = tri[2 * n_faces + ff];
-      r.sf = slot_of_pid[fid[ff]];
-      r.s0 = slot_of_pid[t0];
-      r.s1 = slot_of_pid[t1];
-      r.s2 = slot_of_pid[t2];
+      r.sf = fid[ff];
+      r.s0 = tri[ff];
+      r.s1 = tri[n_faces + ff];
+      r.s2 = tri[2 * n_faces + ff];
     }
     return r;
   };
-  FemIdx cur = resolve(f);
+  auto level2 = [&](const FemIdx& ids) -> FemIdx {  // their current slots
+    return FemIdx{slot_of_pid[ids.sf], slot_of_pid[ids.s0], slot_of_pid[ids.s1], slot_of_pid[ids.s2]};
+  };
+  FemIdx cur = level2(level1(f));     // slots of face f
+  FemIdx ids_n = level1(f + stride);  // particle ids of face f + stride
   for (; f < n_faces; f += stride) {
     const int sf = cur.sf, s0 = cur.s0, s1 = cur.s1, s2 = cur.s2;
     // ---- every load of this face, before any use
@@ -270,8 +275,9 @@ fem_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ fid, const int*
 #pragma unroll
     for (int e = 0; e < 4; ++e) Dmi[e] = Dm_inv[(size_t)e * n_faces + f];
     const T volume = vol[sf];
-    // ---- indices of this thread's next face (in flight during the math below)
-    cur = resolve(f + stride);
+    // ---- indices of this thread's next faces (in flight during the math below)
+    cur = level2(ids_n);                 // ids_n arrived during the previous iteration
+    ids_n = level1(f + 2 * stride);
 
     T xc[3];
 #pragma unroll
@@ -800,74 +806,121 @@ clean_stale_blocks_kernel(const uint32_t* __restrict__ prev_list, const DevCount
 // ------------------------------------------------------------------------------------------------
 constexpr int kG2PWarps = 4;
 
+// 4- or 8-byte asynchronous global -> shared copy (LDGSTS); src_bytes = 0 writes zeros.
 template <typename T>
-__global__ void __launch_bounds__(kG2PWarps * 32, 6)
+__device__ __forceinline__ void cp_async_scalar(T* smem_dst, const T* gsrc, bool valid) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  const int n = valid ? (int)sizeof(T) : 0;
+  if (sizeof(T) == 8)
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(d), "l"(gsrc), "r"(n) : "memory");
+  else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(gsrc), "r"(n) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// Software pipeline, two chunks deep: while chunk c is gathered, the velocity tile of chunk c+1 is in
+// flight to the other shared-memory buffer (cp.async, no registers), its slot indices are loaded, and
+// the queue ticket of chunk c+2 is outstanding; the first batch of positions of chunk c+1 is loaded
+// during the last batch of chunk c.  No load is followed directly by its use.
+template <typename T>
+__global__ void __launch_bounds__(kG2PWarps * 32, 5)
 g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __restrict__ pb_work, uint32_t work_cap,
            const T* __restrict__ g_vel, const T* __restrict__ pos, const T* __restrict__ vol,
            const int* __restrict__ pid, T* __restrict__ pos_out, T* __restrict__ vel_out, T* __restrict__ C_out,
            T* __restrict__ vol_out, int* __restrict__ pid_out, int* __restrict__ slot_of_pid,
            uint32_t* __restrict__ key_out, T* __restrict__ forces_out, DevCounters* ctr, T dt, Consts<T> k) {
-  __shared__ T s_vel[kG2PWarps][3][kTileNodes];
+  __shared__ T s_vel[kG2PWarps][2][3][kTileNodes];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  T* tv = &s_vel[warp][0][0];
   const uint32_t n_big = ctr->n_big, n_work = n_big + ctr->n_small;
   const uint32_t blocks_per_axis = (uint32_t)k.domain_size >> 2;
   const T scale = T(4) * k.dx_inv;
   const T ca = (k.v_blend + T(1)) * T(.5), cb = (k.v_blend - T(1)) * T(.5);
-  uint32_t t = 0;
-  if (lane == 0) t = atomicAdd(&ctr->work_g2p, 1u);
-  t = __shfl_sync(kFullMask, t, 0);
-  while (t < n_work) {
-    const WorkRec w = pb_work[t < n_big ? t : work_cap - 1u - (t - n_big)];
-    uint32_t t_next = 0;
-    if (lane == 0) t_next = atomicAdd(&ctr->work_g2p, 1u);  // in flight while this chunk is processed
-    // slot indices of the whole chunk (<= kChunk = 4 batches) first: the position loads depend on them
-    uint32_t sidx[kChunk / 32];
-#pragma unroll
-    for (int b4 = 0; b4 < kChunk / 32; ++b4) {
-      const uint32_t ii = w.begin + b4 * 32 + lane;
-      sidx[b4] = ii < w.end ? order[ii] : 0u;
-    }
+  constexpr uint32_t kNone = 0xFFFFFFFFu;
+  static_assert(kChunk == 128, "the slot-index rotation below assumes 4 batches per chunk");
+
+  auto ticket = [&]() -> uint32_t {
+    uint32_t t = 0;
+    if (lane == 0) t = atomicAdd(&ctr->work_g2p, 1u);
+    return t;
+  };
+  auto resolve = [&](uint32_t t_lane0) -> WorkRec {
+    const uint32_t t = __shfl_sync(kFullMask, t_lane0, 0);
+    if (t >= n_work) return WorkRec{kNone, 0u, 0u, 0u};
+    return pb_work[t < n_big ? t : work_cap - 1u - (t - n_big)];
+  };
+  // velocity nodes the chunk's stencils can reach -> shared buffer `buf` (asynchronous)
+  auto stage = [&](const WorkRec& w, int buf) {
+    T* tvn = &s_vel[warp][buf][0][0];
     uint32_t bx, by, bz;
     block_coords(w.block, bx, by, bz);
-    // stage the reachable velocity nodes
     for (int n = lane; n < kTileNodes; n += 32) {
       const uint32_t tx = n / 36, ty = (n / 6) % 6, tz = n % 6;
       const uint32_t gx = bx + (tx >> 2), gy = by + (ty >> 2), gz = bz + (tz >> 2);
-      T v0 = T(0), v1 = T(0), v2 = T(0);
-      if (gx < blocks_per_axis && gy < blocks_per_axis && gz < blocks_per_axis) {
-        const size_t vb = (size_t)morton3(gx, gy, gz) * 192 + (((tx & 3u) << 4) | ((ty & 3u) << 2) | (tz & 3u));
-        v0 = g_vel[vb];
-        v1 = g_vel[vb + 64];
-        v2 = g_vel[vb + 128];
-      }
-      tv[n] = v0;
-      tv[kTileNodes + n] = v1;
-      tv[2 * kTileNodes + n] = v2;
+      const bool in = gx < blocks_per_axis && gy < blocks_per_axis && gz < blocks_per_axis;
+      const size_t vb = in ? (size_t)morton3(gx, gy, gz) * 192 + (((tx & 3u) << 4) | ((ty & 3u) << 2) | (tz & 3u)) : 0;
+      cp_async_scalar(tvn + n, g_vel + vb, in);
+      cp_async_scalar(tvn + kTileNodes + n, g_vel + vb + 64, in);
+      cp_async_scalar(tvn + 2 * kTileNodes + n, g_vel + vb + 128, in);
     }
+  };
+  auto load_sidx = [&](const WorkRec& w, uint32_t (&sidx)[4]) {
+#pragma unroll
+    for (int b4 = 0; b4 < 4; ++b4) {
+      const uint32_t ii = w.begin + b4 * 32 + lane;
+      sidx[b4] = ii < w.end ? order[ii] : 0u;
+    }
+  };
+
+  uint32_t t0 = ticket(), t1 = ticket();
+  WorkRec w = resolve(t0);
+  if (w.tile == kNone) return;
+  int buf = 0;
+  uint32_t sidx[4], sidx_n[4] = {0u, 0u, 0u, 0u};
+  stage(w, buf);
+  cp_async_commit();
+  load_sidx(w, sidx);
+  WorkRec wn = resolve(t1);
+  // first batch of positions of the first chunk
+  T x[3] = {T(0), T(0), T(0)};
+  if (w.begin + lane < w.end) {
+    x[0] = pos[sidx[0]];
+    x[1] = pos[(size_t)N + sidx[0]];
+    x[2] = pos[(size_t)2 * N + sidx[0]];
+  }
+  for (;;) {
+    uint32_t t2 = ticket();  // the chunk after next
+    if (wn.tile != kNone) {
+      stage(wn, buf ^ 1);
+      load_sidx(wn, sidx_n);
+    }
+    cp_async_commit();       // (possibly empty) group of the next chunk
+    cp_async_wait<1>();      // this chunk's tile has landed
+    __syncwarp();
+    const T* tv = &s_vel[warp][buf][0][0];
     uint32_t i = w.begin + lane;
     uint32_t s = sidx[0];
-    T x[3] = {T(0), T(0), T(0)};
-    if (i < w.end) {
-      x[0] = pos[s];
-      x[1] = pos[(size_t)N + s];
-      x[2] = pos[(size_t)2 * N + s];
-    }
-    static_assert(kChunk == 128, "the slot-index rotation below assumes 4 batches per chunk");
     uint32_t s1 = sidx[1], s2 = sidx[2], s3 = sidx[3];
-    __syncwarp();
-    while (i < w.end) {
-      // prefetch the next batch (its slot index is already here)
-      const uint32_t i_n = i + 32;
-      const uint32_t s_n = s1;
+    const uint32_t n_batches = (w.end - w.begin + 31u) >> 5;  // warp-uniform trip count
+    for (uint32_t bt = 0; bt < n_batches; ++bt) {
+      const bool active = i < w.end;
+      // prefetch the positions of the next batch: of this chunk, or the first one of the next chunk
+      const bool last = bt + 1 == n_batches;
+      const uint32_t i_n = last ? wn.begin + lane : i + 32;
+      const uint32_t s_n = last ? sidx_n[0] : s1;
+      const bool next_valid = last ? (wn.tile != kNone && i_n < wn.end) : (i_n < w.end);
       s1 = s2;
       s2 = s3;
       T x_n[3] = {T(0), T(0), T(0)};
-      if (i_n < w.end) {
+      if (next_valid) {
         x_n[0] = pos[s_n];
         x_n[1] = pos[(size_t)N + s_n];
         x_n[2] = pos[(size_t)2 * N + s_n];
       }
+      if (active) {
       const T pvol = vol[s];
       const int p = pid[s];
       uint32_t b[3];
@@ -935,15 +988,22 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __rest
       slot_of_pid[p] = (int)i;
       key_out[i] = cell_key(base_node(x[0], k.dx_inv, k.domain_size), base_node(x[1], k.dx_inv, k.domain_size),
                             base_node(x[2], k.dx_inv, k.domain_size));
+      }  // active
       i = i_n;
       s = s_n;
       x[0] = x_n[0];
       x[1] = x_n[1];
       x[2] = x_n[2];
     }
-    __syncwarp();
-    t = __shfl_sync(kFullMask, t_next, 0);
+    __syncwarp();  // every lane is done with this tile before the buffer is staged again
+    if (wn.tile == kNone) break;
+    w = wn;
+#pragma unroll
+    for (int b4 = 0; b4 < 4; ++b4) sidx[b4] = sidx_n[b4];
+    wn = resolve(t2);
+    buf ^= 1;
   }
+  cp_async_wait<0>();
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -311,6 +311,20 @@ def test_single_triangle_and_domain_bits():
         assert_particles_close(st.read, orc.read, 1e-9, bits)
 
 
+def test_cell_size_decoupled_from_cell_count():
+    """gmpm_params.dx: the multi-GPU scenes keep the reference's dx = 1/128 on a 256^3 grid (domain
+    [0,2]^3); a scene placed in the far octant must behave like the oracle with the same parameters."""
+    dtype = np.float64
+    sheets = [(p + np.array([1.0, 1.0, 0.9]), v, t) for p, v, t in small_scene(dtype, res=30, warm=True)]
+    st, sv, orc = make_pair(dtype, sheets, domain_bits=8, dx=1.0 / 128)
+    run_both(st, sv, orc, 1, 1e-3, sort_every=0)
+    assert_particles_close(st.read, orc.read, 1e-9, "1 step, dx=1/128 on 256^3")
+    run_both(st, sv, orc, 29, 1e-3, sort_every=7)
+    assert_particles_close(st.read, orc.read, 1e-7, "30 steps")
+    assert np.array_equal(st.read("sort_keys"), orc.read("sort_keys"))
+    assert np.array_equal(st.read("pids"), orc.read("pids"))
+
+
 def test_near_walls_and_block_corners():
     """Particles whose stencils straddle block corners and the 3-cell sticky walls."""
     dtype = np.float64
