@@ -7,9 +7,11 @@
 // the exchange step sits between ParticleToGrid and UpdateGrid:
 //
 //   plan (for the NEXT substep, off the critical path, on a side stream):
-//   1. halo_flags   : flags[b] = 1 if block b is within one block (3x3x3 neighbourhood) of a block this
-//                     rank's P2G touched NOW.  A particle moves less than a block per substep (CFL), so
-//                     the dilated set contains everything the rank can touch in the next substep.
+//   1. halo_flags   : flags[b] = 1 if block b was touched by this rank's P2G NOW, or is the neighbour of a
+//                     touched block that holds mass in its cell layer facing b.  A particle moves less
+//                     than one CELL per substep (CFL), so next substep's stencils stay inside the cells
+//                     with mass now dilated by one cell: the flagged set contains every block the rank
+//                     can touch in the next substep.
 //      -- host: all-reduce SUM of flags over the ranks (NCCL) --
 //   2. halo_plan    : shared blocks = {b : flags[b] > 1}, listed in ascending block id by a
 //                     deterministic two-kernel compaction (every rank derives the SAME list from the
@@ -37,10 +39,14 @@ constexpr int kHaloBlocksPerCta = 1024;  // grid blocks scanned by one CTA (4 pe
 // also checks the block against the previous dilated set `own_prev` (containment / CFL check).
 __global__ void halo_flags_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __restrict__ ctr,
                                   uint32_t blocks_per_axis, const uint8_t* __restrict__ own_prev,
-                                  uint8_t* __restrict__ flags, uint32_t* __restrict__ err) {
+                                  const uint32_t* __restrict__ nbr_list, uint8_t* __restrict__ flags,
+                                  uint32_t* __restrict__ err) {
   const uint32_t n = ctr->n_touched * 27u;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const uint32_t g = touched_list[i / 27u], d = i % 27u;
+    // nbr_list (from the grid assembly): neighbour directions in which the block has mass in its outer
+    // cell layer; without it every neighbour is flagged
+    if (nbr_list && d != 13u && !((nbr_list[i / 27u] >> d) & 1u)) continue;
     uint32_t bx, by, bz;
     block_coords(g, bx, by, bz);
     const uint32_t nx = bx + d / 9u - 1u, ny = by + (d / 3u) % 3u - 1u, nz = bz + d % 3u - 1u;  // wraps below 0

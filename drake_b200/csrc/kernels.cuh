@@ -487,7 +487,8 @@ p2g_tile_kernel(uint32_t N, uint32_t n_faces, const uint32_t* __restrict__ order
                 const T* __restrict__ pos, const T* __restrict__ vel, const T* __restrict__ vol,
                 const T* __restrict__ C, const int* __restrict__ pid, const T* __restrict__ forces,
                 const T* __restrict__ taus, T* __restrict__ tiles, uint32_t* __restrict__ touched_epoch,
-                uint32_t* __restrict__ touched_list, uint32_t epoch, DevCounters* ctr, T dt, Consts<T> k) {
+                uint32_t* __restrict__ touched_list, uint32_t epoch, DevCounters* ctr, T dt, Consts<T> k,
+                uint32_t* __restrict__ nbr_list = nullptr) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   P2GSmem<T>& sm = *reinterpret_cast<P2GSmem<T>*>(smem_raw);
   const int lane = threadIdx.x;
@@ -628,7 +629,11 @@ p2g_tile_kernel(uint32_t N, uint32_t n_faces, const uint32_t* __restrict__ order
       bz += lane & 1u;
       if (bx < blocks_per_axis && by < blocks_per_axis && bz < blocks_per_axis) {
         const uint32_t g = morton3(bx, by, bz);
-        if (atomicExch(&touched_epoch[g], epoch) != epoch) touched_list[atomicAdd(&ctr->n_touched, 1u)] = g;
+        if (atomicExch(&touched_epoch[g], epoch) != epoch) {
+          const uint32_t idx = atomicAdd(&ctr->n_touched, 1u);
+          touched_list[idx] = g;
+          if (nbr_list) nbr_list[idx] = 0u;  // filled by the grid assembly (multi-GPU planning)
+        }
       }
     }
     __syncwarp();
@@ -709,7 +714,7 @@ __global__ void __launch_bounds__(kThreads)
 grid_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __restrict__ ctr,
             const T* __restrict__ tiles, const uint2* __restrict__ pb_tile, const uint32_t* __restrict__ pb_epoch,
             uint32_t epoch, T* __restrict__ g_mass, T* __restrict__ g_vel, T* __restrict__ g_vstar, int bc,
-            Consts<T> k) {
+            Consts<T> k, uint32_t* __restrict__ nbr_list = nullptr) {
   const uint32_t n_touched = ctr->n_touched;
   const uint32_t l = threadIdx.x & 63u;
   const uint32_t lx = (l >> 4) & 3u, ly = (l >> 2) & 3u, lz = l & 3u;
@@ -747,6 +752,21 @@ grid_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __rest
           p[1] += tl[2 * kTileNodes];
           p[2] += tl[3 * kTileNodes];
         }
+      }
+      if (nbr_list) {
+        // multi-GPU planning (halo.cuh): towards which of the 26 neighbour blocks does this block hold mass
+        // in its outermost cell layer?  Only those can be reached by its particles in the next substep.
+        uint32_t mk = 0;
+        if (m > T(0)) {
+          const uint32_t xb = 2u | (lx == 0u ? 1u : 0u) | (lx == 3u ? 4u : 0u);
+          const uint32_t yb = 2u | (ly == 0u ? 1u : 0u) | (ly == 3u ? 4u : 0u);
+          const uint32_t zb = 2u | (lz == 0u ? 1u : 0u) | (lz == 3u ? 4u : 0u);
+#pragma unroll
+          for (int d = 0; d < 27; ++d)
+            if (((xb >> (d / 9)) & 1u) && ((yb >> ((d / 3) % 3)) & 1u) && ((zb >> (d % 3)) & 1u)) mk |= 1u << d;
+        }
+        mk = __reduce_or_sync(kFullMask, mk);
+        if ((threadIdx.x & 31u) == 0u && mk) atomicOr(&nbr_list[it], mk);
       }
       if (!UPDATE) {
         g_mass[cell] = m;

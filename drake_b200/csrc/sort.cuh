@@ -25,7 +25,10 @@ constexpr int kMaxRadixBits = 11;
 constexpr int kMaxRadix = 1 << kMaxRadixBits;
 constexpr int kSortThreads = 256;
 constexpr int kSortWarps = kSortThreads / 32;
-constexpr int kSortItemsPerLane = 16;                                  // per pass-through of a warp
+#ifndef GMPM_SORT_ITEMS
+#define GMPM_SORT_ITEMS 16
+#endif
+constexpr int kSortItemsPerLane = GMPM_SORT_ITEMS;                                  // per pass-through of a warp
 constexpr int kSortWarpChunk = 32 * kSortItemsPerLane;                 // 512 consecutive items / warp
 constexpr int kSortTile = kSortWarps * kSortWarpChunk;                 // 4096 items / CTA
 constexpr size_t kSortSmemBytes = sizeof(uint32_t) * (size_t)(kSortWarps + 1) * kMaxRadix + 64;

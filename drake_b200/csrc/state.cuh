@@ -150,6 +150,9 @@ struct State {
 
   // shared-block exchange (halo.cuh)
   uint8_t *halo_flags_d = nullptr, *halo_own = nullptr;
+  uint32_t* halo_nbr = nullptr;   // per touched-list entry: outer-layer occupancy towards the 26 neighbours
+  uint32_t halo_nbr_epoch = 0;    // P2G epoch halo_nbr was computed for
+  uint32_t halo_nbr_zeroed_epoch = 0;
   uint32_t *halo_list[2]{}, *halo_cta_counts = nullptr, *halo_dev_words = nullptr;  // [0..1] counts, [2] error
   uint32_t* h_halo_words = nullptr;  // pinned mirror of halo_dev_words (per plan slot: count, error)
   T* halo_packed = nullptr;
@@ -542,10 +545,12 @@ struct State {
       p2g_prologue_kernel<<<1, 1, 0, stream>>>(ctr);
     }
     prologue_done = false;
+    halo_nbr_zeroed_epoch = halo_nbr ? p2g_epoch : 0;  // the tile kernel zeroes the entries it appends
     launch("p2g_tile");
     p2g_tile_kernel<T><<<persistent_ctas(p2g_ctas_per_sm), kP2GThreads, sizeof(P2GSmem<T>), stream>>>(
         (uint32_t)N, (uint32_t)n_faces, order(), sorted_keys(), pb_work, (uint32_t)work_cap, pos[cur], vel[cur],
-        vol[cur], C[cur], pid[cur], forces, taus, tiles, touched_epoch, touched_list[tl_cur], p2g_epoch, ctr, dt, k);
+        vol[cur], C[cur], pid[cur], forces, taus, tiles, touched_epoch, touched_list[tl_cur], p2g_epoch, ctr, dt, k,
+        halo_nbr);
     g2p_queue_ready = true;  // the prologue reset both work queues
     launch("clean_stale_blocks");
     clean_stale_blocks_kernel<T><<<persistent_ctas(2), kThreads, 0, stream>>>(touched_list[tl_cur ^ 1], ctr,
@@ -556,9 +561,11 @@ struct State {
 
   void assemble_momentum() {  // observable P2G result (grid_masses / grid_momentum before UpdateGrid)
     if (stage != GridStage::kTiles) return;
+    if (halo_nbr) halo_nbr_epoch = halo_nbr_zeroed_epoch == p2g_epoch ? p2g_epoch : 0;
     launch("grid_assemble");
     grid_kernel<T, true, false><<<persistent_ctas(4), kThreads, 0, stream>>>(
-        touched_list[tl_cur], ctr, tiles, pb_tile, pb_epoch, bin_epoch, g_mass, g_vel, g_vstar, -1, k);
+        touched_list[tl_cur], ctr, tiles, pb_tile, pb_epoch, bin_epoch, g_mass, g_vel, g_vstar, -1, k,
+        halo_nbr_epoch == p2g_epoch ? halo_nbr : nullptr);
     GMPM_CUDA(cudaGetLastError());
     stage = GridStage::kMomentum;
   }
@@ -611,6 +618,7 @@ struct State {
     if (halo_flags_d) return;
     halo_flags_d = dalloc<uint8_t>(k.n_blocks);
     halo_own = dalloc<uint8_t>(k.n_blocks);
+    halo_nbr = dalloc<uint32_t>(k.n_blocks);
     halo_cta_counts = dalloc<uint32_t>((k.n_blocks + kHaloBlocksPerCta - 1) / kHaloBlocksPerCta);
     halo_dev_words = dalloc<uint32_t>(4);
     GMPM_CUDA(cudaHostAlloc((void**)&h_halo_words, 4 * sizeof(uint32_t), cudaHostAllocDefault));
@@ -644,20 +652,23 @@ struct State {
     if (stage != GridStage::kTiles && stage != GridStage::kMomentum)
       throw std::invalid_argument(std::string(what) + " must follow ParticleToGrid and precede UpdateGrid");
   }
-  // Dilated touched flags of the current P2G.  The host all-reduces them on halo_stream.
+  // Flags of the blocks this rank can reach in the next substep (halo.cuh), built on the compute stream
+  // from the current touched list (measured: building them on the halo stream as well costs more in
+  // contention with FEM / binning than the ~15 us it takes off this stream); the host all-reduces them
+  // on the halo stream.
   uint8_t* halo_flags() {
     require_finalized();
     require_after_p2g("halo_flags");
     halo_init();
-    // the previous plan chain (side stream) still reads the flag buffers
+    // the previous plan chain (halo stream) still reads the flag buffers
     GMPM_CUDA(cudaStreamWaitEvent(stream, ev_halo_plan, 0));
     note("memset");
     GMPM_CUDA(cudaMemsetAsync(halo_flags_d, 0, k.n_blocks, stream));
     launch("halo_flags");
-    halo_flags_kernel<<<persistent_ctas(2), kThreads, 0, stream>>>(touched_list[tl_cur], ctr,
-                                                                  (uint32_t)k.domain_size >> 2,
-                                                                  halo_own_valid ? halo_own : nullptr, halo_flags_d,
-                                                                  halo_dev_words + 2);
+    halo_flags_kernel<<<persistent_ctas(2), kThreads, 0, stream>>>(
+        touched_list[tl_cur], ctr, (uint32_t)k.domain_size >> 2, halo_own_valid ? halo_own : nullptr,
+        (stage == GridStage::kMomentum && halo_nbr_epoch == p2g_epoch) ? halo_nbr : nullptr, halo_flags_d,
+        halo_dev_words + 2);
     GMPM_CUDA(cudaGetLastError());
     GMPM_CUDA(cudaMemcpyAsync(halo_own, halo_flags_d, k.n_blocks, cudaMemcpyDeviceToDevice, stream));
     halo_own_valid = true;

@@ -30,12 +30,36 @@ def dilate_blocks(flags):
     return out[bx + 1, by + 1, bz + 1]
 
 
+def reachable_blocks(mass):
+    """The library's planning rule (csrc/halo.cuh): blocks holding a cell within one CELL of a cell with
+    mass.  mass[n_cells] in block-major order -> bool[n_blocks]."""
+    n_blocks = mass.size // 64
+    side = round(n_blocks ** (1.0 / 3.0))
+    ids = np.arange(n_blocks, dtype=np.uint32)
+    bx, by, bz = _contract(ids >> 2), _contract(ids >> 1), _contract(ids)
+    occ = (mass.reshape(n_blocks, 4, 4, 4) > 0)
+    dense = np.zeros((side * 4 + 2,) * 3, bool)
+    for lx in range(4):
+        for ly in range(4):
+            for lz in range(4):
+                dense[bx * 4 + lx + 1, by * 4 + ly + 1, bz * 4 + lz + 1] = occ[:, lx, ly, lz]
+    out = np.zeros_like(dense)
+    for dx in (-1, 0, 1):
+        for dy in (-1, 0, 1):
+            for dz in (-1, 0, 1):
+                out |= np.roll(dense, (dx, dy, dz), axis=(0, 1, 2))
+    out = out[1:-1, 1:-1, 1:-1].reshape(side, 4, side, 4, side, 4).any(axis=(1, 3, 5))
+    return out[bx, by, bz]
+
+
 class OracleHaloBackend:
     def __init__(self, orc):
         self.orc = orc
         self.planned_own = None     # own dilated flags of the previous plan (containment check)
         self.next_shared = None
         self.shared = None
+        self.have_mass = False
+        self.own_mass = None
         self._flags = None
         self._packed = None
 
@@ -46,7 +70,10 @@ class OracleHaloBackend:
         touched = self._touched()
         if self.planned_own is not None:
             assert not np.any(touched & ~self.planned_own), "touched block outside the planned dilated set"
-        self.planned_own = dilate_blocks(touched)
+        if self.have_mass:      # after the first halo_pack: the tight rule, from this rank's own grid masses
+            self.planned_own = touched | reachable_blocks(self.own_mass)
+        else:                   # start-up (no assembled masses yet): full block dilation
+            self.planned_own = dilate_blocks(touched)
         self._flags = torch.from_numpy(self.planned_own.astype(np.uint8))
         return self._flags
 
@@ -56,6 +83,8 @@ class OracleHaloBackend:
     def halo_pack(self):
         self.shared = self.next_shared
         self.own = self._touched()
+        self.own_mass = self.orc.view("grid_masses").copy()   # before the sums come back
+        self.have_mass = True
         if self.shared.size == 0:
             self._packed = None
             return None
