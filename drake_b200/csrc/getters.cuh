@@ -87,6 +87,7 @@ size_t State<T>::read(const char* name, void* out, size_t cap) {
     to_host(out, buf, bytes);
     return bytes;
   }
+  if (n == "dev_counters") return plain(ctr, sizeof(DevCounters));  // instrumentation (tools/)
   if (n == "pids") return plain(pid_of_vis[vis_cur], sizeof(int) * N);
   if (n == "index_mappings") return plain(vis_of_pid, sizeof(int) * N);
   if (n == "sort_keys") {

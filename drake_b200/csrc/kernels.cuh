@@ -32,7 +32,10 @@ struct DevCounters {
   uint32_t n_big;          // work records of blocks with more particles than the average (front of pb_work)
   uint32_t n_small;        // ... the others (back of pb_work, growing down)
   uint32_t n_tiles;        // P2G tiles handed out (one per work record)
-  uint32_t pad[3];
+  uint32_t win_lo[3];      // bounding box of the particle blocks (binning window), reset by the binning kernel
+  uint32_t win_hi[3];
+  uint32_t sort_passes;    // passes the last binning sort ran (instrumentation)
+  uint32_t phase_ns[8];    // binning kernel: ns from start to the end of window / sort / ranges / records (block 0)
 };
 
 // One unit of work of the per-particle-block kernels: tile index, particle range, grid block id.
@@ -139,15 +142,25 @@ struct BinArgs {
   SortArgs sort;
   uint32_t N, epoch, work_cap;
   int roll_touched;  // binning on behalf of P2G: also do p2g_prologue_kernel's job (saves a launch)
+  int window;        // sort keys relative to the particles' bounding box (grids whose keys need > 2 passes)
+  int key_bits;      // bits of an absolute cell key
   uint32_t *pb_start, *pb_end, *pb_epoch, *pb_list;
   uint2* pb_tile;
   WorkRec* pb_work;
   DevCounters* ctr;
 };
 
+__device__ __forceinline__ uint64_t global_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs a) {
   extern __shared__ __align__(16) uint32_t sort_smem[];
   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  const bool stamp = blockIdx.x == 0 && threadIdx.x == 0;
+  const uint64_t t_begin = stamp ? global_ns() : 0;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     a.ctr->n_pblocks = 0;
     a.ctr->n_big = 0;
@@ -160,9 +173,74 @@ __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs 
       a.ctr->work_g2p = 0;
     }
   }
-  const int r = radix_sort_device(a.sort, sort_smem, grid);  // ends with a grid barrier
-  const uint32_t* sorted_key = a.sort.keys[r];
   const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+  SortWindow win{};
+  if (a.window) {
+    // bounding box of the particle blocks, per axis on the DILATED fields of the Morton block id (dilation is
+    // monotonic, so min / max need no decoding); ctr->win_* are reset at the end of the kernel
+    uint32_t lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0u, 0u, 0u};
+    for (uint32_t i = tid; i < a.N; i += nth) {
+      const uint32_t b = __ldcg(a.sort.keys_in + i) >> 6;
+      const uint32_t c[3] = {b & kMortonX, b & kMortonY, b & kMortonZ};
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        lo[d] = min(lo[d], c[d]);
+        hi[d] = max(hi[d], c[d]);
+      }
+    }
+    __shared__ uint32_t s_lo[3], s_hi[3];
+    if (threadIdx.x < 3) {
+      s_lo[threadIdx.x] = 0xFFFFFFFFu;
+      s_hi[threadIdx.x] = 0u;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      lo[d] = __reduce_min_sync(kFullMask, lo[d]);
+      hi[d] = __reduce_max_sync(kFullMask, hi[d]);
+      if ((threadIdx.x & 31) == 0) {
+        atomicMin(&s_lo[d], lo[d]);
+        atomicMax(&s_hi[d], hi[d]);
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {  // one pair of global atomics per CTA and axis
+      atomicMin(&a.ctr->win_lo[threadIdx.x], s_lo[threadIdx.x]);
+      atomicMax(&a.ctr->win_hi[threadIdx.x], s_hi[threadIdx.x]);
+    }
+    grid.sync();
+    uint32_t ext = 1;
+    uint32_t lo_d[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      lo_d[d] = __ldcg(&a.ctr->win_lo[d]);
+      const uint32_t hi_d = __ldcg(&a.ctr->win_hi[d]);
+      ext = max(ext, contract_bits(hi_d >> (2 - d)) - contract_bits(lo_d[d] >> (2 - d)) + 1u);
+    }
+    int w = 0;
+    while ((1u << w) < ext) ++w;
+    const int rel_bits = 3 * w + 6;
+    if (rel_bits < a.key_bits) {
+      win.on = true;
+      win.ox = lo_d[0];
+      win.oy = lo_d[1];
+      win.oz = lo_d[2];
+      win.n_passes = plan_sort_passes(rel_bits, win.pass);
+      win.final_buf = (a.sort.n_passes - 1) & 1;
+      if (win.n_passes >= a.sort.n_passes) win.on = false;  // no pass saved: keep the absolute keys
+    }
+  }
+  if (stamp) a.ctr->phase_ns[0] = (uint32_t)(global_ns() - t_begin);
+  win.stamp_out = stamp ? &a.ctr->phase_ns[4] : nullptr;
+  win.t0 = t_begin;
+  const int r = radix_sort_device(a.sort, sort_smem, grid, &win);  // ends with a grid barrier
+  if (stamp) a.ctr->phase_ns[1] = (uint32_t)(global_ns() - t_begin);
+  const uint32_t* sorted_key = a.sort.keys[r];
+  if (blockIdx.x == 0 && threadIdx.x == 0) a.ctr->sort_passes = win.on ? win.n_passes : a.sort.n_passes;
+  if (a.window && blockIdx.x == 0 && threadIdx.x < 3) {  // everyone has read the window: reset for the next launch
+    a.ctr->win_lo[threadIdx.x] = 0xFFFFFFFFu;
+    a.ctr->win_hi[threadIdx.x] = 0u;
+  }
   // ---- block ranges + list of particle blocks (uniform trip count: the warp-aggregated append needs all lanes)
   for (uint32_t i0 = 0; i0 < a.N; i0 += nth) {
     const uint32_t i = i0 + tid;
@@ -172,6 +250,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs 
       b = sorted_key[i] >> 6;
       head = (i == 0) || ((sorted_key[i - 1] >> 6) != b);
       const bool tail = (i + 1 == a.N) || ((sorted_key[i + 1] >> 6) != b);
+      if (win.on && (head || tail)) b = window_block_abs(b, win);  // sorted keys are window-relative
       if (head) a.pb_start[b] = i;
       if (tail) a.pb_end[b] = i + 1;
     }
@@ -188,6 +267,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs 
     }
   }
   grid.sync();
+  if (stamp) a.ctr->phase_ns[2] = (uint32_t)(global_ns() - t_begin);
   // ---- chunked work records
   const uint32_t n_pb = a.ctr->n_pblocks;
   for (uint32_t t = tid; t < n_pb; t += nth) {
@@ -205,6 +285,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs 
     if (rest)
       a.pb_work[a.work_cap - 1u - atomicAdd(&a.ctr->n_small, 1u)] = WorkRec{tile0 + n_full, b + n_full * kChunk, e, blk};
   }
+  if (stamp) a.ctr->phase_ns[3] = (uint32_t)(global_ns() - t_begin);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -61,7 +61,7 @@ inline size_t radix_sort_scratch_words(size_t n) {
 }
 
 // Splits num_bit key bits into the fewest passes of <= kMaxRadixBits, evenly.
-inline int plan_sort_passes(int num_bit, SortPass* pass) {
+__host__ __device__ inline int plan_sort_passes(int num_bit, SortPass* pass) {
   if (num_bit <= 0) return 0;
   const int n = (num_bit + kMaxRadixBits - 1) / kMaxRadixBits;
   int shift = 0;
@@ -73,21 +73,60 @@ inline int plan_sort_passes(int num_bit, SortPass* pass) {
   return n;
 }
 
+// Optional key window (binning only): the keys are cell keys; sorting them RELATIVE to the block-aligned
+// corner (ox, oy, oz) of the particles' bounding box needs 3 w + 6 bits instead of 3 domain_bits, which
+// saves a whole pass on the 256^3 and 512^3 grids of the multi-GPU scenes.  The relative key keeps the
+// block grouping and the cell order inside a block, which is all the binning needs.
+struct SortWindow {
+  bool on;
+  uint32_t ox, oy, oz;   // window origin in block coordinates, DILATED onto the Morton bit positions of its axis
+  int n_passes;          // pass plan for the relative keys (decided on the device)
+  SortPass pass[4];
+  int final_buf;         // buffer pair the result must end up in (the host's expectation)
+  uint32_t* stamp_out;   // instrumentation: ns since t0 at the end of hist / scan / scatter of pass 0 (or null)
+  unsigned long long t0;
+};
+// Morton bit positions of the three axes inside a block id (x most significant of each triple).
+constexpr uint32_t kMortonZ = 0x09249249u, kMortonY = kMortonZ << 1, kMortonX = kMortonZ << 2;
+// Per-axis subtraction / addition directly on the interleaved fields (dilated-integer arithmetic).
+__device__ __forceinline__ uint32_t morton_sub(uint32_t b, uint32_t ox, uint32_t oy, uint32_t oz) {
+  // borrows run through the zero gaps of the dilated operands
+  return (((b & kMortonX) - ox) & kMortonX) | (((b & kMortonY) - oy) & kMortonY) | (((b & kMortonZ) - oz) & kMortonZ);
+}
+__device__ __forceinline__ uint32_t morton_add(uint32_t b, uint32_t ox, uint32_t oy, uint32_t oz) {
+  return ((((b & kMortonX) | ~kMortonX) + ox) & kMortonX) | ((((b & kMortonY) | ~kMortonY) + oy) & kMortonY) |
+         ((((b & kMortonZ) | ~kMortonZ) + oz) & kMortonZ);
+}
+__device__ __forceinline__ uint32_t window_key(uint32_t key, uint32_t ox, uint32_t oy, uint32_t oz) {
+  return (morton_sub(key >> 6, ox, oy, oz) << 6) | (key & 63u);
+}
+__device__ __forceinline__ uint32_t window_block_abs(uint32_t rel_block, const SortWindow& w) {
+  return morton_add(rel_block, w.ox, w.oy, w.oz);
+}
+
 // One full sort; every thread of the cooperative grid calls it.  `smem` = kSortSmemBytes.
 // Returns the index (0 or 1) of the buffer pair that holds the result.
 __device__ __forceinline__ int radix_sort_device(const SortArgs& a, uint32_t* smem,
-                                                 cooperative_groups::grid_group& grid) {
+                                                 cooperative_groups::grid_group& grid,
+                                                 const SortWindow* win = nullptr) {
+  const bool windowed = win != nullptr && win->on;
+  const uint32_t wox = windowed ? win->ox : 0u, woy = windowed ? win->oy : 0u, woz = windowed ? win->oz : 0u;
+  const int n_passes = windowed ? win->n_passes : a.n_passes;
+  const SortPass* passes = windowed ? win->pass : a.pass;
+  // pass p writes buffer pair (p + first) & 1; `first` makes the last pass land where the host expects it
+  const int first = windowed ? ((win->final_buf - (n_passes - 1)) & 1) : 0;
   uint32_t* wh = smem;                                   // [kSortWarps][radix]
   uint32_t* sbase = smem + (size_t)kSortWarps * kMaxRadix;  // [radix] digit bases
   __shared__ uint32_t s_part[kSortWarps];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t* src_k = a.keys_in;
   const uint32_t* src_v = a.vals_in;
-  for (int p = 0; p < a.n_passes; ++p) {
-    const int shift = a.pass[p].shift;
-    const uint32_t radix = 1u << a.pass[p].bits, mask = radix - 1u;
-    uint32_t* dst_k = a.keys[p & 1];
-    uint32_t* dst_v = a.vals[p & 1];
+  for (int p = 0; p < n_passes; ++p) {
+    const int shift = passes[p].shift;
+    const uint32_t radix = 1u << passes[p].bits, mask = radix - 1u;
+    uint32_t* dst_k = a.keys[(p + first) & 1];
+    uint32_t* dst_v = a.vals[(p + first) & 1];
+    const bool remap = windowed && p == 0;  // pass 0 reads the absolute keys and carries relative ones on
     // ---- hist: hist[tile][d] = number of keys of the tile with digit d
     for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
       for (uint32_t d = threadIdx.x; d < radix; d += kSortThreads) wh[d] = 0;
@@ -98,6 +137,7 @@ __device__ __forceinline__ int radix_sort_device(const SortArgs& a, uint32_t* sm
       for (int r = 0; r < kSortItemsPerLane; ++r) {  // all loads first: one memory round trip
         const uint32_t i = wbase + r * 32 + lane;
         hk[r] = i < a.n ? __ldcg(src_k + i) : 0u;
+        if (remap) hk[r] = window_key(hk[r], wox, woy, woz);
       }
 #pragma unroll
       for (int r = 0; r < kSortItemsPerLane; ++r) {
@@ -112,6 +152,11 @@ __device__ __forceinline__ int radix_sort_device(const SortArgs& a, uint32_t* sm
       __syncthreads();
     }
     grid.sync();
+    if (win && win->stamp_out && p == 0 && blockIdx.x == 0 && threadIdx.x == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      win->stamp_out[0] = (uint32_t)(t - win->t0);
+    }
     // ---- scan: one warp per digit, exclusive over the tiles (in place, rows are contiguous);
     // totals[d] = digit count.  The row is read 8 x 32 tiles at a time before any of it is rewritten.
     {
@@ -143,6 +188,11 @@ __device__ __forceinline__ int radix_sort_device(const SortArgs& a, uint32_t* sm
       }
     }
     grid.sync();
+    if (win && win->stamp_out && p == 0 && blockIdx.x == 0 && threadIdx.x == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      win->stamp_out[1] = (uint32_t)(t - win->t0);
+    }
     // ---- scatter
     if (blockIdx.x < a.n_tiles) {
       // digit bases: exclusive scan of totals[] (every CTA computes its own copy)
@@ -186,6 +236,7 @@ __device__ __forceinline__ int radix_sort_device(const SortArgs& a, uint32_t* sm
       for (int r = 0; r < kSortItemsPerLane; ++r) {  // all loads first: one memory round trip
         const uint32_t i = wbase + r * 32 + lane;
         key[r] = i < a.n ? __ldcg(src_k + i) : 0u;
+        if (remap) key[r] = window_key(key[r], wox, woy, woz);
         val[r] = (src_v && i < a.n) ? __ldcg(src_v + i) : i;
       }
       // this tile's digit offsets (one more round trip, overlapped with phase 1)
@@ -241,10 +292,15 @@ __device__ __forceinline__ int radix_sort_device(const SortArgs& a, uint32_t* sm
       __syncthreads();
     }
     grid.sync();
+    if (win && win->stamp_out && p == 0 && blockIdx.x == 0 && threadIdx.x == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      win->stamp_out[2] = (uint32_t)(t - win->t0);
+    }
     src_k = dst_k;
     src_v = dst_v;
   }
-  return (a.n_passes - 1) & 1;
+  return (n_passes - 1 + first) & 1;
 }
 
 __global__ void __launch_bounds__(kSortThreads, 2) radix_sort_kernel(SortArgs a) {

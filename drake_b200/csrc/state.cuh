@@ -343,6 +343,12 @@ struct State {
     g_vstar = dalloc<T>((size_t)k.n_cells * 3);
     touched_epoch = dalloc<uint32_t>(k.n_blocks);
     ctr = dalloc<DevCounters>(1);
+    {
+      DevCounters init{};
+      for (int d = 0; d < 3; ++d) init.win_lo[d] = 0xFFFFFFFFu;
+      GMPM_CUDA(cudaMemcpyAsync(ctr, &init, sizeof(init), cudaMemcpyHostToDevice, stream));
+      GMPM_CUDA(cudaStreamSynchronize(stream));
+    }
 
     // upload: [faces | verts] (cuda_mpm_model.cu:40-45), planar
     std::vector<T> hp(3 * N, T(0)), hv(3 * N, T(0));
@@ -420,6 +426,8 @@ struct State {
     a.pb_work = pb_work;
     a.ctr = ctr;
     a.roll_touched = for_p2g ? 1 : 0;
+    a.key_bits = key_bits();
+    a.window = a.sort.n_passes > 2 ? 1 : 0;
     prologue_done = for_p2g;
     sres = (a.sort.n_passes - 1) & 1;
     if (bin_ctas == 0) bin_ctas = sort_grid_ctas(bin_particles_kernel, sm_count, a.sort.n_tiles);

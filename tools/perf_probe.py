@@ -15,8 +15,11 @@ def main():
     for a in sys.argv:
         if a.startswith("--sheets="):
             n_sheets = int(a.split("=")[1])
-    st = GpuMpmState(dtype)
+    big = "--grid256" in sys.argv   # the multi-GPU configuration: 256^3 cells, dx = 1/128, far octant
+    st = GpuMpmState(dtype, **({"domain_bits": 8, "dx": 1.0 / 128} if big else {}))
     for pos, vel, tri in scenes.stacked_sheets(n_sheets, dtype=dtype):
+        if big:
+            pos = (pos.astype(np.float64) + np.array([1.0, 1.0, 0.68])).astype(dtype)
         st.AddQRCloth(pos, vel, tri)
     st.Finalize()
     sv = GpuMpmSolver()
@@ -36,7 +39,7 @@ def main():
         t1 = time.perf_counter()
         print("N=%d %s steps=%d: %.3f ms/step, %.3f G particle-steps/s (wall)" %
               (N, np.dtype(dtype).name, steps, (t1 - t0) / steps * 1e3, N * steps / (t1 - t0) / 1e9))
-    print("pblocks, touched:", st.block_counts(), "device MB:", st.device_bytes() / 1e6)
+    print("pblocks, touched:", st.block_counts(), "device MB:", st.device_bytes() / 1e6, st.dev_counters())
     st.set_profiling(True)
     sv.RunSubsteps(st, 40, dt, -1, 40)
     sv.GpuSync(st)
