@@ -227,6 +227,8 @@ def main():
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-gpu", action="store_true")
+    ap.add_argument("--overlap", action="store_true",
+                    help="N>1: UpdateGrid/G2P in two parts around the exchange (interior work hides the all-reduce)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
@@ -268,7 +270,7 @@ def main():
             sv.RunSubsteps(st, n, DT, -1, SORT_EVERY)      # one ABI crossing, same calls inside
             return
         for i in range(first, first + n):                  # the exchange sits between P2G and UpdateGrid
-            slab.substep(sv, st, ex, DT, -1, i % SORT_EVERY == 0)
+            slab.substep(sv, st, ex, DT, -1, i % SORT_EVERY == 0, overlap=args.overlap)
 
     sampler = ClockSampler(local)
     sampler.start()
@@ -307,9 +309,13 @@ def main():
         sv.RebuildMapping(st, i % SORT_EVERY == 0)
         sv.CalcFemStateAndForce(st, DT)
         sv.ParticleToGrid(st, DT)
-        if ex is not None:
-            ex.exchange()
-        sv.UpdateGrid(st, -1)
+        if ex is not None:                                 # grid update overlapped with the all-reduce; the
+            ex.begin()                                     # contact stage of the driver needs the whole grid,
+            st.update_grid_part(-1, 0)                     # so G2P is not split here
+            ex.finish()
+            st.update_grid_part(-1, 1)
+        else:
+            sv.UpdateGrid(st, -1)
         ph = st.positions_host()                           # host read of this step's particle positions
         e2e_check[0] += float(ph[i % N, 2])
         if contact_ok:

@@ -215,6 +215,12 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
     });                                                                                                        \
   }                                                                                                            \
   int gmpm_halo_unpack_##SUF(gmpm_state_##SUF* s) { return guarded([&] { s->st.halo_unpack(); }); }            \
+  int gmpm_update_grid_part_##SUF(gmpm_state_##SUF* s, int bc, int part) {                                     \
+    return guarded([&] { s->st.update_grid_part(bc, part); });                                                 \
+  }                                                                                                            \
+  int gmpm_g2p_part_##SUF(gmpm_state_##SUF* s, T dt, int part) {                                               \
+    return guarded([&] { s->st.g2p_part(dt, part); });                                                         \
+  }                                                                                                            \
   int gmpm_stream_##SUF(gmpm_state_##SUF* s, void** cuda_stream) {                                             \
     return guarded([&] {                                                                                       \
       if (!cuda_stream) throw std::invalid_argument("null out pointer");                                       \

@@ -134,4 +134,11 @@ halo_pack_kernel(uint32_t n, const uint32_t* __restrict__ list, const uint32_t* 
   }
 }
 
+// mark[list[i]] = value for the first n entries (the blocks of the current exchange).
+__global__ void halo_mark_kernel(uint32_t n, const uint32_t* __restrict__ list, uint8_t value,
+                                 uint8_t* __restrict__ mark) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) mark[list[i]] = value;
+}
+
 }  // namespace gmpm

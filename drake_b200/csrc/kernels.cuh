@@ -49,6 +49,7 @@ __global__ void p2g_prologue_kernel(DevCounters* ctr) {
   ctr->n_touched = 0;
   ctr->work_p2g = 0;
   ctr->work_g2p = 0;
+  ctr->work_grid = 0;
 }
 
 
@@ -171,6 +172,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs 
       a.ctr->n_touched = 0;
       a.ctr->work_p2g = 0;
       a.ctr->work_g2p = 0;
+      a.ctr->work_grid = 0;
     }
   }
   const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
@@ -795,12 +797,15 @@ __global__ void __launch_bounds__(kThreads)
 grid_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __restrict__ ctr,
             const T* __restrict__ tiles, const uint2* __restrict__ pb_tile, const uint32_t* __restrict__ pb_epoch,
             uint32_t epoch, T* __restrict__ g_mass, T* __restrict__ g_vel, T* __restrict__ g_vstar, int bc,
-            Consts<T> k, uint32_t* __restrict__ nbr_list = nullptr) {
+            Consts<T> k, uint32_t* __restrict__ nbr_list = nullptr, const uint8_t* __restrict__ mark = nullptr,
+            int want = -1) {
+  // mark / want (multi-GPU): only blocks with mark[g] == want (0: not exchanged, 1: exchanged with other ranks)
   const uint32_t n_touched = ctr->n_touched;
   const uint32_t l = threadIdx.x & 63u;
   const uint32_t lx = (l >> 4) & 3u, ly = (l >> 2) & 3u, lz = l & 3u;
   for (uint32_t it = blockIdx.x * 4u + (threadIdx.x >> 6); it < n_touched; it += gridDim.x * 4u) {
     const uint32_t g = touched_list[it];
+    if (want >= 0 && (int)mark[g] != want) continue;
     uint32_t gx, gy, gz;
     block_coords(g, gx, gy, gz);
     T m, p[3];
@@ -933,7 +938,10 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __rest
            const T* __restrict__ g_vel, const T* __restrict__ pos, const T* __restrict__ vol,
            const int* __restrict__ pid, T* __restrict__ pos_out, T* __restrict__ vel_out, T* __restrict__ C_out,
            T* __restrict__ vol_out, int* __restrict__ pid_out, int* __restrict__ slot_of_pid,
-           uint32_t* __restrict__ key_out, T* __restrict__ forces_out, DevCounters* ctr, T dt, Consts<T> k) {
+           uint32_t* __restrict__ key_out, T* __restrict__ forces_out, DevCounters* ctr, T dt, Consts<T> k,
+           const uint8_t* __restrict__ mark = nullptr, int want = -1) {
+  // mark / want (multi-GPU): want = 0 -> only chunks whose stencils stay clear of the blocks exchanged with
+  // other ranks (they can run while the exchange is in flight), want = 1 -> only the others, -1 -> all.
   __shared__ T s_vel[kG2PWarps][2][3][kTileNodes];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t n_big = ctr->n_big, n_work = n_big + ctr->n_small;
@@ -943,15 +951,30 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __rest
   constexpr uint32_t kNone = 0xFFFFFFFFu;
   static_assert(kChunk == 128, "the slot-index rotation below assumes 4 batches per chunk");
 
+  uint32_t* queue = want == 1 ? &ctr->work_grid : &ctr->work_g2p;  // the second part has a counter of its own
   auto ticket = [&]() -> uint32_t {
     uint32_t t = 0;
-    if (lane == 0) t = atomicAdd(&ctr->work_g2p, 1u);
+    if (lane == 0) t = atomicAdd(queue, 1u);
     return t;
   };
   auto resolve = [&](uint32_t t_lane0) -> WorkRec {
-    const uint32_t t = __shfl_sync(kFullMask, t_lane0, 0);
-    if (t >= n_work) return WorkRec{kNone, 0u, 0u, 0u};
-    return pb_work[t < n_big ? t : work_cap - 1u - (t - n_big)];
+    uint32_t t = __shfl_sync(kFullMask, t_lane0, 0);
+    for (;;) {
+      if (t >= n_work) return WorkRec{kNone, 0u, 0u, 0u};
+      const WorkRec r = pb_work[t < n_big ? t : work_cap - 1u - (t - n_big)];
+      if (want < 0) return r;
+      // does the chunk reach an exchanged block?  lanes 0-7 look at the 8 blocks block + {0,1}^3
+      uint32_t bx, by, bz;
+      block_coords(r.block, bx, by, bz);
+      bx += (lane >> 2) & 1u;
+      by += (lane >> 1) & 1u;
+      bz += lane & 1u;
+      const bool hit = lane < 8 && bx < blocks_per_axis && by < blocks_per_axis && bz < blocks_per_axis &&
+                       mark[morton3(bx, by, bz)] != 0;
+      const int part = __any_sync(kFullMask, hit) ? 1 : 0;
+      if (part == want) return r;
+      t = __shfl_sync(kFullMask, ticket(), 0);  // not this launch's chunk: take the next one
+    }
   };
   // velocity nodes the chunk's stencils can reach -> shared buffer `buf` (asynchronous)
   auto stage = [&](const WorkRec& w, int buf) {
@@ -976,9 +999,11 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __rest
     }
   };
 
-  uint32_t t0 = ticket(), t1 = ticket();
-  WorkRec w = resolve(t0);
+  // (tickets are taken one at a time here: resolve() may run through the queue to its end when it filters,
+  // and a ticket taken earlier but not yet looked at would be lost)
+  WorkRec w = resolve(ticket());
   if (w.tile == kNone) return;
+  const uint32_t t1 = ticket();
   int buf = 0;
   uint32_t sidx[4], sidx_n[4] = {0u, 0u, 0u, 0u};
   stage(w, buf);

@@ -150,6 +150,7 @@ struct State {
 
   // shared-block exchange (halo.cuh)
   uint8_t *halo_flags_d = nullptr, *halo_own = nullptr;
+  uint8_t* halo_mark = nullptr;   // 1 for the blocks of the exchange in flight (part-wise UpdateGrid / G2P)
   uint32_t* halo_nbr = nullptr;   // per touched-list entry: outer-layer occupancy towards the 26 neighbours
   uint32_t halo_nbr_epoch = 0;    // P2G epoch halo_nbr was computed for
   uint32_t halo_nbr_zeroed_epoch = 0;
@@ -612,11 +613,69 @@ struct State {
         (uint32_t)N, order(), pb_work, (uint32_t)work_cap, g_vel, pos[cur], vol[cur], pid[cur], pos[nx], vel[nx], C[nx],
         vol[nx], pid[nx], slot_of_pid, key, forces, ctr, dt, k);
     GMPM_CUDA(cudaGetLastError());
+    if (halo_mark && halo_n) {  // marks of an exchange whose parts were not run separately
+      halo_mark_kernel<<<blocks_for(halo_n), kThreads, 0, stream>>>(halo_n, halo_list[halo_cur], 0, halo_mark);
+      ++launches;
+    }
     forces_zero = true;
     cur = nx;
     keys_valid = true;   // g2p wrote the key of every new slot
     bin_valid = false;
     fem_valid = false;
+  }
+
+  // ---- UpdateGrid / GridToParticle in two parts around a shared-block exchange in flight ------------
+  // part 0: grid blocks that are NOT exchanged, and the particle chunks whose stencils stay clear of exchanged
+  //         blocks: independent of the other ranks, so they run while the all-reduce is in flight;
+  // part 1: the rest, after halo_unpack.  Same results as update_grid + g2p (disjoint sets, same kernels).
+  void update_grid_part(int bc, int part) {
+    require_finalized();
+    if (part != 0 && part != 1) throw std::invalid_argument("part must be 0 or 1");
+    if (N == 0) return;
+    if (!halo_mark) halo_init();
+    assemble_momentum();
+    if (stage != GridStage::kMomentum) throw std::invalid_argument("update_grid_part must follow ParticleToGrid");
+    launch(part ? "grid_update_shared" : "grid_update_interior");
+    grid_kernel<T, false, true><<<persistent_ctas(4), kThreads, 0, stream>>>(
+        touched_list[tl_cur], ctr, tiles, pb_tile, pb_epoch, bin_epoch, g_mass, g_vel, g_vstar, bc, k, nullptr,
+        halo_mark, part);
+    GMPM_CUDA(cudaGetLastError());
+    if (part == 1) stage = GridStage::kVelocity;
+  }
+  void g2p_part(T dt, int part) {
+    require_finalized();
+    if (part != 0 && part != 1) throw std::invalid_argument("part must be 0 or 1");
+    if (N == 0) return;
+    if (!halo_mark) halo_init();
+    if (part == 0) {
+      if (stage != GridStage::kMomentum) throw std::invalid_argument("g2p_part(0) must follow update_grid_part(0)");
+      ensure_binning();
+      if (!g2p_queue_ready) {
+        note("memset");
+        GMPM_CUDA(cudaMemsetAsync(&ctr->work_g2p, 0, 2 * sizeof(uint32_t), stream));  // work_g2p, work_grid
+      }
+      g2p_queue_ready = false;
+    } else if (stage != GridStage::kVelocity) {
+      throw std::invalid_argument("g2p_part(1) must follow update_grid_part(1)");
+    }
+    launch(part ? "g2p_shared" : "g2p_interior");
+    const int nx = cur ^ 1;
+    g2p_kernel<T><<<persistent_ctas(g2p_ctas_per_sm), kG2PWarps * 32, 0, stream>>>(
+        (uint32_t)N, order(), pb_work, (uint32_t)work_cap, g_vel, pos[cur], vol[cur], pid[cur], pos[nx], vel[nx], C[nx],
+        vol[nx], pid[nx], slot_of_pid, key, forces, ctr, dt, k, halo_mark, part);
+    GMPM_CUDA(cudaGetLastError());
+    if (part == 1) {
+      if (halo_n) {  // the marks of this exchange are spent
+        launch("halo_mark");
+        halo_mark_kernel<<<blocks_for(halo_n), kThreads, 0, stream>>>(halo_n, halo_list[halo_cur], 0, halo_mark);
+        GMPM_CUDA(cudaGetLastError());
+      }
+      forces_zero = true;
+      cur = nx;
+      keys_valid = true;
+      bin_valid = false;
+      fem_valid = false;
+    }
   }
 
   // ---- multi-GPU shared-block exchange (halo.cuh) ---------------------------------------------------
@@ -627,6 +686,7 @@ struct State {
     halo_flags_d = dalloc<uint8_t>(k.n_blocks);
     halo_own = dalloc<uint8_t>(k.n_blocks);
     halo_nbr = dalloc<uint32_t>(k.n_blocks);
+    halo_mark = dalloc<uint8_t>(k.n_blocks);
     halo_cta_counts = dalloc<uint32_t>((k.n_blocks + kHaloBlocksPerCta - 1) / kHaloBlocksPerCta);
     halo_dev_words = dalloc<uint32_t>(4);
     GMPM_CUDA(cudaHostAlloc((void**)&h_halo_words, 4 * sizeof(uint32_t), cudaHostAllocDefault));
@@ -734,6 +794,8 @@ struct State {
     GMPM_CUDA(cudaStreamWaitEvent(stream, ev_halo_plan, 0));
     assemble_momentum();
     if (n) {
+      launch("halo_mark");
+      halo_mark_kernel<<<blocks_for(n), kThreads, 0, stream>>>(n, halo_list[slot], 1, halo_mark);
       launch("halo_pack");
       halo_pack_kernel<T, false><<<std::min<uint32_t>(n, persistent_ctas(8)), kHaloThreads, 0, stream>>>(
           n, halo_list[slot], touched_epoch, p2g_epoch, g_mass, g_vel, halo_packed);

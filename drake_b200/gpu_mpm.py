@@ -210,6 +210,12 @@ class GpuMpmState:
     def halo_unpack(self):
         check(self._f("halo_unpack")(self._h))
 
+    def update_grid_part(self, mpm_bc, part):
+        check(self._f("update_grid_part")(self._h, int(mpm_bc), int(part)))
+
+    def g2p_part(self, dt, part):
+        check(self._f("g2p_part")(self._h, self._ct(dt), int(part)))
+
     # --- host mirrors
     def positions_host(self):
         """cuda_mpm_model.cuh:116-117.  Waits for the snapshot SyncParticleStateToCpu started and returns

@@ -98,6 +98,7 @@ class SlabExchange:
         self.planned = False
         self.last_n_shared = 0
         self.bytes_reduced = 0
+        self._work = None
 
     def _all_reduce(self, t, stream):
         if stream is not None:
@@ -114,17 +115,43 @@ class SlabExchange:
         self.backend.halo_plan_async()
         self.planned = True
 
-    def exchange(self):
-        """Call between ParticleToGrid and UpdateGrid, on every rank."""
+    def begin(self):
+        """After ParticleToGrid: pack this rank's share of the shared blocks and START their all-reduce.
+        Work that does not depend on other ranks (update_grid_part(0), g2p_part(0)) goes between begin()
+        and finish() and runs while the collective is in flight."""
         if not self.planned:
             self._plan()                          # start-up: plan from the current (dilated) touched set
         packed = self.backend.halo_pack()         # every rank holds the same shared-block list
         self.last_n_shared = 0 if packed is None else packed.numel() // 256
+        self._work = None
         if packed is not None:
-            self._all_reduce(packed, self.stream)
+            if self.stream is not None:
+                import torch
+                with torch.cuda.stream(self.stream):
+                    self._work = self.dist.all_reduce(packed, op=self.dist.ReduceOp.SUM, group=self.group, async_op=True)
+            else:
+                self._work = self.dist.all_reduce(packed, op=self.dist.ReduceOp.SUM, group=self.group, async_op=True)
+            self.bytes_reduced += packed.numel() * packed.element_size()
+        return self.last_n_shared
+
+    def finish(self):
+        """Orders the state's stream after the all-reduce, writes the sums back, plans the next exchange."""
+        if self._work is not None:
+            if self.stream is not None:
+                import torch
+                with torch.cuda.stream(self.stream):
+                    self._work.wait()             # stream-ordered: the host does not block
+            else:
+                self._work.wait()
+            self._work = None
         self.backend.halo_unpack()
         self._plan()                              # for the next substep, off the critical path
-        return self.last_n_shared
+
+    def exchange(self):
+        """Call between ParticleToGrid and UpdateGrid, on every rank (no overlap: begin + finish)."""
+        n = self.begin()
+        self.finish()
+        return n
 
 
 class InProcessExchange:
@@ -153,28 +180,49 @@ class InProcessExchange:
             b.halo_plan_async()
         self.planned = True
 
-    def exchange(self):
+    def begin(self):
         if not self.planned:
             self._plan()
-        packed = [b.halo_pack() for b in self.backends]
-        n = 0 if packed[0] is None else packed[0].numel() // 256
+        self._packed = [b.halo_pack() for b in self.backends]
+        return 0 if self._packed[0] is None else self._packed[0].numel() // 256
+
+    def finish(self):
         self.sync()
-        if n:
-            self._sum(packed)
+        if self._packed[0] is not None:
+            self._sum(self._packed)
         self.sync()
         for b in self.backends:
             b.halo_unpack()
         self._plan()
+
+    def exchange(self):
+        n = self.begin()
+        self.finish()
         return n
 
 
-def substep(solver, state, exchange, dt, mpm_bc=-1, sort=False):
+def substep(solver, state, exchange, dt, mpm_bc=-1, sort=False, overlap=False):
     """One no-contact substep of the driver loop (deformable_driver.h:240-260 / cuda_mpm_test.cc:66-72)
-    on this rank's part of the scene, with the exchange between P2G and the grid update."""
+    on this rank's part of the scene.  With `overlap`, UpdateGrid and GridToParticle run in two parts
+    around the exchange: everything that does not touch an exchanged block while the all-reduce is in
+    flight, the rest after it (same result as the plain order).  Measured on 2 B200s (1M particles per
+    rank): the all-reduce (~35 us) disappears from the critical path, but running G2P as two launches
+    costs ~30 us (a chunk of 128 particles is ~25 us of work for its warp, so the second, smaller launch
+    is all tail), so the plain order is the default; the split pays once the collective is slower than that."""
     solver.RebuildMapping(state, sort)
     solver.CalcFemStateAndForce(state, dt)
     solver.ParticleToGrid(state, dt)
-    if exchange is not None:
+    if exchange is None:
+        solver.UpdateGrid(state, mpm_bc)
+        solver.GridToParticle(state, dt)
+    elif overlap:
+        exchange.begin()
+        state.update_grid_part(mpm_bc, 0)
+        state.g2p_part(dt, 0)
+        exchange.finish()
+        state.update_grid_part(mpm_bc, 1)
+        state.g2p_part(dt, 1)
+    else:
         exchange.exchange()
-    solver.UpdateGrid(state, mpm_bc)
-    solver.GridToParticle(state, dt)
+        solver.UpdateGrid(state, mpm_bc)
+        solver.GridToParticle(state, dt)

@@ -161,6 +161,13 @@ int gmpm_device_sync(void);
   int gmpm_halo_plan_async_##SUF(gmpm_state_##SUF* s);                                              \
   int gmpm_halo_pack_##SUF(gmpm_state_##SUF* s, uint32_t* n_shared, void** packed_dev);             \
   int gmpm_halo_unpack_##SUF(gmpm_state_##SUF* s);                                                  \
+  /* UpdateGrid and GridToParticle in two parts, to hide the all-reduce of the exchange: part 0 =    */\
+  /* the blocks that are not exchanged and the particles whose stencils stay clear of exchanged     */\
+  /* blocks (run between halo_pack and halo_unpack, while the all-reduce is in flight), part 1 = the */\
+  /* rest (after halo_unpack).  Order: update(0) g2p(0) [unpack] update(1) g2p(1); the result is     */\
+  /* that of gmpm_update_grid + gmpm_g2p.                                                            */\
+  int gmpm_update_grid_part_##SUF(gmpm_state_##SUF* s, int mpm_bc, int part);                       \
+  int gmpm_g2p_part_##SUF(gmpm_state_##SUF* s, T dt, int part);                                     \
   /* The cudaStream_t all work of this state is issued on, and the side stream of the halo planning  */\
   /* (for stream-ordered collectives). */                                                           \
   int gmpm_stream_##SUF(gmpm_state_##SUF* s, void** cuda_stream);                                   \

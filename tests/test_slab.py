@@ -176,6 +176,71 @@ def test_two_states_one_gpu_match_single_state_and_oracle(dtype, tol):
 
 
 @pytest.mark.gpu
+def test_two_states_one_gpu_overlapped_parts_match_plain_order():
+    """UpdateGrid / GridToParticle split around the exchange (interior first, exchanged blocks after the
+    sums are back) gives the same particles as the plain order; alone, part 0 is everything."""
+    from drake_b200.gpu_mpm import GpuMpmSolver
+    import torch
+    dtype = np.float64
+    sheets = sheets_scene(dtype)
+    sv = GpuMpmSolver()
+    parts = slab.partition_meshes(len(sheets), 2)
+
+    def run(overlap):
+        sts = [make_state(dtype, [sheets[i] for i in p]) for p in parts]
+
+        def sync_all():
+            for s in sts:
+                sv.GpuSync(s)
+            torch.cuda.synchronize()
+
+        ex = slab.InProcessExchange([slab.GpuHaloBackend(s) for s in sts], sync=sync_all)
+        shared = 0
+        for it in range(10):
+            for s in sts:
+                sv.RebuildMapping(s, it == 4)
+                sv.CalcFemStateAndForce(s, DT)
+                sv.ParticleToGrid(s, DT)
+            if overlap:
+                shared += ex.begin()
+                for s in sts:
+                    s.update_grid_part(-1, 0)
+                    s.g2p_part(DT, 0)
+                ex.finish()
+                for s in sts:
+                    s.update_grid_part(-1, 1)
+                    s.g2p_part(DT, 1)
+            else:
+                shared += ex.exchange()
+                for s in sts:
+                    sv.UpdateGrid(s, -1)
+                    sv.GridToParticle(s, DT)
+        assert shared > 0
+        return [(s.read("positions"), s.read("velocities"), s.read("affine_matrices")) for s in sts]
+
+    a, b = run(False), run(True)       # (vertex forces are summed with atomics: equal to rounding, not bitwise)
+    for ra, rb in zip(a, b):
+        for x, y in zip(ra, rb):
+            assert np.max(np.abs(x - y)) <= 1e-9 * max(1.0, np.max(np.abs(x)))
+    # a state that exchanges nothing: the two parts together are the plain calls
+    st1, st2 = make_state(dtype, sheets), make_state(dtype, sheets)
+    for it in range(3):
+        for st in (st1, st2):
+            sv.RebuildMapping(st, False)
+            sv.CalcFemStateAndForce(st, DT)
+            sv.ParticleToGrid(st, DT)
+        sv.UpdateGrid(st1, -1)
+        sv.GridToParticle(st1, DT)
+        st2.update_grid_part(-1, 0)
+        st2.g2p_part(DT, 0)
+        st2.update_grid_part(-1, 1)
+        st2.g2p_part(DT, 1)
+    assert np.max(np.abs(st1.read("positions") - st2.read("positions"))) <= 1e-13
+    c1, c2 = st1.read("affine_matrices"), st2.read("affine_matrices")
+    assert np.max(np.abs(c1 - c2)) <= 1e-9 * max(1.0, np.max(np.abs(c1)))
+
+
+@pytest.mark.gpu
 def test_halo_call_order_is_checked():
     from drake_b200.gpu_mpm import GmpmError, GpuMpmSolver
     st = make_state(np.float64, sheets_scene(np.float64, n_sheets=1))
@@ -215,7 +280,7 @@ def _nccl_worker(rank, world, port, ret):
         ex = slab.SlabExchange(slab.GpuHaloBackend(st))
         shared = 0
         for it in range(20):
-            slab.substep(sv, st, ex, DT, -1, it == 7)
+            slab.substep(sv, st, ex, DT, -1, it == 7, overlap=(it % 2 == 1))   # both orders
             shared += ex.last_n_shared
         got, _ = st.DumpCpuState()
         full = make_oracle(dtype, sheets)
