@@ -227,6 +227,7 @@ def main():
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-gpu", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--overlap", action="store_true",
                     help="N>1: UpdateGrid/G2P in two parts around the exchange (interior work hides the all-reduce)")
     args = ap.parse_args()
@@ -245,6 +246,10 @@ def main():
     if world > 1:
         import torch.distributed as dist_mod
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # the two all-reduces per substep are small (<= 4 MB) and latency bound: the low-latency protocol on the
+        # ring measured fastest on 8 B200s (0.606 vs 0.626 ms/substep with NCCL's own choice; NVLS rejects f64)
+        os.environ.setdefault("NCCL_ALGO", "Ring")
+        os.environ.setdefault("NCCL_PROTO", "LL")
         dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
         dist = dist_mod
 
@@ -265,12 +270,16 @@ def main():
         from drake_b200 import slab
         ex = slab.SlabExchange(slab.GpuHaloBackend(st))
 
+    # interior UpdateGrid/G2P work hides the all-reduce; pays off once the collective is slow (measured: loses
+    # 20 us at 2 ranks, wins 18 us at 8)
+    overlap = args.overlap or (world >= 8 and not args.no_overlap)
+
     def run_substeps(n, first=0):
         if ex is None:
             sv.RunSubsteps(st, n, DT, -1, SORT_EVERY)      # one ABI crossing, same calls inside
             return
         for i in range(first, first + n):                  # the exchange sits between P2G and UpdateGrid
-            slab.substep(sv, st, ex, DT, -1, i % SORT_EVERY == 0, overlap=args.overlap)
+            slab.substep(sv, st, ex, DT, -1, i % SORT_EVERY == 0, overlap=overlap)
 
     sampler = ClockSampler(local)
     sampler.start()
@@ -397,7 +406,8 @@ def main():
                            "parallelism": "single GPU" if world == 1 else
                            "%d ranks, one 34-sheet stack each of one scene on a 256^3 grid (dx = 1/128); grid blocks "
                            "reached by two ranks are summed every substep: all-reduce of block flags + all-reduce of "
-                           "%d shared blocks (%.0f KB/step) over NCCL" % (world, halo_blocks, halo_bytes_per_step / 1e3)},
+                           "%d shared blocks (%.0f KB/step) over NCCL%s" % (world, halo_blocks, halo_bytes_per_step / 1e3,
+                                                                           ", overlapped with interior G2P" if overlap else "")},
                 "clocks": clocks,
                 "e2e": {"value": N_all * Ke / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0,
                         "d2h_bytes_per_step": int(3 * T * N), "steps": Ke, "ms_per_step": e_ms / Ke,
