@@ -21,6 +21,12 @@ class Params(C.Structure):
                 ("sdf_friction", C.c_double), ("gravity", C.c_double), ("epsv", C.c_double), ("dx", C.c_double)]
 
 
+class AnalyticGeometry(C.Structure):
+    """Mirror of gmpm_analytic_geometry."""
+    _fields_ = [("kind", C.c_int), ("rigid_id", C.c_uint32), ("lo", C.c_double * 3), ("hi", C.c_double * 3),
+                ("velocity", C.c_double * 3), ("p_WB", C.c_double * 3)]
+
+
 class ContactStats(C.Structure):
     _fields_ = [("iterations", C.c_int), ("grid_dofs", C.c_int), ("line_search_evals", C.c_int),
                 ("reserved", C.c_int), ("residual", C.c_double), ("energy", C.c_double)]
@@ -32,7 +38,7 @@ PLAIN_SYMBOLS = ["gmpm_default_params", "gmpm_last_error", "gmpm_version", "gmpm
 TYPED_SYMBOLS = ["create", "destroy", "add_qr_cloth", "finalize", "rebuild_mapping", "calc_fem", "p2g",
                  "update_grid", "g2p", "sync", "sync_particle_state_to_cpu", "sync_particle_state_to_cpu_async",
                  "positions_host", "halo_flags", "halo_plan_async", "halo_pack", "halo_unpack", "update_grid_part", "g2p_part", "stream", "halo_stream", "copy_contact_pairs",
-                 "update_contact", "reallocate_external_bodies", "external_body_force_to_host",
+                 "generate_contact_pairs", "update_contact", "reallocate_external_bodies", "external_body_force_to_host",
                  "dump_cpu_state", "n_verts", "n_faces", "n_particles", "n_cells", "num_contacts",
                  "grid_touched_cnt_host", "read", "run_substeps", "kernel_launches", "set_profiling",
                  "kernel_time", "profile_report", "timer_mark", "timer_elapsed_ms", "device_bytes",
@@ -94,6 +100,7 @@ def _declare(L):
         g("stream").argtypes = [vp, C.POINTER(C.c_void_p)]
         g("halo_stream").argtypes = [vp, C.POINTER(C.c_void_p)]
         g("copy_contact_pairs").argtypes = [vp, sz] + [vp] * 7
+        g("generate_contact_pairs").argtypes = [vp, C.POINTER(AnalyticGeometry), sz, C.POINTER(C.c_size_t)]
         g("update_contact").argtypes = [vp, ct, ct, ct, ct, C.c_int, C.c_int, C.POINTER(ContactStats)]
         g("reallocate_external_bodies").argtypes = [vp, sz]
         g("external_body_force_to_host").argtypes = [vp, vp, vp]

@@ -141,6 +141,14 @@ size_t State<T>::read(const char* name, void* out, size_t cap) {
   if (n == "contact_vel") return plain(c_vel, sizeof(T) * 3 * n_contacts);
   if (n == "contact_vel0") return plain(c_vel0, sizeof(T) * 3 * n_contacts);
   if (n == "contact_sort_keys") return plain(c_keys, sizeof(uint32_t) * n_contacts);
+  // the contact-pair arrays as uploaded by CopyContactPairs or produced by gmpm_generate_contact_pairs
+  if (n == "contact_mpm_id") return plain(c_pid, sizeof(uint32_t) * n_contacts);
+  if (n == "contact_rigid_id") return plain(c_rigid_id, sizeof(uint32_t) * n_contacts);
+  if (n == "contact_dist") return plain(c_dist, sizeof(T) * n_contacts);
+  if (n == "contact_normal") return plain(c_normal, sizeof(T) * 3 * n_contacts);
+  if (n == "contact_pos") return plain(c_pos, sizeof(T) * 3 * n_contacts);
+  if (n == "contact_rigid_v") return plain(c_rigid_v, sizeof(T) * 3 * n_contacts);
+  if (n == "contact_rigid_p") return plain(c_rigid_p, sizeof(T) * 3 * n_contacts);
   throw std::out_of_range("gmpm_read: unknown buffer name '" + n + "'");
 }
 

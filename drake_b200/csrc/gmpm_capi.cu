@@ -4,6 +4,7 @@
 #define GMPM_STR(x) GMPM_STR2(x)
 
 #include "contact.cuh"
+#include "contact_gen.cuh"
 #include "getters.cuh"
 #include "state.cuh"
 
@@ -171,6 +172,13 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
                                     const uint32_t* rigid_id, const T* dist, const T* normal, const T* pos,    \
                                     const T* rigid_v, const T* rigid_p) {                                      \
     return guarded([&] { s->st.copy_contact_pairs(n, mpm_id, rigid_id, dist, normal, pos, rigid_v, rigid_p); });\
+  }                                                                                                            \
+  int gmpm_generate_contact_pairs_##SUF(gmpm_state_##SUF* s, const gmpm_analytic_geometry* geoms, size_t n_geoms,\
+                                        size_t* n_pairs) {                                                     \
+    return guarded([&] {                                                                                       \
+      const size_t n = s->st.generate_contact_pairs(geoms, n_geoms);                                           \
+      if (n_pairs) *n_pairs = n;                                                                               \
+    });                                                                                                        \
   }                                                                                                            \
   int gmpm_update_contact_##SUF(gmpm_state_##SUF* s, T dt, T mu, T stiffness, T damping, int exact, int max_it,\
                                 gmpm_contact_stats* stats) {                                                   \

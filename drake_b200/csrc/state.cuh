@@ -147,6 +147,11 @@ struct State {
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_gather = nullptr, ev_copy = nullptr;
   bool copy_pending = false;
+  bool snapshot_valid = false;  // pos_stage holds the positions of the current substep (cleared by g2p)
+  // device-side contact generation (contact_gen.cuh)
+  uint32_t* gen_counts = nullptr;
+  unsigned char* gen_geoms = nullptr;
+  uint32_t gen_cap = 0;
 
   // shared-block exchange (halo.cuh)
   uint8_t *halo_flags_d = nullptr, *halo_own = nullptr;
@@ -620,6 +625,7 @@ struct State {
     forces_zero = true;
     cur = nx;
     keys_valid = true;   // g2p wrote the key of every new slot
+    snapshot_valid = false;
     bin_valid = false;
     fem_valid = false;
   }
@@ -675,6 +681,7 @@ struct State {
       keys_valid = true;
       bin_valid = false;
       fem_valid = false;
+      snapshot_valid = false;
     }
   }
 
@@ -903,6 +910,7 @@ struct State {
     GMPM_CUDA(cudaMemcpyAsync(h_pos_mirror, pos_stage, sizeof(T) * 3 * N, cudaMemcpyDeviceToHost, copy_stream));
     GMPM_CUDA(cudaEventRecord(ev_copy, copy_stream));
     copy_pending = true;
+    snapshot_valid = true;
   }
   // Blocks until the last positions_async() copy has landed; returns the pinned mirror (3N, visible order).
   const T* wait_positions() {
@@ -949,6 +957,7 @@ struct State {
   void reallocate_external_bodies(size_t n);
   void external_body_force_to_host(T* tau, T* f);
   void reallocate_contacts(size_t n);
+  size_t generate_contact_pairs(const gmpm_analytic_geometry* geoms, size_t n_geoms);
   T* contact_grid_dense(const T* src, int comps);
   void dfree(void* p);
 };

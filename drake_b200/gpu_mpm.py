@@ -126,7 +126,9 @@ _BUFFERS = {
     "grid_momentum": ("T", "cells", 3), "grid_v_star": ("T", "cells", 3), "grid_touched_flags": ("u", "blocks", 1),
     "grid_touched_ids": ("u", "blocks", 1), "grid_Hess": ("T", "cells", 9), "grid_Grad": ("T", "cells", 3),
     "grid_Dir": ("T", "cells", 3), "contact_vel": ("T", "Nc", 3), "contact_vel0": ("T", "Nc", 3),
-    "contact_sort_keys": ("u", "Nc", 1),
+    "contact_sort_keys": ("u", "Nc", 1), "contact_mpm_id": ("u", "Nc", 1), "contact_rigid_id": ("u", "Nc", 1),
+    "contact_dist": ("T", "Nc", 1), "contact_normal": ("T", "Nc", 3), "contact_pos": ("T", "Nc", 3),
+    "contact_rigid_v": ("T", "Nc", 3), "contact_rigid_p": ("T", "Nc", 3),
 }
 
 
@@ -381,6 +383,25 @@ class GpuMpmSolver:
         keep = [a.astype(state.dtype, copy=False) for a in (dist, nrm, pos, rv, rp)]
         keep = [np.ascontiguousarray(a) for a in keep]
         check(state._f("copy_contact_pairs")(state._h, ids.size, _ptr(ids), _ptr(rid), *[_ptr(a) for a in keep]))
+
+    def GenerateContactPairs(self, state, geometries):
+        """Device-side CalcMpmContactPairs + CopyContactPairs for analytic rigid geometry (boxes, spheres):
+        `geometries` = list of dicts {kind: "box"|"sphere", rigid_id, lo, hi | center, radius, velocity, p_WB}.
+        Returns the number of pairs; UpdateContact follows as after CopyContactPairs."""
+        arr = (_lib.AnalyticGeometry * max(1, len(geometries)))()
+        for a, g in zip(arr, geometries):
+            sphere = g.get("kind", "box") == "sphere"
+            a.kind = 1 if sphere else 0
+            a.rigid_id = int(g["rigid_id"])
+            lo = g["center"] if sphere else g["lo"]
+            hi = (g["radius"], 0.0, 0.0) if sphere else g["hi"]
+            vel = g.get("velocity", (0.0, 0.0, 0.0))
+            pwb = g.get("p_WB", lo if sphere else [0.5 * (x + y) for x, y in zip(lo, hi)])
+            for d in range(3):
+                a.lo[d], a.hi[d], a.velocity[d], a.p_WB[d] = float(lo[d]), float(hi[d]), float(vel[d]), float(pwb[d])
+        n = C.c_size_t()
+        check(state._f("generate_contact_pairs")(state._h, arr, len(geometries), C.byref(n)))
+        return n.value
 
     def UpdateContact(self, state, frame, substep, dt, friction_mu, stiffness, damping, dump=False,
                       exact_line_search=False, max_iterations=0):

@@ -71,6 +71,16 @@ typedef struct gmpm_contact_stats {
   double energy;         /* last accepted E1 (:531)                                            */
 } gmpm_contact_stats;
 
+/* Analytic rigid geometry for device-side contact-pair generation (gmpm_generate_contact_pairs). */
+enum { GMPM_GEOM_BOX = 0, GMPM_GEOM_SPHERE = 1 };
+typedef struct gmpm_analytic_geometry {
+  int kind;            /* GMPM_GEOM_BOX: axis-aligned [lo, hi];  GMPM_GEOM_SPHERE: centre lo, radius hi[0]   */
+  uint32_t rigid_id;   /* MpmParticleContactPairs::non_mpm_id (cpu_mpm_model.h:77)                        */
+  double lo[3], hi[3];
+  double velocity[3];  /* rigid_v: velocity of the body at the contact points (translating body)          */
+  double p_WB[3];      /* rigid_p_WB: body origin, the lever arm reference of the contact torque           */
+} gmpm_analytic_geometry;
+
 void gmpm_default_params(gmpm_params* p);
 const char* gmpm_last_error(void);
 /* Library build string, e.g. "gmpm_b200 sm_100a". */
@@ -116,6 +126,13 @@ int gmpm_device_sync(void);
   int gmpm_copy_contact_pairs_##SUF(gmpm_state_##SUF* s, size_t n, const uint32_t* mpm_id,          \
                                     const uint32_t* rigid_id, const T* dist, const T* normal,       \
                                     const T* pos, const T* rigid_v, const T* rigid_p_WB);           \
+  /* Replaces DeformableDriver::CalcMpmContactPairs + CopyContactPairs (deformable_driver.h:120-194,   */\
+  /* cuda_mpm_solver.cu:194-212) when every rigid geometry is an analytic box or sphere: the pairs     */\
+  /* are generated on the device from the last SyncParticleStateToCpu snapshot, in the order the host  */\
+  /* loop would produce them (geometry by geometry, particles in visible order), with                  */\
+  /* penetration_distance = signed distance < 0 and normal = -gradient.  *n_pairs <- number of pairs.  */\
+  int gmpm_generate_contact_pairs_##SUF(gmpm_state_##SUF* s, const gmpm_analytic_geometry* geoms,   \
+                                        size_t n_geoms, size_t* n_pairs);                           \
   /* GpuMpmSolver<T>::UpdateContact, cuda_mpm_solver.cu:215-621.  max_iterations <= 0 -> 2000. */   \
   int gmpm_update_contact_##SUF(gmpm_state_##SUF* s, T dt, T friction_mu, T stiffness, T damping,   \
                                 int exact_line_search, int max_iterations,                          \
@@ -138,7 +155,9 @@ int gmpm_device_sync(void);
   /* without the current_ prefix: positions velocities volumes affine_matrices pids sort_keys     */\
   /* sort_ids forces taus index_mappings indices Dm_inverses deformation_gradients grid_masses    */\
   /* grid_momentum grid_v_star grid_touched_flags grid_touched_ids grid_Hess grid_Grad grid_Dir   */\
-  /* contact_vel contact_vel0 contact_sort_keys.  *bytes_written <- size; fails if cap too small. */\
+  /* contact_vel contact_vel0 contact_sort_keys contact_mpm_id contact_rigid_id contact_dist        */\
+  /* contact_normal contact_pos contact_rigid_v contact_rigid_p.  *bytes_written <- size; fails if  */\
+  /* cap too small.                                                                                   */\
   int gmpm_read_##SUF(gmpm_state_##SUF* s, const char* name, void* out, size_t cap_bytes,           \
                       size_t* bytes_written);                                                       \
   /* ---- multi-GPU extension (not in the reference: settings.h:40 G_DEVICE_COUNT = 1 is unused). ---- */\

@@ -254,3 +254,65 @@ def test_contact_oracle_pinned_against_reference_kernels(exact, mu):
     assert rel(f_o.reshape(-1, 3), f_r, 1e-12) <= tol_f
     assert rel(tau_o.reshape(-1, 3), tau_r, 1e-12) <= tol_f
     ref.close()
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_device_generated_pairs_equal_the_host_path(dtype):
+    """gmpm_generate_contact_pairs against the host loop it replaces: positions_host() ->
+    analytic signed-distance query per geometry and particle -> CopyContactPairs.  Same pairs, same order,
+    same values; the solves that follow agree."""
+    geoms = [{"kind": "box", "rigid_id": 1, "lo": BOX[0], "hi": BOX[1], "velocity": (0.0, 0.0, 0.05)},
+             {"kind": "sphere", "rigid_id": 2, "center": (0.45, 0.5, 0.52), "radius": 0.05, "velocity": (0.0, 0.0, -0.1)}]
+
+    def host_pairs(ph):
+        out = [scenes.box_contacts(ph, BOX[0], BOX[1], rigid_id=1, rigid_v=(0.0, 0.0, 0.05))]
+        c, r = np.array(geoms[1]["center"]), geoms[1]["radius"]
+        x = np.asarray(ph, dtype).reshape(-1, 3)          # the device evaluates in the state's scalar type
+        rel = x - c.astype(dtype)
+        ln = np.sqrt((rel * rel).sum(axis=1, dtype=dtype)).astype(dtype)
+        idx = np.nonzero(ln < dtype(r))[0]
+        n = len(idx)
+        grad = rel[idx] / ln[idx, None]
+        out.append((idx.astype(np.uint32), np.full(n, 2, np.uint32), ln[idx] - dtype(r), -grad, x[idx],
+                    np.tile(np.array([0.0, 0.0, -0.1]), (n, 1)), np.tile(c, (n, 1))))
+        return out
+
+    runs = []
+    for device_side in (False, True):
+        st = GpuMpmState(dtype)
+        for pos, vel, tri in sheet_over_box(dtype):
+            st.AddQRCloth(pos, vel, tri)
+        st.Finalize()
+        st.ReallocateExternelBodies(3)
+        sv = GpuMpmSolver()
+        for it in range(3):
+            sv.SyncParticleStateToCpu(st)
+            sv.RebuildMapping(st, it == 1)
+            sv.CalcFemStateAndForce(st, DT)
+            sv.ParticleToGrid(st, DT)
+            sv.UpdateGrid(st, -1)
+            if device_side:
+                n = sv.GenerateContactPairs(st, geoms)
+            else:
+                pairs = MpmParticleContactPairs(dtype)
+                for c in host_pairs(st.positions_host()):
+                    pairs.extend(*c)
+                sv.CopyContactPairs(st, pairs)
+                n = pairs.size()
+            assert n > 50
+            arrays = {k: st.read(k) for k in ("contact_mpm_id", "contact_rigid_id", "contact_dist", "contact_normal",
+                                              "contact_pos", "contact_rigid_v", "contact_rigid_p")}
+            stats = sv.UpdateContact(st, 0, it, DT, 0.3, 1e6, 1e-5, False, False, 3)
+            sv.GridToParticle(st, DT)
+            runs.append((n, arrays, stats.iterations, st.read("positions")))
+    half = len(runs) // 2
+    for (n_h, a_h, it_h, p_h), (n_d, a_d, it_d, p_d) in zip(runs[:half], runs[half:]):
+        assert n_h == n_d and it_h == it_d
+        for k in a_h:
+            if k in ("contact_mpm_id", "contact_rigid_id"):
+                assert np.array_equal(a_h[k], a_d[k]), k       # same pairs in the same order
+            else:
+                # two separate runs (vertex forces are summed with atomics) and FMA contraction of |x - c|:
+                # equal to rounding
+                assert rel(a_d[k], a_h[k], 1e-3) <= (1e-12 if dtype == np.float64 else 1e-4), k   # f32: one ulp of x ~ 0.5 on |dist| ~ 1e-3
+        assert rel(p_d, p_h) <= (1e-12 if dtype == np.float64 else 1e-5)

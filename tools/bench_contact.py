@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--exact", action="store_true")
     ap.add_argument("--f32", action="store_true")
+    ap.add_argument("--device-pairs", action="store_true",
+                    help="generate the contact pairs on the device (gmpm_generate_contact_pairs) instead of on the host")
     ap.add_argument("--mu", type=float, default=1.0)
     ap.add_argument("--stiffness", type=float, default=1e6)
     ap.add_argument("--damping", type=float, default=1e-5)
@@ -58,21 +60,31 @@ def main():
         sv.CalcFemStateAndForce(st, DT)
         sv.ParticleToGrid(st, DT)
         sv.UpdateGrid(st, -1)
-        ph = st.positions_host()
         h0 = time.perf_counter()
-        pairs = MpmParticleContactPairs(dtype)
-        for b in range(2):
-            c = centers[b] + pad_v[b] * DT * i
-            pairs.extend(*scenes.box_contacts(ph, c - half, c + half, rigid_id=b + 1, rigid_v=pad_v[b], rigid_p_WB=c))
-        host_ms.append((time.perf_counter() - h0) * 1e3)
-        sv.CopyContactPairs(st, pairs)
+        if args.device_pairs:
+            geoms = []
+            for b in range(2):
+                c = centers[b] + pad_v[b] * DT * i
+                geoms.append({"kind": "box", "rigid_id": b + 1, "lo": c - half, "hi": c + half, "velocity": pad_v[b], "p_WB": c})
+            n_now = sv.GenerateContactPairs(st, geoms)
+            host_ms.append((time.perf_counter() - h0) * 1e3)
+        else:
+            ph = st.positions_host()
+            h0 = time.perf_counter()
+            pairs = MpmParticleContactPairs(dtype)
+            for b in range(2):
+                c = centers[b] + pad_v[b] * DT * i
+                pairs.extend(*scenes.box_contacts(ph, c - half, c + half, rigid_id=b + 1, rigid_v=pad_v[b], rigid_p_WB=c))
+            host_ms.append((time.perf_counter() - h0) * 1e3)
+            sv.CopyContactPairs(st, pairs)
+            n_now = pairs.size()
         st.timer_mark(0)
         stats = sv.UpdateContact(st, 0, i, DT, args.mu, args.stiffness, args.damping, False, args.exact)
         st.timer_mark(1)
         sv.GridToParticle(st, DT)
         solve_ms.append(st.timer_elapsed_ms(0, 1))
         iters.append(stats.iterations)
-        n_pairs.append(pairs.size())
+        n_pairs.append(n_now)
     sv.GpuSync(st)
     wall = time.perf_counter() - t_begin
     st.ExternelBodyForceToHost()
@@ -85,7 +97,8 @@ def main():
             "contact_pairs_mean": float(np.mean(n_pairs)), "newton_iterations_mean": float(np.mean(iters)),
             "newton_iterations_max": int(np.max(iters)), "solve_ms_mean": float(np.mean(solve_ms)),
             "solve_us_per_newton_iteration": float(1e3 * np.sum(solve_ms) / max(1, np.sum(iters))),
-            "host_contact_query_ms_mean": float(np.mean(host_ms)),
+            "contact_pairs_from": "device (gmpm_generate_contact_pairs)" if args.device_pairs else "host (numpy analytic SDF on positions_host())",
+            "contact_query_ms_mean": float(np.mean(host_ms)),
             "pad_impulse_x": [float(f[1][0]), float(f[2][0])]}
     print(json.dumps(line))
     st.Destroy()
