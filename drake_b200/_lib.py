@@ -40,7 +40,7 @@ TYPED_SYMBOLS = ["create", "destroy", "add_qr_cloth", "finalize", "rebuild_mappi
                  "positions_host", "halo_flags", "halo_plan_async", "halo_pack", "halo_unpack", "update_grid_part", "g2p_part", "stream", "halo_stream", "copy_contact_pairs",
                  "generate_contact_pairs", "update_contact", "reallocate_external_bodies", "external_body_force_to_host",
                  "dump_cpu_state", "n_verts", "n_faces", "n_particles", "n_cells", "num_contacts",
-                 "grid_touched_cnt_host", "read", "run_substeps", "kernel_launches", "set_profiling",
+                 "grid_touched_cnt_host", "read", "checkpoint_bytes", "save_state", "load_state", "run_substeps", "kernel_launches", "set_profiling",
                  "kernel_time", "profile_report", "timer_mark", "timer_elapsed_ms", "device_bytes",
                  "block_counts"]
 
@@ -91,6 +91,10 @@ def _declare(L):
         g("sync_particle_state_to_cpu").argtypes = [vp, vp]
         g("sync_particle_state_to_cpu_async").argtypes = [vp]
         g("positions_host").argtypes = [vp, C.POINTER(C.c_void_p)]
+        g("checkpoint_bytes").argtypes = [vp]
+        g("checkpoint_bytes").restype = sz
+        g("save_state").argtypes = [vp, vp, sz, C.POINTER(sz)]
+        g("load_state").argtypes = [vp, vp, sz]
         g("halo_flags").argtypes = [vp, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
         g("halo_plan_async").argtypes = [vp]
         g("halo_pack").argtypes = [vp, C.POINTER(C.c_uint32), C.POINTER(C.c_void_p)]

@@ -4,6 +4,7 @@
 #define GMPM_STR(x) GMPM_STR2(x)
 
 #include "contact.cuh"
+#include "checkpoint.cuh"
 #include "contact_gen.cuh"
 #include "getters.cuh"
 #include "state.cuh"
@@ -242,6 +243,16 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
       s->st.halo_init();                                                                                       \
       *cuda_stream = (void*)s->st.halo_stream;                                                                 \
     });                                                                                                        \
+  }                                                                                                            \
+  size_t gmpm_checkpoint_bytes_##SUF(const gmpm_state_##SUF* s) { return s->st.checkpoint_bytes(); }           \
+  int gmpm_save_state_##SUF(gmpm_state_##SUF* s, void* out, size_t cap, size_t* written) {                     \
+    return guarded([&] {                                                                                       \
+      const size_t b = s->st.save_state(out, cap);                                                             \
+      if (written) *written = b;                                                                               \
+    });                                                                                                        \
+  }                                                                                                            \
+  int gmpm_load_state_##SUF(gmpm_state_##SUF* s, const void* in, size_t bytes) {                               \
+    return guarded([&] { s->st.load_state(in, bytes); });                                                      \
   }                                                                                                            \
   int gmpm_run_substeps_##SUF(gmpm_state_##SUF* s, int n, T dt, int bc, int sort_every) {                      \
     return guarded([&] { s->st.run_substeps(n, dt, bc, sort_every); });                                        \

@@ -950,6 +950,9 @@ struct State {
   }
 
   size_t read(const char* name, void* out, size_t cap);  // getters.cuh
+  size_t checkpoint_bytes() const;                       // checkpoint.cuh
+  size_t save_state(void* out, size_t cap);
+  void load_state(const void* in, size_t bytes);
   // contact.cuh
   void copy_contact_pairs(size_t n, const uint32_t* mpm_id, const uint32_t* rigid_id, const T* dist, const T* normal,
                           const T* cpos, const T* rigid_v, const T* rigid_p);

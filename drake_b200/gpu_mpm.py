@@ -183,6 +183,20 @@ class GpuMpmState:
     def device_bytes(self):
         return self._f("device_bytes")(self._h)
 
+    # --- checkpoint / restore (gmpm_c.h; the reference has none)
+    def save_state(self):
+        """-> bytes: positions, velocities, volumes, affine matrices, pids, F, Dm^-1 (reference layout)."""
+        n = self._f("checkpoint_bytes")(self._h)
+        buf = np.zeros(n, np.uint8)
+        w = C.c_size_t()
+        check(self._f("save_state")(self._h, _ptr(buf), n, C.byref(w)))
+        return buf[:w.value].tobytes()
+
+    def load_state(self, blob):
+        buf = np.frombuffer(blob, np.uint8)
+        check(self._f("load_state")(self._h, C.c_void_p(buf.ctypes.data), buf.size))
+        self._positions_pending = False
+
     # --- multi-GPU shared-block exchange (gmpm_c.h, "multi-GPU extension"); driven by drake_b200.slab
     def stream_handle(self):
         p = C.c_void_p()

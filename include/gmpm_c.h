@@ -191,6 +191,13 @@ int gmpm_device_sync(void);
   /* (for stream-ordered collectives). */                                                           \
   int gmpm_stream_##SUF(gmpm_state_##SUF* s, void** cuda_stream);                                   \
   int gmpm_halo_stream_##SUF(gmpm_state_##SUF* s, void** cuda_stream);                              \
+  /* Checkpoint / restore (not in the reference: its state cannot be resumed, DumpCpuState keeps vertex */\
+  /* positions only, cuda_mpm_model.cu:245-265).  The blob holds positions, velocities, volumes, affine */\
+  /* matrices, deformation gradients, Dm^-1 and pids in the reference's layout and visible order;       */\
+  /* load_state needs a finalized state built from the same meshes.                                     */\
+  size_t gmpm_checkpoint_bytes_##SUF(const gmpm_state_##SUF* s);                                    \
+  int gmpm_save_state_##SUF(gmpm_state_##SUF* s, void* out, size_t cap_bytes, size_t* bytes_written);\
+  int gmpm_load_state_##SUF(gmpm_state_##SUF* s, const void* in, size_t bytes);                     \
   /* One substep of the driver loop without contact (deformable_driver.h:240-260 /                */\
   /* cuda_mpm_test.cc:66-72): RebuildMapping(sort) CalcFemStateAndForce ParticleToGrid            */\
   /* UpdateGrid(mpm_bc) GridToParticle, n_substeps times; sort_every = k sorts at substeps        */\

@@ -79,6 +79,7 @@ template <typename T> struct Abi;
     static constexpr auto positions_host = gmpm_positions_host_##SUF;                                \
     static constexpr auto copy_contact_pairs = gmpm_copy_contact_pairs_##SUF;                        \
     static constexpr auto update_contact = gmpm_update_contact_##SUF;                                \
+    static constexpr auto generate_contact_pairs = gmpm_generate_contact_pairs_##SUF;                \
     static constexpr auto reallocate_external_bodies = gmpm_reallocate_external_bodies_##SUF;        \
     static constexpr auto external_body_force_to_host = gmpm_external_body_force_to_host_##SUF;      \
     static constexpr auto dump_cpu_state = gmpm_dump_cpu_state_##SUF;                                \
@@ -89,6 +90,9 @@ template <typename T> struct Abi;
     static constexpr auto grid_touched_cnt_host = gmpm_grid_touched_cnt_host_##SUF;                  \
     static constexpr auto read = gmpm_read_##SUF;                                                    \
     static constexpr auto run_substeps = gmpm_run_substeps_##SUF;                                    \
+    static constexpr auto checkpoint_bytes = gmpm_checkpoint_bytes_##SUF;                            \
+    static constexpr auto save_state = gmpm_save_state_##SUF;                                        \
+    static constexpr auto load_state = gmpm_load_state_##SUF;                                        \
   };
 GMPM_B200_ABI(f32, float)
 GMPM_B200_ABI(f64, double)
@@ -177,6 +181,19 @@ struct GpuMpmState {
     internal::Check(Abi::read(raw(), name, out.data(), count * sizeof(U), &written), name);
     out.resize(written / sizeof(U));
     return out;
+  }
+
+  // Checkpoint / restore (extension; DumpCpuState above keeps vertex positions only): the whole particle and
+  // face state as one blob; LoadState needs a finalized state built from the same meshes.
+  std::vector<unsigned char> SaveState() const {
+    std::vector<unsigned char> blob(Abi::checkpoint_bytes(raw()));
+    size_t written = 0;
+    internal::Check(Abi::save_state(raw(), blob.data(), blob.size(), &written), "SaveState");
+    blob.resize(written);
+    return blob;
+  }
+  void LoadState(const std::vector<unsigned char>& blob) {
+    internal::Check(Abi::load_state(raw(), blob.data(), blob.size()), "LoadState");
   }
 
   int total_contact_iteration_count = 0;  // cuda_mpm_model.cuh:175

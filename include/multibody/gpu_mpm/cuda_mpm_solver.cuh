@@ -66,6 +66,16 @@ class GpuMpmSolver {
                     "CopyContactPairs");
   }
 
+  // Extension: CalcMpmContactPairs + CopyContactPairs on the device, for rigid geometry that is an
+  // analytic box or sphere (deformable_driver.h:120-194 does this on the host with one signed-distance query per
+  // particle and geometry).  Uses the positions of the last SyncParticleStateToCpu.  Returns the number of pairs.
+  size_t GenerateContactPairs(GpuMpmState<T>* state, const std::vector<gmpm_analytic_geometry>& geometries) const {
+    size_t n = 0;
+    internal::Check(Abi::generate_contact_pairs(state->raw(), geometries.data(), geometries.size(), &n),
+                    "GenerateContactPairs");
+    return n;
+  }
+
   // cuda_mpm_solver.cu:215-621.  `dump` (per-iteration JSON to a developer path) is not reproduced.
   void UpdateContact(GpuMpmState<T>* state, const int frame, const int substep, const T& dt, const T& friction_mu,
                      const T& stiffness, const T& damping, const bool dump, const bool exact_line_search) const {

@@ -422,3 +422,42 @@ def test_oracle_pinned_against_reference_kernels(dtype, tol1, tol20):
         else:
             assert not warm or steps > 1
         ref.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_checkpoint_restore_continues_the_run(dtype):
+    """save_state after a few substeps, load it into a FRESH state built from the same meshes
+    and continue -- both runs must agree to summation-order rounding (the restored run keeps a different
+    physical particle order), and the restored state reads back exactly what was saved."""
+    def fresh():
+        st = GpuMpmState(dtype)
+        for pos, vel, tri in scenes.stacked_sheets(3, res=20, dtype=dtype):
+            st.AddQRCloth(pos, vel, tri)
+        st.Finalize()
+        return st
+    sv = GpuMpmSolver()
+    a = fresh()
+    sv.RunSubsteps(a, 7, 1e-3, -1, 3)   # includes visible re-sorts: pids are no longer the identity
+    blob = a.save_state()
+    b = fresh()
+    b.load_state(blob)
+    for name in ("positions", "velocities", "volumes", "affine_matrices", "pids", "deformation_gradients", "Dm_inverses"):
+        np.testing.assert_array_equal(a.read(name), b.read(name), err_msg=name)
+    assert b.save_state() == blob
+    sv.RunSubsteps(a, 6, 1e-3, -1, 3)
+    sv.RunSubsteps(b, 6, 1e-3, -1, 3)
+    tol = 1e-11 if dtype == np.float64 else 2e-4
+    np.testing.assert_array_equal(a.read("pids"), b.read("pids"))
+    for name in ("positions", "velocities", "affine_matrices", "deformation_gradients"):
+        x, y = a.read(name), b.read(name)
+        assert np.max(np.abs(x - y)) <= tol * max(1.0, np.max(np.abs(x))), name
+    # a checkpoint of another scene is refused
+    c = GpuMpmState(dtype)
+    pos, vel, tri = next(iter(scenes.stacked_sheets(1, res=10, dtype=dtype)))
+    c.AddQRCloth(pos, vel, tri)
+    c.Finalize()
+    with pytest.raises(Exception):
+        c.load_state(blob)
+    for s in (a, b, c):
+        s.Destroy()
