@@ -230,6 +230,8 @@ def main():
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--overlap", action="store_true",
                     help="N>1: UpdateGrid/G2P in two parts around the exchange (interior work hides the all-reduce)")
+    ap.add_argument("--no-peer", action="store_true",
+                    help="N>1: exchange the shared blocks with an NCCL all-reduce instead of the peer-memory windows")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
@@ -268,11 +270,12 @@ def main():
     ex = None
     if world > 1:
         from drake_b200 import slab
-        ex = slab.SlabExchange(slab.GpuHaloBackend(st))
+        peer = world <= 8 and not args.no_peer             # block sums through peer-memory windows (csrc/halo.cuh)
+        ex = slab.SlabExchange(slab.GpuHaloBackend(st), peer=peer)
 
     # interior UpdateGrid/G2P work hides the all-reduce; pays off once the collective is slow (measured: loses
     # 20 us at 2 ranks, wins 18 us at 8)
-    overlap = args.overlap or (world >= 8 and not args.no_overlap)
+    overlap = args.overlap or (world >= 8 and args.no_peer and not args.no_overlap)
 
     def run_substeps(n, first=0):
         if ex is None:
@@ -405,9 +408,11 @@ def main():
                            "l2": "inputs larger than L2 (particle state %.0f MB per step > 126 MB)" % (N * (44 * T + 8) / 1e6),
                            "parallelism": "single GPU" if world == 1 else
                            "%d ranks, one 34-sheet stack each of one scene on a 256^3 grid (dx = 1/128); grid blocks "
-                           "reached by two ranks are summed every substep: all-reduce of block flags + all-reduce of "
-                           "%d shared blocks (%.0f KB/step) over NCCL%s" % (world, halo_blocks, halo_bytes_per_step / 1e3,
-                                                                           ", overlapped with interior G2P" if overlap else "")},
+                           "reached by two ranks are summed every substep: all-reduce of block flags (NCCL, side stream, "
+                           "one substep ahead) + %s of %d shared blocks (%.0f KB/step all-reduced)%s"
+                           % (world, "stores into the sharers' peer-memory windows (NVLink) with device-side delivery flags"
+                              if ex is not None and ex.peer else "NCCL all-reduce", halo_blocks,
+                              halo_bytes_per_step / 1e3, ", overlapped with interior G2P" if overlap else "")},
                 "clocks": clocks,
                 "e2e": {"value": N_all * Ke / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0,
                         "d2h_bytes_per_step": int(3 * T * N), "steps": Ke, "ms_per_step": e_ms / Ke,

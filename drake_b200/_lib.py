@@ -37,7 +37,7 @@ PLAIN_SYMBOLS = ["gmpm_default_params", "gmpm_last_error", "gmpm_version", "gmpm
                  "gmpm_morton_code", "gmpm_cell_index", "gmpm_inverse_cell_index", "gmpm_radix_sort_pairs"]
 TYPED_SYMBOLS = ["create", "destroy", "add_qr_cloth", "finalize", "rebuild_mapping", "calc_fem", "p2g",
                  "update_grid", "g2p", "sync", "sync_particle_state_to_cpu", "sync_particle_state_to_cpu_async",
-                 "positions_host", "halo_flags", "halo_plan_async", "halo_pack", "halo_unpack", "update_grid_part", "g2p_part", "stream", "halo_stream", "copy_contact_pairs",
+                 "positions_host", "halo_flags", "halo_plan_async", "halo_pack", "halo_unpack", "halo_peer_init", "halo_peer_window", "halo_peer_attach", "halo_peer_send", "halo_peer_recv", "update_grid_part", "g2p_part", "stream", "halo_stream", "copy_contact_pairs",
                  "generate_contact_pairs", "update_contact", "reallocate_external_bodies", "external_body_force_to_host",
                  "dump_cpu_state", "n_verts", "n_faces", "n_particles", "n_cells", "num_contacts",
                  "grid_touched_cnt_host", "read", "checkpoint_bytes", "save_state", "load_state", "run_substeps", "kernel_launches", "set_profiling",
@@ -99,6 +99,11 @@ def _declare(L):
         g("halo_plan_async").argtypes = [vp]
         g("halo_pack").argtypes = [vp, C.POINTER(C.c_uint32), C.POINTER(C.c_void_p)]
         g("halo_unpack").argtypes = [vp]
+        g("halo_peer_init").argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32]
+        g("halo_peer_window").argtypes = [vp, C.c_char_p, C.POINTER(C.c_void_p)]
+        g("halo_peer_attach").argtypes = [vp, C.c_uint32, C.c_char_p, C.c_void_p]
+        g("halo_peer_send").argtypes = [vp, C.POINTER(C.c_uint32)]
+        g("halo_peer_recv").argtypes = [vp]
         g("update_grid_part").argtypes = [vp, C.c_int, C.c_int]
         g("g2p_part").argtypes = [vp, ct, C.c_int]
         g("stream").argtypes = [vp, C.POINTER(C.c_void_p)]

@@ -224,6 +224,27 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
     });                                                                                                        \
   }                                                                                                            \
   int gmpm_halo_unpack_##SUF(gmpm_state_##SUF* s) { return guarded([&] { s->st.halo_unpack(); }); }            \
+  int gmpm_halo_peer_init_##SUF(gmpm_state_##SUF* s, uint32_t rank, uint32_t world, uint32_t cap_blocks) {     \
+    return guarded([&] { s->st.halo_peer_init(rank, world, cap_blocks); });                                    \
+  }                                                                                                            \
+  int gmpm_halo_peer_window_##SUF(gmpm_state_##SUF* s, unsigned char* ipc_handle64, void** local_ptr) {        \
+    return guarded([&] {                                                                                       \
+      if (ipc_handle64) s->st.halo_peer_ipc_handle(ipc_handle64);                                              \
+      s->st.require_peer("halo_peer_window");                                                                  \
+      if (local_ptr) *local_ptr = s->st.halo_window;                                                           \
+    });                                                                                                        \
+  }                                                                                                            \
+  int gmpm_halo_peer_attach_##SUF(gmpm_state_##SUF* s, uint32_t peer, const unsigned char* ipc_handle64,       \
+                                  void* same_process_ptr) {                                                    \
+    return guarded([&] { s->st.halo_peer_attach(peer, ipc_handle64, same_process_ptr); });                     \
+  }                                                                                                            \
+  int gmpm_halo_peer_send_##SUF(gmpm_state_##SUF* s, uint32_t* n_shared) {                                     \
+    return guarded([&] {                                                                                       \
+      const uint32_t n = s->st.halo_peer_send();                                                               \
+      if (n_shared) *n_shared = n;                                                                             \
+    });                                                                                                        \
+  }                                                                                                            \
+  int gmpm_halo_peer_recv_##SUF(gmpm_state_##SUF* s) { return guarded([&] { s->st.halo_peer_recv(); }); }      \
   int gmpm_update_grid_part_##SUF(gmpm_state_##SUF* s, int bc, int part) {                                     \
     return guarded([&] { s->st.update_grid_part(bc, part); });                                                 \
   }                                                                                                            \

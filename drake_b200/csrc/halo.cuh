@@ -40,7 +40,7 @@ constexpr int kHaloBlocksPerCta = 1024;  // grid blocks scanned by one CTA (4 pe
 __global__ void halo_flags_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __restrict__ ctr,
                                   uint32_t blocks_per_axis, const uint8_t* __restrict__ own_prev,
                                   const uint32_t* __restrict__ nbr_list, uint8_t* __restrict__ flags,
-                                  uint32_t* __restrict__ err) {
+                                  uint32_t* __restrict__ err, uint8_t contribution) {
   const uint32_t n = ctr->n_touched * 27u;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const uint32_t g = touched_list[i / 27u], d = i % 27u;
@@ -50,28 +50,33 @@ __global__ void halo_flags_kernel(const uint32_t* __restrict__ touched_list, con
     uint32_t bx, by, bz;
     block_coords(g, bx, by, bz);
     const uint32_t nx = bx + d / 9u - 1u, ny = by + (d / 3u) % 3u - 1u, nz = bz + d % 3u - 1u;  // wraps below 0
-    if (nx < blocks_per_axis && ny < blocks_per_axis && nz < blocks_per_axis) flags[morton3(nx, ny, nz)] = 1;
+    if (nx < blocks_per_axis && ny < blocks_per_axis && nz < blocks_per_axis) flags[morton3(nx, ny, nz)] = contribution;
     if (d == 13u && own_prev && own_prev[g] == 0) atomicAdd(err, 1u);
   }
 }
 
+// Shared = reached by more than one rank.  The ranks contribute either 1 each (flags = number of sharers) or,
+// in peer mode (<= 8 ranks), the bit 1 << rank (flags = sharer set; the SUM all-reduce of distinct bits is their OR).
+__device__ __forceinline__ bool halo_is_shared(uint32_t f, bool bits) { return bits ? (f & (f - 1u)) != 0u : f > 1u; }
 __device__ __forceinline__ uint32_t halo_shared_mask(const uint8_t* __restrict__ flags, uint32_t n_blocks,
-                                                     uint32_t b0) {
+                                                     uint32_t b0, bool bits) {
   uint32_t m = 0;
 #pragma unroll
   for (int j = 0; j < 4; ++j)
-    if (b0 + j < n_blocks && flags[b0 + j] > 1) m |= 1u << j;
+    if (b0 + j < n_blocks && halo_is_shared(flags[b0 + j], bits)) m |= 1u << j;
   return m;
 }
 
 // Pass 1: number of shared blocks in each CTA's span.
 __global__ void __launch_bounds__(kHaloThreads)
-halo_count_kernel(uint32_t n_blocks, const uint8_t* __restrict__ flags, uint32_t* __restrict__ cta_counts) {
+halo_count_kernel(uint32_t n_blocks, const uint8_t* __restrict__ flags, uint32_t* __restrict__ cta_counts, bool bits,
+                  uint32_t* __restrict__ union_out) {
   __shared__ uint32_t s_sum;
   if (threadIdx.x == 0) s_sum = 0;
+  if (blockIdx.x == 0 && threadIdx.x == 0) *union_out = 0;  // accumulated by the compaction that follows
   __syncthreads();
   const uint32_t b0 = (blockIdx.x * kHaloThreads + threadIdx.x) * 4u;
-  uint32_t c = __popc(halo_shared_mask(flags, n_blocks, b0));
+  uint32_t c = __popc(halo_shared_mask(flags, n_blocks, b0, bits));
   c = __reduce_add_sync(kFullMask, c);
   if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_sum, c);
   __syncthreads();
@@ -82,7 +87,8 @@ halo_count_kernel(uint32_t n_blocks, const uint8_t* __restrict__ flags, uint32_t
 // in-CTA offset by an exclusive scan over the threads).
 __global__ void __launch_bounds__(kHaloThreads)
 halo_compact_kernel(uint32_t n_blocks, const uint8_t* __restrict__ flags, const uint32_t* __restrict__ cta_counts,
-                    uint32_t* __restrict__ list, uint32_t list_cap, uint32_t* __restrict__ n_shared) {
+                    uint32_t* __restrict__ list, uint32_t list_cap, uint32_t* __restrict__ n_shared, bool bits,
+                    uint8_t* __restrict__ sharers, uint32_t* __restrict__ union_out) {
   __shared__ uint32_t s_warp[kHaloThreads / 32];
   __shared__ uint32_t s_base;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -94,9 +100,10 @@ halo_compact_kernel(uint32_t n_blocks, const uint8_t* __restrict__ flags, const 
   __syncthreads();
   if (lane == 0 && pre) atomicAdd(&s_base, pre);
   const uint32_t b0 = (blockIdx.x * kHaloThreads + threadIdx.x) * 4u;
-  const uint32_t m = halo_shared_mask(flags, n_blocks, b0);
+  const uint32_t m = halo_shared_mask(flags, n_blocks, b0, bits);
   const uint32_t c = __popc(m);
   uint32_t incl = c;
+  uint32_t who = 0;  // ranks this thread's shared blocks are shared with (peer mode)
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const uint32_t t = __shfl_up_sync(kFullMask, incl, o);
@@ -109,9 +116,19 @@ halo_compact_kernel(uint32_t n_blocks, const uint8_t* __restrict__ flags, const 
 #pragma unroll
   for (int j = 0; j < 4; ++j)
     if ((m >> j) & 1u) {
-      if (off < list_cap) list[off] = b0 + j;
+      if (off < list_cap) {
+        list[off] = b0 + j;
+        if (bits) {
+          sharers[off] = flags[b0 + j];
+          who |= flags[b0 + j];
+        }
+      }
       ++off;
     }
+  if (bits) {
+    who = __reduce_or_sync(kFullMask, who);
+    if (lane == 0 && who) atomicOr(union_out, who);
+  }
   if (blockIdx.x == gridDim.x - 1 && threadIdx.x == kHaloThreads - 1) *n_shared = off;  // grand total
 }
 
@@ -139,6 +156,102 @@ __global__ void halo_mark_kernel(uint32_t n, const uint32_t* __restrict__ list, 
                                  uint8_t* __restrict__ mark) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) mark[list[i]] = value;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Peer mode: the exchange itself over NVLink peer memory, no collective on the critical path.
+//
+// Every rank owns a receive WINDOW (one cudaMalloc, opened by the other ranks through CUDA IPC, or shared
+// by pointer when several states live in one process):
+//     uint32 flag[64]                      flag[r] = number of the last exchange rank r has delivered
+//     T      data[2][world][cap][4][64]    data[e & 1][r][i] = rank r's mass / momentum of shared block i
+// i indexes the shared-block list, which is identical on all ranks, so no per-pair lists are needed.
+//   send : for every listed block, this rank's values (zeros if it did not touch the block) are STORED into the
+//          window of every other sharer; after a system-scope fence the last CTA stores the exchange number
+//          into flag[rank] of every rank it shares a block with (release).
+//   recv : spins (acquire) until every rank it shares a block with has delivered this exchange, then sums the
+//          contributions of a block's sharers IN ASCENDING RANK ORDER -- every sharer computes the same
+//          bits -- into the blocks this rank touched.
+// The two window halves alternate: a rank can be at most one exchange ahead of a neighbour (its next recv
+// needs the neighbour's next send, which follows the neighbour's current recv in stream order).
+// ------------------------------------------------------------------------------------------------
+constexpr int kHaloMaxPeers = 8;
+constexpr size_t kHaloWindowHeader = 256;  // bytes reserved for the flags
+struct HaloWindows {
+  unsigned char* base[kHaloMaxPeers];
+};
+template <typename T>
+__device__ __forceinline__ T* halo_window_data(unsigned char* base, uint32_t parity, uint32_t world, uint32_t src,
+                                               uint32_t cap, uint32_t i) {
+  return reinterpret_cast<T*>(base + kHaloWindowHeader) + (((size_t)parity * world + src) * cap + i) * 256;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kHaloThreads)
+halo_peer_send_kernel(uint32_t n, const uint32_t* __restrict__ list, const uint8_t* __restrict__ sharers,
+                      const uint32_t* __restrict__ touched_epoch, uint32_t epoch, const T* __restrict__ g_mass,
+                      const T* __restrict__ g_vel, HaloWindows win, uint32_t rank, uint32_t world, uint32_t cap,
+                      uint32_t xchg, const uint32_t* __restrict__ union_mask, uint32_t* __restrict__ done) {
+  const uint32_t c = threadIdx.x >> 6, l = threadIdx.x & 63u;
+  for (uint32_t i = blockIdx.x; i < n; i += gridDim.x) {
+    const uint32_t g = list[i];
+    const uint32_t who = sharers[i] & ~(1u << rank);
+    const bool own = touched_epoch[g] == epoch;
+    const T v = !own ? T(0) : (c == 0 ? g_mass[(size_t)g * 64 + l] : g_vel[(size_t)g * 192 + (size_t)(c - 1) * 64 + l]);
+    for (uint32_t q = 0; q < world; ++q)
+      if ((who >> q) & 1u) halo_window_data<T>(win.base[q], xchg & 1u, world, rank, cap, i)[threadIdx.x] = v;
+  }
+  // all stores of all CTAs before the flags (threadFenceReduction pattern at system scope)
+  __threadfence_system();
+  __syncthreads();
+  __shared__ bool s_last;
+  if (threadIdx.x == 0) s_last = atomicAdd(done, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!s_last) return;
+  if (threadIdx.x == 0) *done = 0;
+  const uint32_t peers = *union_mask & ~(1u << rank);
+  if (threadIdx.x < world && ((peers >> threadIdx.x) & 1u)) {
+    __threadfence_system();
+    st_release_sys(reinterpret_cast<uint32_t*>(win.base[threadIdx.x]) + rank, xchg);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kHaloThreads)
+halo_peer_recv_kernel(uint32_t n, const uint32_t* __restrict__ list, const uint8_t* __restrict__ sharers,
+                      const uint32_t* __restrict__ touched_epoch, uint32_t epoch, T* __restrict__ g_mass,
+                      T* __restrict__ g_vel, unsigned char* __restrict__ window, uint32_t rank, uint32_t world,
+                      uint32_t cap, uint32_t xchg, const uint32_t* __restrict__ union_mask) {
+  const uint32_t peers = *union_mask & ~(1u << rank);
+  if (threadIdx.x < world && ((peers >> threadIdx.x) & 1u)) {
+    const uint32_t* flag = reinterpret_cast<const uint32_t*>(window) + threadIdx.x;
+    while ((int32_t)(ld_acquire_sys(flag) - xchg) < 0) __nanosleep(64);
+  }
+  __syncthreads();
+  const uint32_t c = threadIdx.x >> 6, l = threadIdx.x & 63u;
+  for (uint32_t i = blockIdx.x; i < n; i += gridDim.x) {
+    const uint32_t g = list[i];
+    if (touched_epoch[g] != epoch) continue;  // not this rank's block now (the list is the dilated set)
+    T* cell = c == 0 ? g_mass + (size_t)g * 64 + l : g_vel + (size_t)g * 192 + (size_t)(c - 1) * 64 + l;
+    const uint32_t who = sharers[i];
+    T acc = T(0);
+    bool first = true;
+    for (uint32_t q = 0; q < world; ++q) {
+      if (!((who >> q) & 1u)) continue;
+      const T v = q == rank ? *cell : __ldcg(halo_window_data<T>(window, xchg & 1u, world, q, cap, i) + threadIdx.x);
+      acc = first ? v : acc + v;
+      first = false;
+    }
+    *cell = acc;
+  }
 }
 
 }  // namespace gmpm

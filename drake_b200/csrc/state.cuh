@@ -168,6 +168,15 @@ struct State {
   bool halo_planned = false, halo_flags_out = false, halo_own_valid = false, halo_packed_out = false;
   cudaStream_t halo_stream = nullptr;
   cudaEvent_t ev_halo_flags = nullptr, ev_halo_plan = nullptr;
+  // peer mode (halo.cuh): exchange through receive windows in peer memory instead of an all-reduce
+  bool halo_peer = false;
+  uint32_t halo_rank = 0, halo_world = 1, halo_win_cap = 0, halo_xchg = 0;
+  unsigned char* halo_window = nullptr;          // this rank's window (plain cudaMalloc: exportable through CUDA IPC)
+  size_t halo_window_bytes = 0;
+  HaloWindows halo_windows{};                    // every rank's window as mapped into this process
+  bool halo_window_ipc[kHaloMaxPeers]{};         // opened with cudaIpcOpenMemHandle (to be closed)
+  uint8_t* halo_sharers[2]{};                    // sharer set of each listed block
+  bool halo_sent = false;
 
   std::vector<void*> allocs;
   size_t device_bytes = 0;
@@ -256,6 +265,14 @@ struct State {
       cudaStreamDestroy(halo_stream);
       halo_stream = nullptr;
     }
+    for (int q = 0; q < kHaloMaxPeers; ++q)
+      if (halo_window_ipc[q] && halo_windows.base[q]) {
+        cudaIpcCloseMemHandle(halo_windows.base[q]);
+        halo_window_ipc[q] = false;
+      }
+    if (halo_window) cudaFree(halo_window);
+    halo_window = nullptr;
+    halo_windows = HaloWindows{};
     if (h_halo_words) cudaFreeHost(h_halo_words);
     h_halo_words = nullptr;
     if (ev_halo_flags) cudaEventDestroy(ev_halo_flags);
@@ -695,7 +712,7 @@ struct State {
     halo_nbr = dalloc<uint32_t>(k.n_blocks);
     halo_mark = dalloc<uint8_t>(k.n_blocks);
     halo_cta_counts = dalloc<uint32_t>((k.n_blocks + kHaloBlocksPerCta - 1) / kHaloBlocksPerCta);
-    halo_dev_words = dalloc<uint32_t>(4);
+    halo_dev_words = dalloc<uint32_t>(8);  // [0..1] counts per plan slot, [2] containment errors, [3] send counter, [4..5] peers per slot
     GMPM_CUDA(cudaHostAlloc((void**)&h_halo_words, 4 * sizeof(uint32_t), cudaHostAllocDefault));
     memset(h_halo_words, 0, 4 * sizeof(uint32_t));
     GMPM_CUDA(cudaStreamCreateWithFlags(&halo_stream, cudaStreamNonBlocking));
@@ -712,11 +729,15 @@ struct State {
     GMPM_CUDA(cudaStreamSynchronize(halo_stream));
     for (int i = 0; i < 2; ++i) {
       uint32_t* old = halo_list[i];
+      uint8_t* old_sh = halo_sharers[i];
       halo_list[i] = dalloc<uint32_t>(cap, false);
+      halo_sharers[i] = dalloc<uint8_t>(cap);
       if (old) {
         GMPM_CUDA(cudaMemcpyAsync(halo_list[i], old, sizeof(uint32_t) * halo_cap, cudaMemcpyDeviceToDevice, stream));
+        GMPM_CUDA(cudaMemcpyAsync(halo_sharers[i], old_sh, halo_cap, cudaMemcpyDeviceToDevice, stream));
         GMPM_CUDA(cudaStreamSynchronize(stream));
         dfree(old);
+        dfree(old_sh);
       }
     }
     if (halo_packed) dfree(halo_packed);
@@ -743,7 +764,7 @@ struct State {
     halo_flags_kernel<<<persistent_ctas(2), kThreads, 0, stream>>>(
         touched_list[tl_cur], ctr, (uint32_t)k.domain_size >> 2, halo_own_valid ? halo_own : nullptr,
         (stage == GridStage::kMomentum && halo_nbr_epoch == p2g_epoch) ? halo_nbr : nullptr, halo_flags_d,
-        halo_dev_words + 2);
+        halo_dev_words + 2, (uint8_t)(halo_peer ? 1u << halo_rank : 1u));
     GMPM_CUDA(cudaGetLastError());
     GMPM_CUDA(cudaMemcpyAsync(halo_own, halo_flags_d, k.n_blocks, cudaMemcpyDeviceToDevice, stream));
     halo_own_valid = true;
@@ -754,9 +775,11 @@ struct State {
   }
   void halo_compact_into(int slot, cudaStream_t st) {
     const uint32_t ctas = (k.n_blocks + kHaloBlocksPerCta - 1) / kHaloBlocksPerCta;
-    halo_count_kernel<<<ctas, kHaloThreads, 0, st>>>(k.n_blocks, halo_flags_d, halo_cta_counts);
+    halo_count_kernel<<<ctas, kHaloThreads, 0, st>>>(k.n_blocks, halo_flags_d, halo_cta_counts, halo_peer,
+                                                    halo_dev_words + 4 + slot);
     halo_compact_kernel<<<ctas, kHaloThreads, 0, st>>>(k.n_blocks, halo_flags_d, halo_cta_counts, halo_list[slot],
-                                                      (uint32_t)halo_cap, halo_dev_words + slot);
+                                                      (uint32_t)halo_cap, halo_dev_words + slot, halo_peer,
+                                                      halo_sharers[slot], halo_dev_words + 4 + slot);
     GMPM_CUDA(cudaGetLastError());
     launches += 2;
   }
@@ -778,11 +801,12 @@ struct State {
   }
   int halo_next_slot = 0;
   bool halo_plan_pending = false;
-  // Packs this rank's share of the planned shared blocks; returns their number (known on the host).
-  uint32_t halo_pack() {
+  // Start of an exchange: picks up the list planned for it (count through pinned memory), checks containment,
+  // assembles the block sums and marks the listed blocks.  Returns the number of shared blocks.
+  uint32_t halo_begin_exchange(const char* what) {
     require_finalized();
-    require_after_p2g("halo_pack");
-    if (!halo_plan_pending) throw std::invalid_argument("halo_pack without a plan (halo_flags / halo_plan first)");
+    require_after_p2g(what);
+    if (!halo_plan_pending) throw std::invalid_argument(std::string(what) + " without a plan (halo_flags / halo_plan first)");
     GMPM_CUDA(cudaEventSynchronize(ev_halo_plan));  // issued a whole substep ago (or just now at start-up)
     const int slot = halo_next_slot;
     if (h_halo_words[2 * slot + 1] != 0)
@@ -803,6 +827,16 @@ struct State {
     if (n) {
       launch("halo_mark");
       halo_mark_kernel<<<blocks_for(n), kThreads, 0, stream>>>(n, halo_list[slot], 1, halo_mark);
+      GMPM_CUDA(cudaGetLastError());
+    }
+    return n;
+  }
+  // Packs this rank's share of the planned shared blocks; returns their number (known on the host).
+  uint32_t halo_pack() {
+    if (halo_peer) throw std::invalid_argument("halo_pack: this state exchanges through peer windows (halo_peer_send / recv)");
+    const uint32_t n = halo_begin_exchange("halo_pack");
+    const int slot = halo_cur;
+    if (n) {
       launch("halo_pack");
       halo_pack_kernel<T, false><<<std::min<uint32_t>(n, persistent_ctas(8)), kHaloThreads, 0, stream>>>(
           n, halo_list[slot], touched_epoch, p2g_epoch, g_mass, g_vel, halo_packed);
@@ -821,6 +855,93 @@ struct State {
       GMPM_CUDA(cudaGetLastError());
     }
     halo_packed_out = false;
+  }
+
+  // ---- peer mode ------------------------------------------------------------------------------------
+  // Must precede the first halo_flags.  `cap_blocks` bounds the shared-block list (the window cannot move
+  // once the other ranks have mapped it).
+  void halo_peer_init(uint32_t rank, uint32_t world, uint32_t cap_blocks) {
+    require_finalized();
+    if (world < 1 || world > (uint32_t)kHaloMaxPeers || rank >= world)
+      throw std::invalid_argument("halo_peer_init: peer mode serves 1..8 ranks (one NVSwitch domain)");
+    if (halo_window) throw std::invalid_argument("halo_peer_init: already initialised");
+    if (halo_planned || halo_plan_pending || halo_flags_out)
+      throw std::invalid_argument("halo_peer_init must precede the first halo_flags");
+    halo_init();
+    halo_reserve(cap_blocks);
+    halo_win_cap = (uint32_t)halo_cap;
+    halo_window_bytes = kHaloWindowHeader + sizeof(T) * 256 * 2 * (size_t)world * halo_win_cap;
+    GMPM_CUDA(cudaMalloc((void**)&halo_window, halo_window_bytes));
+    GMPM_CUDA(cudaMemsetAsync(halo_window, 0, halo_window_bytes, stream));
+    GMPM_CUDA(cudaStreamSynchronize(stream));
+    halo_rank = rank;
+    halo_world = world;
+    halo_windows.base[rank] = halo_window;
+    halo_peer = true;
+    halo_own_valid = false;
+    halo_xchg = 0;
+  }
+  void require_peer(const char* what) const {
+    require_finalized();
+    if (!halo_peer) throw std::invalid_argument(std::string(what) + ": halo_peer_init first");
+  }
+  void halo_peer_ipc_handle(void* out64) {
+    require_peer("halo_peer_ipc_handle");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+    cudaIpcMemHandle_t h;
+    GMPM_CUDA(cudaIpcGetMemHandle(&h, halo_window));
+    std::memcpy(out64, &h, sizeof(h));
+  }
+  // Another rank's window: either its CUDA IPC handle (other process) or its raw device pointer (same process).
+  void halo_peer_attach(uint32_t peer, const void* ipc_handle64, void* same_process_ptr) {
+    require_peer("halo_peer_attach");
+    if (peer >= halo_world || peer == halo_rank) throw std::invalid_argument("halo_peer_attach: bad peer rank");
+    if (halo_windows.base[peer]) throw std::invalid_argument("halo_peer_attach: peer already attached");
+    if (ipc_handle64) {
+      cudaIpcMemHandle_t h;
+      std::memcpy(&h, ipc_handle64, sizeof(h));
+      void* p = nullptr;
+      GMPM_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+      halo_windows.base[peer] = static_cast<unsigned char*>(p);
+      halo_window_ipc[peer] = true;
+    } else if (same_process_ptr) {
+      halo_windows.base[peer] = static_cast<unsigned char*>(same_process_ptr);
+    } else {
+      throw std::invalid_argument("halo_peer_attach: neither a handle nor a pointer");
+    }
+  }
+  // pack + peer stores + delivery flags, one kernel.  Returns the number of shared blocks.
+  uint32_t halo_peer_send() {
+    require_peer("halo_peer_send");
+    for (uint32_t q = 0; q < halo_world; ++q)
+      if (!halo_windows.base[q]) throw std::invalid_argument("halo_peer_send: not every peer window is attached");
+    if (halo_sent) throw std::invalid_argument("halo_peer_send: the previous exchange was not received");
+    const uint32_t n = halo_begin_exchange("halo_peer_send");
+    if (n > halo_win_cap)
+      throw std::runtime_error("halo_peer_send: more shared blocks than the peer windows were sized for (halo_peer_init cap_blocks)");
+    ++halo_xchg;
+    if (n) {
+      launch("halo_peer_send");
+      halo_peer_send_kernel<T><<<std::min<uint32_t>(n, persistent_ctas(4)), kHaloThreads, 0, stream>>>(
+          n, halo_list[halo_cur], halo_sharers[halo_cur], touched_epoch, p2g_epoch, g_mass, g_vel, halo_windows, halo_rank,
+          halo_world, halo_win_cap, halo_xchg, halo_dev_words + 4 + halo_cur, halo_dev_words + 3);
+      GMPM_CUDA(cudaGetLastError());
+    }
+    halo_sent = true;
+    return n;
+  }
+  // waits for the sharers' deliveries on the device and writes the rank-ordered sums into this rank's blocks
+  void halo_peer_recv() {
+    require_peer("halo_peer_recv");
+    if (!halo_sent) throw std::invalid_argument("halo_peer_recv without halo_peer_send");
+    if (halo_n) {
+      launch("halo_peer_recv");
+      halo_peer_recv_kernel<T><<<std::min<uint32_t>(halo_n, persistent_ctas(1)), kHaloThreads, 0, stream>>>(
+          halo_n, halo_list[halo_cur], halo_sharers[halo_cur], touched_epoch, p2g_epoch, g_mass, g_vel, halo_window, halo_rank,
+          halo_world, halo_win_cap, halo_xchg, halo_dev_words + 4 + halo_cur);
+      GMPM_CUDA(cudaGetLastError());
+    }
+    halo_sent = false;
   }
 
   cudaEvent_t timers[16]{};

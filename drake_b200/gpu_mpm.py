@@ -226,6 +226,28 @@ class GpuMpmState:
     def halo_unpack(self):
         check(self._f("halo_unpack")(self._h))
 
+    # peer mode: the exchange through receive windows in peer memory (gmpm_c.h)
+    def halo_peer_init(self, rank, world, cap_blocks=8192):
+        check(self._f("halo_peer_init")(self._h, rank, world, cap_blocks))
+
+    def halo_peer_window(self):
+        """-> (64-byte CUDA IPC handle, raw device pointer) of this rank's receive window."""
+        h = C.create_string_buffer(64)
+        p = C.c_void_p()
+        check(self._f("halo_peer_window")(self._h, h, C.byref(p)))
+        return h.raw, p.value
+
+    def halo_peer_attach(self, peer, ipc_handle=None, pointer=None):
+        check(self._f("halo_peer_attach")(self._h, peer, ipc_handle, pointer))
+
+    def halo_peer_send(self):
+        n = C.c_uint32()
+        check(self._f("halo_peer_send")(self._h, C.byref(n)))
+        return n.value
+
+    def halo_peer_recv(self):
+        check(self._f("halo_peer_recv")(self._h))
+
     def update_grid_part(self, mpm_bc, part):
         check(self._f("update_grid_part")(self._h, int(mpm_bc), int(part)))
 

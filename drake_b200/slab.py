@@ -19,6 +19,12 @@ A particle moves less than one grid block per substep, so the dilated set planne
 everything substep k+1 can touch (checked on the device; halo_pack raises otherwise).  Nothing in the
 substep blocks the host: the count of shared blocks travels through pinned memory one substep ahead.
 
+Peer mode (`SlabExchange(..., peer=True)`, <= 8 ranks of one NVSwitch domain) takes the collective off the
+critical path altogether: every rank owns a receive window in device memory that the others map through
+CUDA IPC; `halo_peer_send` stores a rank's block values straight into the windows of the ranks sharing
+each block and raises their delivery flags, `halo_peer_recv` waits for its sharers on the device and sums
+in ascending rank order.  NCCL then only carries the 1-byte-per-block flags of the plan, on the side stream.
+
 `backend` is anything with those four methods returning torch tensors that alias its buffers: the GPU
 backend below wraps a GpuMpmState (tensors alias device memory, collectives are enqueued on the state's
 own CUDA streams); the CPU tests drive the same protocol class with a backend built on the oracle.
@@ -84,15 +90,34 @@ class GpuHaloBackend:
     def halo_unpack(self):
         self.state.halo_unpack()
 
+    def halo_peer_send(self):
+        return self.state.halo_peer_send()
+
+    def halo_peer_recv(self):
+        self.state.halo_peer_recv()
+
 
 class SlabExchange:
     """Runs the exchange protocol over a torch.distributed process group (NCCL on GPUs, gloo on CPU)."""
 
-    def __init__(self, backend, group=None):
+    def __init__(self, backend, group=None, peer=False, peer_cap_blocks=8192):
         import torch.distributed as dist
         self.backend = backend
         self.dist = dist
         self.group = group
+        self.peer = bool(peer)
+        if self.peer:
+            # windows: allocate, publish the CUDA IPC handles, map everybody else's (once; they never move)
+            rank, world = dist.get_rank(group), dist.get_world_size(group)
+            st = backend.state
+            st.halo_peer_init(rank, world, peer_cap_blocks)
+            handle, _ = st.halo_peer_window()
+            handles = [None] * world
+            dist.all_gather_object(handles, handle, group=group)
+            for q, h in enumerate(handles):
+                if q != rank:
+                    st.halo_peer_attach(q, ipc_handle=h)
+            dist.barrier(group=group)
         self.stream = getattr(backend, "stream", None)
         self.plan_stream = getattr(backend, "plan_stream", None)
         self.planned = False
@@ -121,6 +146,9 @@ class SlabExchange:
         and finish() and runs while the collective is in flight."""
         if not self.planned:
             self._plan()                          # start-up: plan from the current (dilated) touched set
+        if self.peer:
+            self.last_n_shared = self.backend.halo_peer_send()
+            return self.last_n_shared
         packed = self.backend.halo_pack()         # every rank holds the same shared-block list
         self.last_n_shared = 0 if packed is None else packed.numel() // 256
         self._work = None
@@ -136,6 +164,10 @@ class SlabExchange:
 
     def finish(self):
         """Orders the state's stream after the all-reduce, writes the sums back, plans the next exchange."""
+        if self.peer:
+            self.backend.halo_peer_recv()
+            self._plan()
+            return
         if self._work is not None:
             if self.stream is not None:
                 import torch
@@ -158,10 +190,20 @@ class InProcessExchange:
     """The same protocol for several states living in ONE process (tests: two states on one GPU, or two
     oracles on the CPU): the all-reduces become explicit sums over the backends' tensors."""
 
-    def __init__(self, backends, sync=None):
+    def __init__(self, backends, sync=None, peer=False, peer_cap_blocks=8192):
         self.backends = backends
         self.sync = sync or (lambda: None)        # GPU states use several streams: order them by hand
         self.planned = False
+        self.peer = bool(peer)
+        if self.peer:                             # same process: the windows are shared by raw pointer
+            states = [b.state for b in backends]
+            for r, st in enumerate(states):
+                st.halo_peer_init(r, len(states), peer_cap_blocks)
+            ptrs = [st.halo_peer_window()[1] for st in states]
+            for r, st in enumerate(states):
+                for q, p in enumerate(ptrs):
+                    if q != r:
+                        st.halo_peer_attach(q, pointer=p)
 
     @staticmethod
     def _sum(ts):
@@ -183,10 +225,17 @@ class InProcessExchange:
     def begin(self):
         if not self.planned:
             self._plan()
+        if self.peer:                             # every send is enqueued before any recv starts to wait
+            return [b.halo_peer_send() for b in self.backends][0]
         self._packed = [b.halo_pack() for b in self.backends]
         return 0 if self._packed[0] is None else self._packed[0].numel() // 256
 
     def finish(self):
+        if self.peer:
+            for b in self.backends:
+                b.halo_peer_recv()
+            self._plan()
+            return
         self.sync()
         if self._packed[0] is not None:
             self._sum(self._packed)

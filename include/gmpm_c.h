@@ -180,6 +180,21 @@ int gmpm_device_sync(void);
   int gmpm_halo_plan_async_##SUF(gmpm_state_##SUF* s);                                              \
   int gmpm_halo_pack_##SUF(gmpm_state_##SUF* s, uint32_t* n_shared, void** packed_dev);             \
   int gmpm_halo_unpack_##SUF(gmpm_state_##SUF* s);                                                  \
+  /* Peer mode (<= 8 ranks of one NVSwitch domain): the exchange itself goes through receive windows  */\
+  /* in peer memory -- halo_peer_send stores this rank's block values straight into the windows of    */\
+  /* the ranks sharing each block and raises their delivery flags; halo_peer_recv waits for its       */\
+  /* sharers ON THE DEVICE and sums in ascending rank order (identical bits on every sharer).  They    */\
+  /* replace halo_pack / all-reduce / halo_unpack; the plan half (halo_flags / halo_plan_async) is     */\
+  /* unchanged, its flags now carry 1 << rank.  Set-up, once, after finalize and before the first      */\
+  /* halo_flags: peer_init on every rank; peer_window yields the CUDA IPC handle (64 bytes; other      */\
+  /* processes) and the raw pointer (states of one process) of this rank's window; peer_attach maps    */\
+  /* every other rank's window (exactly one of ipc_handle64 / same_process_ptr non-NULL).              */\
+  int gmpm_halo_peer_init_##SUF(gmpm_state_##SUF* s, uint32_t rank, uint32_t world, uint32_t cap_blocks); \
+  int gmpm_halo_peer_window_##SUF(gmpm_state_##SUF* s, unsigned char* ipc_handle64, void** local_ptr); \
+  int gmpm_halo_peer_attach_##SUF(gmpm_state_##SUF* s, uint32_t peer, const unsigned char* ipc_handle64, \
+                                  void* same_process_ptr);                                          \
+  int gmpm_halo_peer_send_##SUF(gmpm_state_##SUF* s, uint32_t* n_shared);                           \
+  int gmpm_halo_peer_recv_##SUF(gmpm_state_##SUF* s);                                               \
   /* UpdateGrid and GridToParticle in two parts, to hide the all-reduce of the exchange: part 0 =    */\
   /* the blocks that are not exchanged and the particles whose stencils stay clear of exchanged     */\
   /* blocks (run between halo_pack and halo_unpack, while the all-reduce is in flight), part 1 = the */\

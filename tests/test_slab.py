@@ -241,6 +241,68 @@ def test_two_states_one_gpu_overlapped_parts_match_plain_order():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("n_states,overlap", [(2, False), (3, False), (2, True)])
+def test_peer_window_exchange_matches_single_state(n_states, overlap):
+    """Peer mode: the block sums travel through receive windows (stores into the sharers' windows, delivery
+    flags, device-side wait, rank-ordered sums) instead of an all-reduce.  Several states on ONE GPU share
+    their windows by raw pointer; with 3 states some blocks have three sharers."""
+    from drake_b200.gpu_mpm import GpuMpmSolver
+    import torch
+    dtype = np.float64
+    sheets = sheets_scene(dtype, n_sheets=6, res=40)
+    sv = GpuMpmSolver()
+    full = make_state(dtype, sheets)
+    parts = slab.partition_meshes(len(sheets), n_states)
+    sts = [make_state(dtype, [sheets[i] for i in p]) for p in parts]
+
+    def sync_all():
+        for s in sts:
+            sv.GpuSync(s)
+        torch.cuda.synchronize()
+
+    ex = slab.InProcessExchange([slab.GpuHaloBackend(s) for s in sts], sync=sync_all, peer=True, peer_cap_blocks=4096)
+    shared = 0
+    for it in range(12):
+        sort = it == 5
+        slab.substep(sv, full, None, DT, -1, sort)
+        for s in sts:
+            sv.RebuildMapping(s, sort)
+            sv.CalcFemStateAndForce(s, DT)
+            sv.ParticleToGrid(s, DT)
+        if overlap:
+            shared += ex.begin()
+            for s in sts:
+                s.update_grid_part(-1, 0)
+                s.g2p_part(DT, 0)
+            ex.finish()
+            for s in sts:
+                s.update_grid_part(-1, 1)
+                s.g2p_part(DT, 1)
+        else:
+            shared += ex.exchange()
+            for s in sts:
+                sv.UpdateGrid(s, -1)
+                sv.GridToParticle(s, DT)
+    assert shared > 0
+    ref, _ = full.DumpCpuState()
+    scale = np.max(np.abs(ref))
+    for s, p in zip(sts, parts):
+        lo, hi = vert_range(sheets, p)
+        got, _ = s.DumpCpuState()
+        assert np.max(np.abs(got - ref[lo:hi])) <= 1e-10 * scale
+    # shared blocks carry identical bits on every sharer: grid velocities of the last substep agree exactly
+    v = [s.read("grid_v_star") for s in sts]
+    m = [s.read("grid_masses") for s in sts]
+    tf = [s.read("grid_touched_flags") for s in sts]
+    both = np.repeat((tf[0] > 0) & (tf[1] > 0), 64)    # cells of the blocks both ranks touched (block-major keys)
+    assert both.any()
+    np.testing.assert_array_equal(m[0][both], m[1][both])
+    np.testing.assert_array_equal(v[0].reshape(-1, 3)[both], v[1].reshape(-1, 3)[both])
+    with pytest.raises(Exception):
+        sts[0].halo_pack()                     # a peer-mode state has no packed buffer to all-reduce
+
+
+@pytest.mark.gpu
 def test_halo_call_order_is_checked():
     from drake_b200.gpu_mpm import GmpmError, GpuMpmSolver
     st = make_state(np.float64, sheets_scene(np.float64, n_sheets=1))
@@ -264,7 +326,7 @@ def test_halo_call_order_is_checked():
     sv.GridToParticle(st, DT)
 
 
-def _nccl_worker(rank, world, port, ret):
+def _nccl_worker(rank, world, port, ret, peer=False):
     import torch
     import torch.distributed as dist
     from drake_b200.gpu_mpm import GpuMpmSolver
@@ -277,7 +339,7 @@ def _nccl_worker(rank, world, port, ret):
         part = slab.partition_meshes(len(sheets), world)[rank]
         st = make_state(dtype, [sheets[i] for i in part], device=rank)
         sv = GpuMpmSolver()
-        ex = slab.SlabExchange(slab.GpuHaloBackend(st))
+        ex = slab.SlabExchange(slab.GpuHaloBackend(st), peer=peer, peer_cap_blocks=4096)
         shared = 0
         for it in range(20):
             slab.substep(sv, st, ex, DT, -1, it == 7, overlap=(it % 2 == 1))   # both orders
@@ -295,7 +357,9 @@ def _nccl_worker(rank, world, port, ret):
 
 
 @pytest.mark.gpu
-def test_nccl_world2_matches_single_process_oracle():
+@pytest.mark.parametrize("peer", [False, True])
+def test_nccl_world2_matches_single_process_oracle(peer):
+    """peer=True: windows mapped across the two processes through CUDA IPC, stores over NVLink."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
@@ -303,7 +367,7 @@ def test_nccl_world2_matches_single_process_oracle():
     world, port = 2, free_port()
     with mp.Manager() as m:
         ret = m.dict()
-        mp.spawn(_nccl_worker, args=(world, port, ret), nprocs=world, join=True)
+        mp.spawn(_nccl_worker, args=(world, port, ret, peer), nprocs=world, join=True)
         for r in range(world):
             err, shared = ret[r]
             assert err <= 1e-9, (r, err)
