@@ -88,7 +88,7 @@ halo_count_kernel(uint32_t n_blocks, const uint8_t* __restrict__ flags, uint32_t
 __global__ void __launch_bounds__(kHaloThreads)
 halo_compact_kernel(uint32_t n_blocks, const uint8_t* __restrict__ flags, const uint32_t* __restrict__ cta_counts,
                     uint32_t* __restrict__ list, uint32_t list_cap, uint32_t* __restrict__ n_shared, bool bits,
-                    uint8_t* __restrict__ sharers, uint32_t* __restrict__ union_out) {
+                    uint8_t* __restrict__ sharers, uint32_t* __restrict__ union_out, uint32_t rank) {
   __shared__ uint32_t s_warp[kHaloThreads / 32];
   __shared__ uint32_t s_base;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -103,7 +103,7 @@ halo_compact_kernel(uint32_t n_blocks, const uint8_t* __restrict__ flags, const 
   const uint32_t m = halo_shared_mask(flags, n_blocks, b0, bits);
   const uint32_t c = __popc(m);
   uint32_t incl = c;
-  uint32_t who = 0;  // ranks this thread's shared blocks are shared with (peer mode)
+  uint32_t who = 0;  // ranks this rank shares one of this thread's blocks with (peer mode)
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const uint32_t t = __shfl_up_sync(kFullMask, incl, o);
@@ -120,7 +120,7 @@ halo_compact_kernel(uint32_t n_blocks, const uint8_t* __restrict__ flags, const 
         list[off] = b0 + j;
         if (bits) {
           sharers[off] = flags[b0 + j];
-          who |= flags[b0 + j];
+          if ((flags[b0 + j] >> rank) & 1u) who |= flags[b0 + j];  // q in peers(r) <=> r in peers(q)
         }
       }
       ++off;
@@ -176,6 +176,13 @@ __global__ void halo_mark_kernel(uint32_t n, const uint32_t* __restrict__ list, 
 // needs the neighbour's next send, which follows the neighbour's current recv in stream order).
 // ------------------------------------------------------------------------------------------------
 constexpr int kHaloMaxPeers = 8;
+constexpr unsigned long long kHaloPeerTimeoutNs = 5000000000ull;  // a delivery takes microseconds
+constexpr uint32_t kHaloPeerTimeoutCode = 1u << 16;               // added to the error word the next exchange checks
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 constexpr size_t kHaloWindowHeader = 256;  // bytes reserved for the flags
 struct HaloWindows {
   unsigned char* base[kHaloMaxPeers];
@@ -229,11 +236,18 @@ __global__ void __launch_bounds__(kHaloThreads)
 halo_peer_recv_kernel(uint32_t n, const uint32_t* __restrict__ list, const uint8_t* __restrict__ sharers,
                       const uint32_t* __restrict__ touched_epoch, uint32_t epoch, T* __restrict__ g_mass,
                       T* __restrict__ g_vel, unsigned char* __restrict__ window, uint32_t rank, uint32_t world,
-                      uint32_t cap, uint32_t xchg, const uint32_t* __restrict__ union_mask) {
+                      uint32_t cap, uint32_t xchg, const uint32_t* __restrict__ union_mask, uint32_t* __restrict__ err) {
   const uint32_t peers = *union_mask & ~(1u << rank);
   if (threadIdx.x < world && ((peers >> threadIdx.x) & 1u)) {
     const uint32_t* flag = reinterpret_cast<const uint32_t*>(window) + threadIdx.x;
-    while ((int32_t)(ld_acquire_sys(flag) - xchg) < 0) __nanosleep(64);
+    const unsigned long long t0 = global_timer_ns();
+    while ((int32_t)(ld_acquire_sys(flag) - xchg) < 0) {
+      __nanosleep(64);
+      if (global_timer_ns() - t0 > kHaloPeerTimeoutNs) {  // a peer died or the call order differs between ranks
+        atomicAdd(err, kHaloPeerTimeoutCode);
+        break;
+      }
+    }
   }
   __syncthreads();
   const uint32_t c = threadIdx.x >> 6, l = threadIdx.x & 63u;

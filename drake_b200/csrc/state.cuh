@@ -779,7 +779,7 @@ struct State {
                                                     halo_dev_words + 4 + slot);
     halo_compact_kernel<<<ctas, kHaloThreads, 0, st>>>(k.n_blocks, halo_flags_d, halo_cta_counts, halo_list[slot],
                                                       (uint32_t)halo_cap, halo_dev_words + slot, halo_peer,
-                                                      halo_sharers[slot], halo_dev_words + 4 + slot);
+                                                      halo_sharers[slot], halo_dev_words + 4 + slot, halo_rank);
     GMPM_CUDA(cudaGetLastError());
     launches += 2;
   }
@@ -809,6 +809,9 @@ struct State {
     if (!halo_plan_pending) throw std::invalid_argument(std::string(what) + " without a plan (halo_flags / halo_plan first)");
     GMPM_CUDA(cudaEventSynchronize(ev_halo_plan));  // issued a whole substep ago (or just now at start-up)
     const int slot = halo_next_slot;
+    if (h_halo_words[2 * slot + 1] >= kHaloPeerTimeoutCode)
+      throw std::runtime_error("halo exchange: a rank waited 5 s for a peer's block values (peer-memory windows): a peer "
+                               "stopped, or the ranks do not issue the same sequence of exchanges");
     if (h_halo_words[2 * slot + 1] != 0)
       throw std::runtime_error("halo exchange: a particle block appeared outside the dilated block set planned one "
                                "substep earlier (a particle moved more than one grid block in a substep)");
@@ -938,7 +941,7 @@ struct State {
       launch("halo_peer_recv");
       halo_peer_recv_kernel<T><<<std::min<uint32_t>(halo_n, persistent_ctas(1)), kHaloThreads, 0, stream>>>(
           halo_n, halo_list[halo_cur], halo_sharers[halo_cur], touched_epoch, p2g_epoch, g_mass, g_vel, halo_window, halo_rank,
-          halo_world, halo_win_cap, halo_xchg, halo_dev_words + 4 + halo_cur);
+          halo_world, halo_win_cap, halo_xchg, halo_dev_words + 4 + halo_cur, halo_dev_words + 2);
       GMPM_CUDA(cudaGetLastError());
     }
     halo_sent = false;

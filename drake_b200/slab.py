@@ -232,6 +232,7 @@ class InProcessExchange:
 
     def finish(self):
         if self.peer:
+            self.sync()                           # one GPU, one host thread: no recv may spin ahead of a send
             for b in self.backends:
                 b.halo_peer_recv()
             self._plan()
