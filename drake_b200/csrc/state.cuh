@@ -766,10 +766,13 @@ struct State {
         (stage == GridStage::kMomentum && halo_nbr_epoch == p2g_epoch) ? halo_nbr : nullptr, halo_flags_d,
         halo_dev_words + 2, (uint8_t)(halo_peer ? 1u << halo_rank : 1u));
     GMPM_CUDA(cudaGetLastError());
-    GMPM_CUDA(cudaMemcpyAsync(halo_own, halo_flags_d, k.n_blocks, cudaMemcpyDeviceToDevice, stream));
-    halo_own_valid = true;
     GMPM_CUDA(cudaEventRecord(ev_halo_flags, stream));
     GMPM_CUDA(cudaStreamWaitEvent(halo_stream, ev_halo_flags, 0));
+    // this rank's own set, for the containment check of the next halo_flags (which waits for ev_halo_plan): copied
+    // on the side stream, before the all-reduce overwrites the flags in place
+    GMPM_CUDA(cudaMemcpyAsync(halo_own, halo_flags_d, k.n_blocks, cudaMemcpyDeviceToDevice, halo_stream));
+    GMPM_CUDA(cudaEventRecord(ev_halo_plan, halo_stream));  // re-recorded by halo_plan_async; orders a repeated halo_flags
+    halo_own_valid = true;
     halo_flags_out = true;
     return halo_flags_d;
   }
