@@ -164,6 +164,7 @@ __global__ void halo_mark_kernel(uint32_t n, const uint32_t* __restrict__ list, 
 // Every rank owns a receive WINDOW (one cudaMalloc, opened by the other ranks through CUDA IPC, or shared
 // by pointer when several states live in one process):
 //     uint32 flag[64]                      flag[r] = number of the last exchange rank r has delivered
+//     uint32 present[2][world][cap]        present[e & 1][r][i] = e if rank r touched block i in exchange e
 //     T      data[2][world][cap][4][64]    data[e & 1][r][i] = rank r's mass / momentum of shared block i
 // i indexes the shared-block list, which is identical on all ranks, so no per-pair lists are needed.
 //   send : for every listed block, this rank's values (zeros if it did not touch the block) are STORED into the
@@ -176,6 +177,7 @@ __global__ void halo_mark_kernel(uint32_t n, const uint32_t* __restrict__ list, 
 // needs the neighbour's next send, which follows the neighbour's current recv in stream order).
 // ------------------------------------------------------------------------------------------------
 constexpr int kHaloMaxPeers = 8;
+constexpr int kHaloPeerThreads = 128;                              // one CTA per listed block, two values per thread
 constexpr unsigned long long kHaloPeerTimeoutNs = 5000000000ull;  // a delivery takes microseconds
 constexpr uint32_t kHaloPeerTimeoutCode = 1u << 16;               // added to the error word the next exchange checks
 __device__ __forceinline__ unsigned long long global_timer_ns() {
@@ -183,14 +185,25 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-constexpr size_t kHaloWindowHeader = 256;  // bytes reserved for the flags
 struct HaloWindows {
   unsigned char* base[kHaloMaxPeers];
 };
+// Window layout: flag[64] | present[2][world][cap] | (256-byte aligned) data[2][world][cap][256]
+__host__ __device__ inline size_t halo_window_data_offset(uint32_t world, uint32_t cap) {
+  return (256 + sizeof(uint32_t) * 2 * (size_t)world * cap + 255) & ~(size_t)255;
+}
+template <typename T>
+__host__ __device__ inline size_t halo_window_bytes(uint32_t world, uint32_t cap) {
+  return halo_window_data_offset(world, cap) + sizeof(T) * 256 * 2 * (size_t)world * cap;
+}
+__device__ __forceinline__ uint32_t* halo_window_present(unsigned char* base, uint32_t parity, uint32_t world,
+                                                         uint32_t src, uint32_t cap, uint32_t i) {
+  return reinterpret_cast<uint32_t*>(base + 256) + ((size_t)parity * world + src) * cap + i;
+}
 template <typename T>
 __device__ __forceinline__ T* halo_window_data(unsigned char* base, uint32_t parity, uint32_t world, uint32_t src,
                                                uint32_t cap, uint32_t i) {
-  return reinterpret_cast<T*>(base + kHaloWindowHeader) + (((size_t)parity * world + src) * cap + i) * 256;
+  return reinterpret_cast<T*>(base + halo_window_data_offset(world, cap)) + (((size_t)parity * world + src) * cap + i) * 256;
 }
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -200,24 +213,38 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-
+template <typename T> struct Pair;
+template <> struct Pair<float> { using type = float2; };
+template <> struct Pair<double> { using type = double2; };
+// the 256 values of a block, [mass 64 | momentum 3 x 64], as 128 pairs: pair t of block g
 template <typename T>
-__global__ void __launch_bounds__(kHaloThreads)
+__device__ __forceinline__ typename Pair<T>::type* halo_block_pair(T* g_mass, T* g_vel, uint32_t g, uint32_t t) {
+  T* p = t < 32u ? g_mass + (size_t)g * 64 + 2u * t : g_vel + (size_t)g * 192 + 2u * (t - 32u);
+  return reinterpret_cast<typename Pair<T>::type*>(p);
+}
+
+// One CTA per listed block.  A block this rank did not touch sends nothing: its `present` word keeps an older
+// exchange number and the receivers read it as zeros.
+template <typename T>
+__global__ void __launch_bounds__(kHaloPeerThreads)
 halo_peer_send_kernel(uint32_t n, const uint32_t* __restrict__ list, const uint8_t* __restrict__ sharers,
-                      const uint32_t* __restrict__ touched_epoch, uint32_t epoch, const T* __restrict__ g_mass,
-                      const T* __restrict__ g_vel, HaloWindows win, uint32_t rank, uint32_t world, uint32_t cap,
+                      const uint32_t* __restrict__ touched_epoch, uint32_t epoch, T* __restrict__ g_mass,
+                      T* __restrict__ g_vel, HaloWindows win, uint32_t rank, uint32_t world, uint32_t cap,
                       uint32_t xchg, const uint32_t* __restrict__ union_mask, uint32_t* __restrict__ done) {
-  const uint32_t c = threadIdx.x >> 6, l = threadIdx.x & 63u;
-  for (uint32_t i = blockIdx.x; i < n; i += gridDim.x) {
-    const uint32_t g = list[i];
+  using P2 = typename Pair<T>::type;
+  const uint32_t i = blockIdx.x;
+  const uint32_t g = list[i];
+  if (touched_epoch[g] == epoch) {
     const uint32_t who = sharers[i] & ~(1u << rank);
-    const bool own = touched_epoch[g] == epoch;
-    const T v = !own ? T(0) : (c == 0 ? g_mass[(size_t)g * 64 + l] : g_vel[(size_t)g * 192 + (size_t)(c - 1) * 64 + l]);
+    const P2 v = *halo_block_pair<T>(g_mass, g_vel, g, threadIdx.x);
     for (uint32_t q = 0; q < world; ++q)
-      if ((who >> q) & 1u) halo_window_data<T>(win.base[q], xchg & 1u, world, rank, cap, i)[threadIdx.x] = v;
+      if ((who >> q) & 1u) {
+        reinterpret_cast<P2*>(halo_window_data<T>(win.base[q], xchg & 1u, world, rank, cap, i))[threadIdx.x] = v;
+        if (threadIdx.x == 0) *halo_window_present(win.base[q], xchg & 1u, world, rank, cap, i) = xchg;
+      }
+    __threadfence_system();  // this CTA's stores before its arrival below
   }
-  // all stores of all CTAs before the flags (threadFenceReduction pattern at system scope)
-  __threadfence_system();
+  // all stores of all CTAs before the delivery flags (threadFenceReduction pattern at system scope)
   __syncthreads();
   __shared__ bool s_last;
   if (threadIdx.x == 0) s_last = atomicAdd(done, 1u) == gridDim.x - 1;
@@ -232,17 +259,22 @@ halo_peer_send_kernel(uint32_t n, const uint32_t* __restrict__ list, const uint8
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kHaloThreads)
+__global__ void __launch_bounds__(kHaloPeerThreads)
 halo_peer_recv_kernel(uint32_t n, const uint32_t* __restrict__ list, const uint8_t* __restrict__ sharers,
                       const uint32_t* __restrict__ touched_epoch, uint32_t epoch, T* __restrict__ g_mass,
                       T* __restrict__ g_vel, unsigned char* __restrict__ window, uint32_t rank, uint32_t world,
-                      uint32_t cap, uint32_t xchg, const uint32_t* __restrict__ union_mask, uint32_t* __restrict__ err) {
-  const uint32_t peers = *union_mask & ~(1u << rank);
-  if (threadIdx.x < world && ((peers >> threadIdx.x) & 1u)) {
+                      uint32_t cap, uint32_t xchg, uint32_t* __restrict__ err) {
+  using P2 = typename Pair<T>::type;
+  const uint32_t i = blockIdx.x;
+  const uint32_t g = list[i];
+  if (touched_epoch[g] != epoch) return;  // not this rank's block now (the list is the dilated set)
+  const uint32_t who = sharers[i];
+  // wait for the deliveries of this block's other sharers
+  if (threadIdx.x < world && threadIdx.x != rank && ((who >> threadIdx.x) & 1u)) {
     const uint32_t* flag = reinterpret_cast<const uint32_t*>(window) + threadIdx.x;
     const unsigned long long t0 = global_timer_ns();
     while ((int32_t)(ld_acquire_sys(flag) - xchg) < 0) {
-      __nanosleep(64);
+      __nanosleep(32);
       if (global_timer_ns() - t0 > kHaloPeerTimeoutNs) {  // a peer died or the call order differs between ranks
         atomicAdd(err, kHaloPeerTimeoutCode);
         break;
@@ -250,22 +282,28 @@ halo_peer_recv_kernel(uint32_t n, const uint32_t* __restrict__ list, const uint8
     }
   }
   __syncthreads();
-  const uint32_t c = threadIdx.x >> 6, l = threadIdx.x & 63u;
-  for (uint32_t i = blockIdx.x; i < n; i += gridDim.x) {
-    const uint32_t g = list[i];
-    if (touched_epoch[g] != epoch) continue;  // not this rank's block now (the list is the dilated set)
-    T* cell = c == 0 ? g_mass + (size_t)g * 64 + l : g_vel + (size_t)g * 192 + (size_t)(c - 1) * 64 + l;
-    const uint32_t who = sharers[i];
-    T acc = T(0);
-    bool first = true;
-    for (uint32_t q = 0; q < world; ++q) {
-      if (!((who >> q) & 1u)) continue;
-      const T v = q == rank ? *cell : __ldcg(halo_window_data<T>(window, xchg & 1u, world, q, cap, i) + threadIdx.x);
-      acc = first ? v : acc + v;
-      first = false;
+  P2* cell = halo_block_pair<T>(g_mass, g_vel, g, threadIdx.x);
+  P2 acc;
+  bool first = true;
+  for (uint32_t q = 0; q < world; ++q) {  // ascending rank order: the same bits on every sharer
+    if (!((who >> q) & 1u)) continue;
+    P2 v;
+    if (q == rank) {
+      v = *cell;
+    } else if (__ldcg(halo_window_present(window, xchg & 1u, world, q, cap, i)) == xchg) {
+      v = __ldcg(reinterpret_cast<const P2*>(halo_window_data<T>(window, xchg & 1u, world, q, cap, i)) + threadIdx.x);
+    } else {
+      v.x = v.y = T(0);
     }
-    *cell = acc;
+    if (first) {
+      acc = v;
+      first = false;
+    } else {
+      acc.x += v.x;
+      acc.y += v.y;
+    }
   }
+  *cell = acc;
 }
 
 }  // namespace gmpm

@@ -155,6 +155,9 @@ struct State {
 
   // shared-block exchange (halo.cuh)
   uint8_t *halo_flags_d = nullptr, *halo_own = nullptr;
+  uint8_t* halo_flags_buf[2]{};   // the plans alternate between two flag buffers; the idle one is zeroed on the side stream
+  bool halo_flags_clean[2]{};
+  int halo_flags_idx = 0;
   uint8_t* halo_mark = nullptr;   // 1 for the blocks of the exchange in flight (part-wise UpdateGrid / G2P)
   uint32_t* halo_nbr = nullptr;   // per touched-list entry: outer-layer occupancy towards the 26 neighbours
   uint32_t halo_nbr_epoch = 0;    // P2G epoch halo_nbr was computed for
@@ -635,10 +638,7 @@ struct State {
         (uint32_t)N, order(), pb_work, (uint32_t)work_cap, g_vel, pos[cur], vol[cur], pid[cur], pos[nx], vel[nx], C[nx],
         vol[nx], pid[nx], slot_of_pid, key, forces, ctr, dt, k);
     GMPM_CUDA(cudaGetLastError());
-    if (halo_mark && halo_n) {  // marks of an exchange whose parts were not run separately
-      halo_mark_kernel<<<blocks_for(halo_n), kThreads, 0, stream>>>(halo_n, halo_list[halo_cur], 0, halo_mark);
-      ++launches;
-    }
+    halo_clear_marks();  // an exchange whose parts were started but finished with the plain calls
     forces_zero = true;
     cur = nx;
     keys_valid = true;   // g2p wrote the key of every new slot
@@ -658,6 +658,8 @@ struct State {
     if (!halo_mark) halo_init();
     assemble_momentum();
     if (stage != GridStage::kMomentum) throw std::invalid_argument("update_grid_part must follow ParticleToGrid");
+    if (!halo_mark) halo_init();
+    halo_set_marks();
     launch(part ? "grid_update_shared" : "grid_update_interior");
     grid_kernel<T, false, true><<<persistent_ctas(4), kThreads, 0, stream>>>(
         touched_list[tl_cur], ctr, tiles, pb_tile, pb_epoch, bin_epoch, g_mass, g_vel, g_vstar, bc, k, nullptr,
@@ -681,6 +683,7 @@ struct State {
     } else if (stage != GridStage::kVelocity) {
       throw std::invalid_argument("g2p_part(1) must follow update_grid_part(1)");
     }
+    halo_set_marks();
     launch(part ? "g2p_shared" : "g2p_interior");
     const int nx = cur ^ 1;
     g2p_kernel<T><<<persistent_ctas(g2p_ctas_per_sm), kG2PWarps * 32, 0, stream>>>(
@@ -688,11 +691,7 @@ struct State {
         vol[nx], pid[nx], slot_of_pid, key, forces, ctr, dt, k, halo_mark, part);
     GMPM_CUDA(cudaGetLastError());
     if (part == 1) {
-      if (halo_n) {  // the marks of this exchange are spent
-        launch("halo_mark");
-        halo_mark_kernel<<<blocks_for(halo_n), kThreads, 0, stream>>>(halo_n, halo_list[halo_cur], 0, halo_mark);
-        GMPM_CUDA(cudaGetLastError());
-      }
+      halo_clear_marks();  // the marks of this exchange are spent
       forces_zero = true;
       cur = nx;
       keys_valid = true;
@@ -707,7 +706,11 @@ struct State {
   // exchange:  halo_pack  -> [all-reduce on stream]      -> halo_unpack          (between P2G and UpdateGrid)
   void halo_init() {
     if (halo_flags_d) return;
-    halo_flags_d = dalloc<uint8_t>(k.n_blocks);
+    for (int i = 0; i < 2; ++i) {
+      halo_flags_buf[i] = dalloc<uint8_t>(k.n_blocks);  // zero-initialised
+      halo_flags_clean[i] = true;
+    }
+    halo_flags_d = halo_flags_buf[0];
     halo_own = dalloc<uint8_t>(k.n_blocks);
     halo_nbr = dalloc<uint32_t>(k.n_blocks);
     halo_mark = dalloc<uint8_t>(k.n_blocks);
@@ -758,8 +761,12 @@ struct State {
     halo_init();
     // the previous plan chain (halo stream) still reads the flag buffers
     GMPM_CUDA(cudaStreamWaitEvent(stream, ev_halo_plan, 0));
-    note("memset");
-    GMPM_CUDA(cudaMemsetAsync(halo_flags_d, 0, k.n_blocks, stream));
+    halo_flags_d = halo_flags_buf[halo_flags_idx];
+    if (!halo_flags_clean[halo_flags_idx]) {  // only when halo_flags is repeated without a plan in between
+      note("memset");
+      GMPM_CUDA(cudaMemsetAsync(halo_flags_d, 0, k.n_blocks, stream));
+    }
+    halo_flags_clean[halo_flags_idx] = false;
     launch("halo_flags");
     halo_flags_kernel<<<persistent_ctas(2), kThreads, 0, stream>>>(
         touched_list[tl_cur], ctr, (uint32_t)k.domain_size >> 2, halo_own_valid ? halo_own : nullptr,
@@ -797,6 +804,13 @@ struct State {
                               halo_stream));
     GMPM_CUDA(cudaMemcpyAsync(h_halo_words + 2 * slot + 1, halo_dev_words + 2, sizeof(uint32_t),
                               cudaMemcpyDeviceToHost, halo_stream));
+    // the other flag buffer belongs to the plan the current exchange has already consumed: zero it for the next
+    // halo_flags here, off the compute stream
+    if (!halo_flags_clean[halo_flags_idx ^ 1]) {
+      GMPM_CUDA(cudaMemsetAsync(halo_flags_buf[halo_flags_idx ^ 1], 0, k.n_blocks, halo_stream));
+      halo_flags_clean[halo_flags_idx ^ 1] = true;
+    }
+    halo_flags_idx ^= 1;
     GMPM_CUDA(cudaEventRecord(ev_halo_plan, halo_stream));
     halo_flags_out = false;
     halo_next_slot = slot;
@@ -830,12 +844,24 @@ struct State {
     halo_n = n;
     GMPM_CUDA(cudaStreamWaitEvent(stream, ev_halo_plan, 0));
     assemble_momentum();
-    if (n) {
-      launch("halo_mark");
-      halo_mark_kernel<<<blocks_for(n), kThreads, 0, stream>>>(n, halo_list[slot], 1, halo_mark);
-      GMPM_CUDA(cudaGetLastError());
-    }
     return n;
+  }
+  // mark[b] = 1 for the blocks of the exchange in flight: only the part-wise UpdateGrid / G2P read them, so they
+  // are set when the first part call arrives and cleared after the last
+  bool halo_marked = false;
+  void halo_set_marks() {
+    if (halo_marked || !halo_n) return;
+    launch("halo_mark");
+    halo_mark_kernel<<<blocks_for(halo_n), kThreads, 0, stream>>>(halo_n, halo_list[halo_cur], 1, halo_mark);
+    GMPM_CUDA(cudaGetLastError());
+    halo_marked = true;
+  }
+  void halo_clear_marks() {
+    if (!halo_marked) return;
+    launch("halo_mark");
+    halo_mark_kernel<<<blocks_for(halo_n), kThreads, 0, stream>>>(halo_n, halo_list[halo_cur], 0, halo_mark);
+    GMPM_CUDA(cudaGetLastError());
+    halo_marked = false;
   }
   // Packs this rank's share of the planned shared blocks; returns their number (known on the host).
   uint32_t halo_pack() {
@@ -876,7 +902,7 @@ struct State {
     halo_init();
     halo_reserve(cap_blocks);
     halo_win_cap = (uint32_t)halo_cap;
-    halo_window_bytes = kHaloWindowHeader + sizeof(T) * 256 * 2 * (size_t)world * halo_win_cap;
+    halo_window_bytes = gmpm::halo_window_bytes<T>(world, halo_win_cap);
     GMPM_CUDA(cudaMalloc((void**)&halo_window, halo_window_bytes));
     GMPM_CUDA(cudaMemsetAsync(halo_window, 0, halo_window_bytes, stream));
     GMPM_CUDA(cudaStreamSynchronize(stream));
@@ -928,7 +954,7 @@ struct State {
     ++halo_xchg;
     if (n) {
       launch("halo_peer_send");
-      halo_peer_send_kernel<T><<<std::min<uint32_t>(n, persistent_ctas(4)), kHaloThreads, 0, stream>>>(
+      halo_peer_send_kernel<T><<<n, kHaloPeerThreads, 0, stream>>>(
           n, halo_list[halo_cur], halo_sharers[halo_cur], touched_epoch, p2g_epoch, g_mass, g_vel, halo_windows, halo_rank,
           halo_world, halo_win_cap, halo_xchg, halo_dev_words + 4 + halo_cur, halo_dev_words + 3);
       GMPM_CUDA(cudaGetLastError());
@@ -942,9 +968,9 @@ struct State {
     if (!halo_sent) throw std::invalid_argument("halo_peer_recv without halo_peer_send");
     if (halo_n) {
       launch("halo_peer_recv");
-      halo_peer_recv_kernel<T><<<std::min<uint32_t>(halo_n, persistent_ctas(1)), kHaloThreads, 0, stream>>>(
+      halo_peer_recv_kernel<T><<<halo_n, kHaloPeerThreads, 0, stream>>>(
           halo_n, halo_list[halo_cur], halo_sharers[halo_cur], touched_epoch, p2g_epoch, g_mass, g_vel, halo_window, halo_rank,
-          halo_world, halo_win_cap, halo_xchg, halo_dev_words + 4 + halo_cur, halo_dev_words + 2);
+          halo_world, halo_win_cap, halo_xchg, halo_dev_words + 2);
       GMPM_CUDA(cudaGetLastError());
     }
     halo_sent = false;
