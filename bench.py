@@ -284,6 +284,19 @@ def main():
         for i in range(first, first + n):                  # the exchange sits between P2G and UpdateGrid
             slab.substep(sv, st, ex, DT, -1, i % SORT_EVERY == 0, overlap=overlap)
 
+    # host slack: the only call of the substep that can block is the start of the exchange (it waits for the
+    # plan issued one substep earlier); time spent there = how far the host runs ahead of the device
+    plan_wait = [0.0]
+    if ex is not None:
+        begin0 = ex.begin
+
+        def timed_begin():
+            t = time.perf_counter()
+            r = begin0()
+            plan_wait[0] += time.perf_counter() - t
+            return r
+        ex.begin = timed_begin
+
     sampler = ClockSampler(local)
     sampler.start()
 
@@ -294,12 +307,16 @@ def main():
     l0 = st.kernel_launches()
     shared0 = ex.bytes_reduced if ex else 0
     w0 = time.perf_counter()
+    plan_wait[0] = 0.0
     st.timer_mark(0)
     run_substeps(K)
     st.timer_mark(1)
+    w_enq = time.perf_counter()                            # host done enqueueing; the device may still be running
     sv.GpuSync(st)
     barrier()
     w1 = time.perf_counter()
+    print("[bench] rank %d: host enqueue %.3f ms/substep (of which %.3f waiting for the plan of the exchange), wall %.3f ms/substep" %
+          (rank, (w_enq - w0) / K * 1e3, plan_wait[0] / K * 1e3, (w1 - w0) / K * 1e3), file=sys.stderr)
     launches = st.kernel_launches() - l0
     ms = st.timer_elapsed_ms(0, 1)
     halo_bytes_per_step = (ex.bytes_reduced - shared0) / K if ex else 0
