@@ -214,6 +214,24 @@ def emit(line):
     os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (json.dumps(line) + "\n").encode())
 
 
+def bind_to_gpu_numa_node(torch, local):
+    """Multi-rank runs: keep this process (and the pinned position mirror it is about to allocate, first touch) on
+    the CPUs next to its GPU, so that 8 ranks do not push their 24 MB/substep snapshots through one socket."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        p = torch.cuda.get_device_properties(local)
+        try:
+            h = pynvml.nvmlDeviceGetHandleByPciBusId("%08x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id))
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        return sorted(os.sched_getaffinity(0))
+    except Exception as e:                      # affinity is an optimisation, never a requirement
+        print("[bench] no CPU affinity for GPU %d: %s" % (local, e), file=sys.stderr)
+        return None
+
+
 def main():
     global _REAL_STDOUT
     sys.stdout.flush()
@@ -246,6 +264,10 @@ def main():
     torch.cuda.set_device(local)
     dist = None
     if world > 1:
+        cpus = bind_to_gpu_numa_node(torch, local)
+        if cpus:
+            print("[bench] rank %d: bound to %d CPUs next to GPU %d (%d..%d)" % (rank, len(cpus), local, cpus[0], cpus[-1]),
+                  file=sys.stderr)
         import torch.distributed as dist_mod
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         # the two all-reduces per substep are small (<= 4 MB) and latency bound: the low-latency protocol on the
