@@ -27,6 +27,12 @@ class AnalyticGeometry(C.Structure):
                 ("velocity", C.c_double * 3), ("p_WB", C.c_double * 3)]
 
 
+class DriverStats(C.Structure):
+    """Mirror of gmpm_driver_stats."""
+    _fields_ = [("substeps", C.c_int), ("contact_queries", C.c_int), ("newton_iterations", C.c_int),
+                ("newton_iterations_max", C.c_int), ("contact_pairs", C.c_uint64), ("last_residual", C.c_double)]
+
+
 class ContactStats(C.Structure):
     _fields_ = [("iterations", C.c_int), ("grid_dofs", C.c_int), ("line_search_evals", C.c_int),
                 ("reserved", C.c_int), ("residual", C.c_double), ("energy", C.c_double)]
@@ -38,7 +44,7 @@ PLAIN_SYMBOLS = ["gmpm_default_params", "gmpm_last_error", "gmpm_version", "gmpm
 TYPED_SYMBOLS = ["create", "destroy", "add_qr_cloth", "finalize", "rebuild_mapping", "calc_fem", "p2g",
                  "update_grid", "g2p", "sync", "sync_particle_state_to_cpu", "sync_particle_state_to_cpu_async",
                  "positions_host", "halo_flags", "halo_plan_async", "halo_pack", "halo_unpack", "halo_peer_init", "halo_peer_window", "halo_peer_attach", "halo_peer_send", "halo_peer_recv", "update_grid_part", "g2p_part", "stream", "halo_stream", "copy_contact_pairs",
-                 "generate_contact_pairs", "update_contact", "reallocate_external_bodies", "external_body_force_to_host",
+                 "generate_contact_pairs", "run_driver_substeps", "update_contact", "reallocate_external_bodies", "external_body_force_to_host",
                  "dump_cpu_state", "n_verts", "n_faces", "n_particles", "n_cells", "num_contacts",
                  "grid_touched_cnt_host", "read", "checkpoint_bytes", "save_state", "load_state", "run_substeps", "kernel_launches", "set_profiling",
                  "kernel_time", "profile_report", "timer_mark", "timer_elapsed_ms", "device_bytes",
@@ -111,6 +117,8 @@ def _declare(L):
         g("copy_contact_pairs").argtypes = [vp, sz] + [vp] * 7
         g("generate_contact_pairs").argtypes = [vp, C.POINTER(AnalyticGeometry), sz, C.POINTER(C.c_size_t)]
         g("update_contact").argtypes = [vp, ct, ct, ct, ct, C.c_int, C.c_int, C.POINTER(ContactStats)]
+        g("run_driver_substeps").argtypes = [vp, C.c_int, ct, C.c_int, C.c_int, C.POINTER(AnalyticGeometry), sz, C.c_int,
+                                             ct, ct, ct, C.c_int, C.c_int, C.POINTER(DriverStats)]
         g("reallocate_external_bodies").argtypes = [vp, sz]
         g("external_body_force_to_host").argtypes = [vp, vp, vp]
         g("dump_cpu_state").argtypes = [vp, vp, vp]

@@ -155,7 +155,7 @@ size_t State<T>::generate_contact_pairs(const gmpm_analytic_geometry* geoms, siz
       h[i].p[d] = T(g.p_WB[d]);
     }
   }
-  if (!snapshot_valid) positions_async();  // same data the host query would read: the last position snapshot
+  if (!snapshot_valid) snapshot_positions_device();  // same data the host query would read: the last position snapshot
   const uint64_t n_items = (uint64_t)N * n_geoms;
   const uint32_t ctas = (uint32_t)((n_items + kGenItemsPerCta - 1) / kGenItemsPerCta);
   if (ctas > gen_cap) {
@@ -193,6 +193,61 @@ size_t State<T>::generate_contact_pairs(const gmpm_analytic_geometry* geoms, siz
                                                                     pid_of_vis[vis_cur], slot_of_pid, vel[cur], c_vel);
   GMPM_CUDA(cudaGetLastError());
   return n;
+}
+
+// The DeformableDriver substep loop (deformable_driver.h:240-260) on the library side of the ABI, for scenes whose
+// rigid geometry is analytic: snapshot -> RebuildMapping -> FEM -> P2G -> UpdateGrid -> contact query ->
+// UpdateContact -> G2P, n times in one call.  `query_every` is MpmConfigParams::contact_query_frequency
+// (cpu_mpm_model.h:23, declared and never read upstream): the pairs are regenerated every query_every-th substep
+// (and after every visible re-sort, which renumbers the particles) and reused in between with their contact
+// velocities re-initialised.  The geometries move with their `velocity` from the pose they were given.
+template <typename T>
+void State<T>::run_driver_substeps(int n, T dt, int bc, int sort_every, const gmpm_analytic_geometry* geoms,
+                                   size_t n_geoms, int query_every, T mu, T stiffness, T damping, bool exact,
+                                   int max_it, gmpm_driver_stats* out) {
+  require_finalized();
+  if (n_geoms && !geoms) throw std::invalid_argument("run_driver_substeps: null geometry array");
+  if (query_every < 1) query_every = 1;
+  gmpm_driver_stats st{};
+  std::vector<gmpm_analytic_geometry> moved(geoms, geoms + n_geoms);
+  bool have_pairs = false;
+  for (int i = 0; i < n; ++i) {
+    const bool sort = sort_every > 0 && (i % sort_every) == 0;
+    const bool query = n_geoms && (!have_pairs || sort || (i % query_every) == 0);
+    rebuild_mapping(sort);
+    if (query) snapshot_positions_device();  // the positions SyncParticleStateToCpu would hand to the host query (:243)
+    calc_fem(dt);
+    p2g(dt);
+    update_grid(bc);
+    if (query) {
+      for (size_t g = 0; g < n_geoms; ++g)
+        for (int d = 0; d < 3; ++d) {
+          const double shift = geoms[g].velocity[d] * (double)dt * i;
+          moved[g].lo[d] = geoms[g].lo[d] + shift;
+          if (geoms[g].kind == GMPM_GEOM_BOX) moved[g].hi[d] = geoms[g].hi[d] + shift;
+          moved[g].p_WB[d] = geoms[g].p_WB[d] + shift;
+        }
+      generate_contact_pairs(moved.data(), n_geoms);
+      have_pairs = true;
+      ++st.contact_queries;
+    } else if (n_contacts) {
+      launch("contact_init_vel");
+      contact_init_vel_kernel<T><<<blocks_for(n_contacts), kThreads, 0, stream>>>(
+          (uint32_t)n_contacts, (uint32_t)N, c_pid, pid_of_vis[vis_cur], slot_of_pid, vel[cur], c_vel);
+      GMPM_CUDA(cudaGetLastError());
+    }
+    if (n_contacts) {
+      gmpm_contact_stats cs{};
+      update_contact(dt, mu, stiffness, damping, exact, max_it, &cs);
+      st.newton_iterations += cs.iterations;
+      if (cs.iterations > st.newton_iterations_max) st.newton_iterations_max = cs.iterations;
+      st.last_residual = cs.residual;
+    }
+    st.contact_pairs += n_contacts;
+    g2p(dt);
+    ++st.substeps;
+  }
+  if (out) *out = st;
 }
 
 }  // namespace gmpm

@@ -181,6 +181,14 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
       if (n_pairs) *n_pairs = n;                                                                               \
     });                                                                                                        \
   }                                                                                                            \
+  int gmpm_run_driver_substeps_##SUF(gmpm_state_##SUF* s, int n, T dt, int bc, int sort_every,                 \
+                                     const gmpm_analytic_geometry* geoms, size_t n_geoms, int query_every, T mu,\
+                                     T stiffness, T damping, int exact, int max_it, gmpm_driver_stats* stats) { \
+    return guarded([&] {                                                                                       \
+      s->st.run_driver_substeps(n, dt, bc, sort_every, geoms, n_geoms, query_every, mu, stiffness, damping,    \
+                                exact != 0, max_it, stats);                                                    \
+    });                                                                                                        \
+  }                                                                                                            \
   int gmpm_update_contact_##SUF(gmpm_state_##SUF* s, T dt, T mu, T stiffness, T damping, int exact, int max_it,\
                                 gmpm_contact_stats* stats) {                                                   \
     return guarded([&] { s->st.update_contact(dt, mu, stiffness, damping, exact != 0, max_it, stats); });      \

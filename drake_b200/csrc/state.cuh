@@ -1043,6 +1043,19 @@ struct State {
   // run under FEM / P2G / UpdateGrid: the gather to the reference's layout and visible order runs in
   // order on the compute stream (positions as of THIS call), the D2H runs on a copy stream into a
   // library-owned pinned mirror, and wait_positions() blocks on that copy alone.
+  // The device half alone: positions of this moment in the reference's layout and visible order in pos_stage
+  // (what the device-side contact query reads when nobody asked for a host copy).
+  void snapshot_positions_device() {
+    require_finalized();
+    if (N == 0) return;
+    if (!pos_stage) pos_stage = dalloc<T>(3 * N, false);
+    if (copy_pending) GMPM_CUDA(cudaStreamWaitEvent(stream, ev_copy, 0));  // staging buffer still being read
+    launch("gather_positions");
+    gather_particle_field_kernel<T><<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, 3, pos[cur],
+                                                                           pid_of_vis[vis_cur], slot_of_pid, pos_stage);
+    GMPM_CUDA(cudaGetLastError());
+    snapshot_valid = true;
+  }
   void positions_async() {
     require_finalized();
     if (N == 0) return;
@@ -1050,14 +1063,9 @@ struct State {
       GMPM_CUDA(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
       GMPM_CUDA(cudaEventCreateWithFlags(&ev_gather, cudaEventDisableTiming));
       GMPM_CUDA(cudaEventCreateWithFlags(&ev_copy, cudaEventDisableTiming));
-      pos_stage = dalloc<T>(3 * N, false);
       GMPM_CUDA(cudaHostAlloc((void**)&h_pos_mirror, sizeof(T) * 3 * N, cudaHostAllocDefault));
     }
-    if (copy_pending) GMPM_CUDA(cudaStreamWaitEvent(stream, ev_copy, 0));  // staging buffer still being read
-    launch("gather_positions");
-    gather_particle_field_kernel<T><<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, 3, pos[cur],
-                                                                           pid_of_vis[vis_cur], slot_of_pid, pos_stage);
-    GMPM_CUDA(cudaGetLastError());
+    snapshot_positions_device();
     GMPM_CUDA(cudaEventRecord(ev_gather, stream));
     GMPM_CUDA(cudaStreamWaitEvent(copy_stream, ev_gather, 0));
     GMPM_CUDA(cudaMemcpyAsync(h_pos_mirror, pos_stage, sizeof(T) * 3 * N, cudaMemcpyDeviceToHost, copy_stream));
@@ -1103,6 +1111,9 @@ struct State {
   }
 
   size_t read(const char* name, void* out, size_t cap);  // getters.cuh
+  void run_driver_substeps(int n, T dt, int bc, int sort_every, const gmpm_analytic_geometry* geoms, size_t n_geoms,
+                           int query_every, T mu, T stiffness, T damping, bool exact, int max_it,
+                           gmpm_driver_stats* out);      // contact_gen.cuh
   size_t checkpoint_bytes() const;                       // checkpoint.cuh
   size_t save_state(void* out, size_t cap);
   void load_state(const void* in, size_t bytes);

@@ -424,6 +424,13 @@ class GpuMpmSolver:
         """Device-side CalcMpmContactPairs + CopyContactPairs for analytic rigid geometry (boxes, spheres):
         `geometries` = list of dicts {kind: "box"|"sphere", rigid_id, lo, hi | center, radius, velocity, p_WB}.
         Returns the number of pairs; UpdateContact follows as after CopyContactPairs."""
+        arr = self._geometry_array(geometries)
+        n = C.c_size_t()
+        check(state._f("generate_contact_pairs")(state._h, arr, len(geometries), C.byref(n)))
+        return n.value
+
+    @staticmethod
+    def _geometry_array(geometries):
         arr = (_lib.AnalyticGeometry * max(1, len(geometries)))()
         for a, g in zip(arr, geometries):
             sphere = g.get("kind", "box") == "sphere"
@@ -435,9 +442,22 @@ class GpuMpmSolver:
             pwb = g.get("p_WB", lo if sphere else [0.5 * (x + y) for x, y in zip(lo, hi)])
             for d in range(3):
                 a.lo[d], a.hi[d], a.velocity[d], a.p_WB[d] = float(lo[d]), float(hi[d]), float(vel[d]), float(pwb[d])
-        n = C.c_size_t()
-        check(state._f("generate_contact_pairs")(state._h, arr, len(geometries), C.byref(n)))
-        return n.value
+        return arr
+
+    def RunDriverSubsteps(self, state, n, dt, geometries=(), mpm_bc=-1, sort_every=0, contact_query_frequency=1,
+                          friction_mu=0.0, stiffness=0.0, damping=0.0, exact_line_search=False, max_iterations=0):
+        """n substeps of the DeformableDriver loop (deformable_driver.h:240-260) in one ABI call, contact pairs
+        from analytic geometry generated on the device every `contact_query_frequency` substeps
+        (MpmConfigParams::contact_query_frequency).  Geometries move with their velocity.  -> DriverStats."""
+        geometries = list(geometries)
+        arr = self._geometry_array(geometries)
+        st = _lib.DriverStats()
+        ct = state._ct
+        check(state._f("run_driver_substeps")(state._h, int(n), ct(dt), int(mpm_bc), int(sort_every), arr, len(geometries),
+                                              int(contact_query_frequency), ct(friction_mu), ct(stiffness), ct(damping),
+                                              1 if exact_line_search else 0, int(max_iterations), C.byref(st)))
+        state._positions_pending = False
+        return st
 
     def UpdateContact(self, state, frame, substep, dt, friction_mu, stiffness, damping, dump=False,
                       exact_line_search=False, max_iterations=0):

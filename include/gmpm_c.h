@@ -71,6 +71,16 @@ typedef struct gmpm_contact_stats {
   double energy;         /* last accepted E1 (:531)                                            */
 } gmpm_contact_stats;
 
+/* Result of gmpm_run_driver_substeps. */
+typedef struct gmpm_driver_stats {
+  int substeps;
+  int contact_queries;       /* substeps in which the contact pairs were regenerated */
+  int newton_iterations;     /* summed over the substeps */
+  int newton_iterations_max; /* largest count of one substep */
+  uint64_t contact_pairs;    /* summed over the substeps */
+  double last_residual;
+} gmpm_driver_stats;
+
 /* Analytic rigid geometry for device-side contact-pair generation (gmpm_generate_contact_pairs). */
 enum { GMPM_GEOM_BOX = 0, GMPM_GEOM_SPHERE = 1 };
 typedef struct gmpm_analytic_geometry {
@@ -133,6 +143,17 @@ int gmpm_device_sync(void);
   /* penetration_distance = signed distance < 0 and normal = -gradient.  *n_pairs <- number of pairs.  */\
   int gmpm_generate_contact_pairs_##SUF(gmpm_state_##SUF* s, const gmpm_analytic_geometry* geoms,   \
                                         size_t n_geoms, size_t* n_pairs);                           \
+  /* The whole DeformableDriver substep loop (deformable_driver.h:240-260) n times in one call, for    */\
+  /* analytic rigid geometry: RebuildMapping (sorted every sort_every-th substep), FEM, P2G,          */\
+  /* UpdateGrid, device-side contact query, UpdateContact, G2P.  contact_query_frequency is           */\
+  /* MpmConfigParams::contact_query_frequency (cpu_mpm_model.h:23, unused upstream): pairs are        */\
+  /* regenerated every that many substeps (and after every re-sort) and reused in between.  The        */\
+  /* geometries move with their velocity from the given pose.  With n_geoms = 0 this is run_substeps.  */\
+  int gmpm_run_driver_substeps_##SUF(gmpm_state_##SUF* s, int n, T dt, int mpm_bc, int sort_every,  \
+                                     const gmpm_analytic_geometry* geoms, size_t n_geoms,           \
+                                     int contact_query_frequency, T friction_mu, T stiffness,       \
+                                     T damping, int exact_line_search, int max_iterations,          \
+                                     gmpm_driver_stats* stats);                                     \
   /* GpuMpmSolver<T>::UpdateContact, cuda_mpm_solver.cu:215-621.  max_iterations <= 0 -> 2000. */   \
   int gmpm_update_contact_##SUF(gmpm_state_##SUF* s, T dt, T friction_mu, T stiffness, T damping,   \
                                 int exact_line_search, int max_iterations,                          \

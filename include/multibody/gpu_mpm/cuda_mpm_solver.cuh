@@ -76,6 +76,22 @@ class GpuMpmSolver {
     return n;
   }
 
+  // Extension: n substeps of the DeformableDriver loop (deformable_driver.h:240-260) in one call,
+  // contact pairs regenerated on the device every params.contact_query_frequency substeps
+  // (cpu_mpm_model.h:23: declared upstream, never read) while the geometries move with their velocity.
+  gmpm_driver_stats RunDriverSubsteps(GpuMpmState<T>* state, int n, const T& dt,
+                                      const std::vector<gmpm_analytic_geometry>& geometries, int mpm_bc, int sort_every,
+                                      int contact_query_frequency, const T& friction_mu, const T& stiffness,
+                                      const T& damping, bool exact_line_search) const {
+    gmpm_driver_stats stats{};
+    internal::Check(Abi::run_driver_substeps(state->raw(), n, dt, mpm_bc, sort_every, geometries.data(),
+                                             geometries.size(), contact_query_frequency, friction_mu, stiffness, damping,
+                                             exact_line_search ? 1 : 0, 0, &stats),
+                    "RunDriverSubsteps");
+    state->total_contact_iteration_count += stats.newton_iterations;
+    return stats;
+  }
+
   // cuda_mpm_solver.cu:215-621.  `dump` (per-iteration JSON to a developer path) is not reproduced.
   void UpdateContact(GpuMpmState<T>* state, const int frame, const int substep, const T& dt, const T& friction_mu,
                      const T& stiffness, const T& damping, const bool dump, const bool exact_line_search) const {

@@ -316,3 +316,64 @@ def test_device_generated_pairs_equal_the_host_path(dtype):
                 # equal to rounding
                 assert rel(a_d[k], a_h[k], 1e-3) <= (1e-12 if dtype == np.float64 else 1e-4), k   # f32: one ulp of x ~ 0.5 on |dist| ~ 1e-3
         assert rel(p_d, p_h) <= (1e-12 if dtype == np.float64 else 1e-5)
+
+
+def test_library_side_driver_loop_equals_the_call_by_call_loop():
+    """gmpm_run_driver_substeps: the DeformableDriver substep loop in ONE ABI call, contact
+    pairs regenerated on the device while the geometries move, against the same loop issued call by call.
+    With contact_query_frequency = 3 the pairs are reused between queries."""
+    dtype = np.float64
+    n_steps, mu, k, d = 6, 0.3, 1e6, 1e-5
+    box_v = np.array([0.0, 0.0, 0.05])
+
+    def fresh():
+        st = GpuMpmState(dtype)
+        for pos, vel, tri in sheet_over_box(dtype):
+            st.AddQRCloth(pos, vel, tri)
+        st.Finalize()
+        st.ReallocateExternelBodies(2)
+        return st
+
+    def geom(i):
+        s = box_v * DT * i
+        return [{"kind": "box", "rigid_id": 1, "lo": np.array(BOX[0]) + s, "hi": np.array(BOX[1]) + s, "velocity": box_v,
+                 "p_WB": 0.5 * (np.array(BOX[0]) + np.array(BOX[1])) + s}]
+
+    sv = GpuMpmSolver()
+    a = fresh()
+    iters = pairs = 0
+    for i in range(n_steps):
+        sort = i % 4 == 0
+        sv.SyncParticleStateToCpu(a)
+        sv.RebuildMapping(a, sort)
+        sv.CalcFemStateAndForce(a, DT)
+        sv.ParticleToGrid(a, DT)
+        sv.UpdateGrid(a, -1)
+        pairs += sv.GenerateContactPairs(a, geom(i))
+        iters += sv.UpdateContact(a, 0, i, DT, mu, k, d, False, False, 5).iterations
+        sv.GridToParticle(a, DT)
+    b = fresh()
+    st = sv.RunDriverSubsteps(b, n_steps, DT, geom(0), -1, 4, 1, mu, k, d, False, 5)
+    assert st.substeps == n_steps and st.contact_queries == n_steps
+    assert st.contact_pairs == pairs and pairs > 50 * n_steps
+    assert st.newton_iterations == iters and st.newton_iterations_max <= 5
+    for name in ("positions", "velocities", "affine_matrices"):
+        assert rel(b.read(name), a.read(name)) <= 1e-11, name
+    a.ExternelBodyForceToHost()
+    b.ExternelBodyForceToHost()
+    fa, fb = a.external_forces_host().F_Bq_W_f, b.external_forces_host().F_Bq_W_f
+    assert np.max(np.abs(np.asarray(fa) - np.asarray(fb))) <= 1e-9 * max(1.0, np.max(np.abs(np.asarray(fa))))
+    # contact_query_frequency = 3: queries at substeps 0, 3 and at the re-sort of substep 4
+    c = fresh()
+    st3 = sv.RunDriverSubsteps(c, n_steps, DT, geom(0), -1, 4, 3, mu, k, d, False, 5)
+    assert st3.substeps == n_steps and st3.contact_queries == 3
+    assert st3.contact_pairs > 0 and np.all(np.isfinite(c.read("positions")))
+    assert rel(c.read("positions"), a.read("positions")) <= 1e-3        # stale pairs for at most two substeps
+    # no geometry: the plain loop
+    e, f = fresh(), fresh()
+    sv.RunSubsteps(e, 4, DT, -1, 2)
+    st0 = sv.RunDriverSubsteps(f, 4, DT, (), -1, 2)
+    assert st0.contact_queries == 0 and st0.contact_pairs == 0
+    assert rel(f.read("positions"), e.read("positions")) <= 1e-12
+    for s in (a, b, c, e, f):
+        s.Destroy()

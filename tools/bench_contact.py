@@ -32,6 +32,9 @@ def main():
     ap.add_argument("--f32", action="store_true")
     ap.add_argument("--device-pairs", action="store_true",
                     help="generate the contact pairs on the device (gmpm_generate_contact_pairs) instead of on the host")
+    ap.add_argument("--library-loop", action="store_true",
+                    help="the whole coupled loop in one ABI call (gmpm_run_driver_substeps), pairs generated on the device")
+    ap.add_argument("--query-every", type=int, default=1, help="contact_query_frequency of the library loop")
     ap.add_argument("--mu", type=float, default=1.0)
     ap.add_argument("--stiffness", type=float, default=1e6)
     ap.add_argument("--damping", type=float, default=1e-5)
@@ -51,6 +54,27 @@ def main():
     pad_v = [np.array([0.1, 0.0, 0.0]), np.array([-0.1, 0.0, 0.0])]
     sv.RunSubsteps(st, 20, DT, -1, 40)   # settle
     sv.GpuSync(st)
+
+    if args.library_loop:
+        geoms = [{"kind": "box", "rigid_id": b + 1, "lo": centers[b] - half, "hi": centers[b] + half,
+                  "velocity": pad_v[b], "p_WB": centers[b]} for b in range(2)]
+        t_begin = time.perf_counter()
+        ds = sv.RunDriverSubsteps(st, args.steps, DT, geoms, -1, 0, args.query_every, args.mu, args.stiffness,
+                                  args.damping, args.exact)
+        sv.GpuSync(st)
+        wall = time.perf_counter() - t_begin
+        st.ExternelBodyForceToHost()
+        f = st.external_forces_host().F_Bq_W_f
+        print(json.dumps({"workload": "cfg-4: %d sheets, N=%d, %s, two moving box pads, library-side driver loop, "
+                                      "contact_query_frequency=%d" % (args.sheets, N, np.dtype(dtype).name, args.query_every),
+                          "steps": args.steps, "particle_steps_per_sec_e2e": N * args.steps / wall,
+                          "ms_per_substep_e2e": wall / args.steps * 1e3, "contact_queries": ds.contact_queries,
+                          "contact_pairs_mean": ds.contact_pairs / max(1, ds.substeps),
+                          "newton_iterations_mean": ds.newton_iterations / max(1, ds.substeps),
+                          "newton_iterations_max": ds.newton_iterations_max,
+                          "pad_impulse_x": [float(f[1][0]), float(f[2][0])]}))
+        st.Destroy()
+        return
 
     iters, n_pairs, solve_ms, host_ms = [], [], [], []
     t_begin = time.perf_counter()
