@@ -200,7 +200,9 @@ size_t State<T>::generate_contact_pairs(const gmpm_analytic_geometry* geoms, siz
 // UpdateContact -> G2P, n times in one call.  `query_every` is MpmConfigParams::contact_query_frequency
 // (cpu_mpm_model.h:23, declared and never read upstream): the pairs are regenerated every query_every-th substep
 // (and after every visible re-sort, which renumbers the particles) and reused in between with their contact
-// velocities re-initialised.  The geometries move with their `velocity` from the pose they were given.
+// velocities re-initialised.  The geometries move with their `velocity` from the pose they were given.  The
+// position snapshot is taken AFTER RebuildMapping: pair indices are visible indices and a re-sort renumbers
+// them (upstream's driver never sorts in this loop, deformable_driver.h:244).
 template <typename T>
 void State<T>::run_driver_substeps(int n, T dt, int bc, int sort_every, const gmpm_analytic_geometry* geoms,
                                    size_t n_geoms, int query_every, T mu, T stiffness, T damping, bool exact,
