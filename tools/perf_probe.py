@@ -16,8 +16,14 @@ def main():
         if a.startswith("--sheets="):
             n_sheets = int(a.split("=")[1])
     big = "--grid256" in sys.argv   # the multi-GPU configuration: 256^3 cells, dx = 1/128, far octant
-    st = GpuMpmState(dtype, **({"domain_bits": 8, "dx": 1.0 / 128} if big else {}))
-    for pos, vel, tri in scenes.stacked_sheets(n_sheets, dtype=dtype):
+    huge = "--grid512" in sys.argv  # cfg-3 / cfg-5 of BASELINE.json: 2^9 grid bits (4 m domain at dx = 1/128), tall stacks
+    dz = 0.02
+    for a in sys.argv:
+        if a.startswith("--dz="):
+            dz = float(a.split("=")[1])
+    params = {"domain_bits": 9, "dx": 1.0 / 128} if huge else ({"domain_bits": 8, "dx": 1.0 / 128} if big else {})
+    st = GpuMpmState(dtype, **params)
+    for pos, vel, tri in scenes.stacked_sheets(n_sheets, dz=dz, dtype=dtype):
         if big:
             pos = (pos.astype(np.float64) + np.array([1.0, 1.0, 0.68])).astype(dtype)
         st.AddQRCloth(pos, vel, tri)
