@@ -325,6 +325,28 @@ def test_cell_size_decoupled_from_cell_count():
     assert np.array_equal(st.read("pids"), orc.read("pids"))
 
 
+def test_grid512_equals_grid128_in_the_same_cells():
+    """BASELINE cfg-3 / cfg-5 use 2^9 grid bits (27-bit cell keys, three radix passes).  A scene in the [0,1]^3
+    corner of the 512^3 grid at dx = 1/128 occupies the same cells as on the 128^3 grid, and Morton order within
+    that octant is the same, so the particles must agree (the far walls are out of reach) and so must the
+    visible order after a re-sort."""
+    dtype = np.float64
+    sheets = small_scene(dtype, res=30, warm=True)
+    runs = []
+    for params in ({}, {"domain_bits": 9, "dx": 1.0 / 128}):
+        st = GpuMpmState(dtype, **params)
+        for pos, vel, tri in sheets:
+            st.AddQRCloth(pos, vel, tri)
+        st.Finalize()
+        GpuMpmSolver().RunSubsteps(st, 12, 1e-3, -1, 5)
+        runs.append({n: st.read(n) for n in ("positions", "velocities", "affine_matrices", "pids", "index_mappings")})
+        st.Destroy()
+    a, b = runs
+    assert np.array_equal(a["pids"], b["pids"]) and np.array_equal(a["index_mappings"], b["index_mappings"])
+    for n in ("positions", "velocities", "affine_matrices"):
+        assert np.max(np.abs(a[n] - b[n])) <= 1e-11 * max(1.0, np.max(np.abs(a[n]))), n
+
+
 def test_near_walls_and_block_corners():
     """Particles whose stencils straddle block corners and the 3-cell sticky walls."""
     dtype = np.float64
