@@ -317,18 +317,23 @@ fem_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ fid, const int*
            const int* __restrict__ slot_of_pid,
            const T* __restrict__ vol, const T* __restrict__ C, const T* __restrict__ Dm_inv, T* __restrict__ pos,
            T* __restrict__ vel, T* __restrict__ Fd, T* __restrict__ forces, T* __restrict__ taus,
-           uint32_t* __restrict__ key, T dt, Consts<T> k) {
+           uint32_t* __restrict__ key, T dt, Consts<T> k, bool reverse) {
   const uint32_t stride = gridDim.x * blockDim.x;
   uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+  // Traversal order: G2P, which ran just before, wrote the particle state in ascending slot order and the face
+  // records are in slot order too, so walking them from the END meets the lines G2P wrote last while they are
+  // still in L2 (walking from the start meets only lines the rest of G2P has already evicted).
+  auto rec = [&](uint32_t ff) -> uint32_t { return reverse ? n_faces - 1u - ff : ff; };
   // two index levels, each resolved one iteration ahead of its use (an in-order warp stalls at the first
   // instruction whose operand is still in flight, so a dependent pair of loads must not share an iteration)
   auto level1 = [&](uint32_t ff) -> FemIdx {  // particle ids of the record: face particle, three vertices
     FemIdx r{0, 0, 0, 0};
     if (ff < n_faces) {
-      r.sf = fid[ff];
-      r.s0 = tri[ff];
-      r.s1 = tri[n_faces + ff];
-      r.s2 = tri[2 * n_faces + ff];
+      const uint32_t j = rec(ff);
+      r.sf = fid[j];
+      r.s0 = tri[j];
+      r.s1 = tri[n_faces + j];
+      r.s2 = tri[2 * n_faces + j];
     }
     return r;
   };
@@ -339,6 +344,7 @@ fem_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ fid, const int*
   FemIdx ids_n = level1(f + stride);  // particle ids of face f + stride
   for (; f < n_faces; f += stride) {
     const int sf = cur.sf, s0 = cur.s0, s1 = cur.s1, s2 = cur.s2;
+    const uint32_t j = rec(f);  // record index
     // ---- every load of this face, before any use
     T x0[3], x1[3], x2[3], v0[3], v1[3], v2[3], F[9], Cm[9], Dmi[4];
 #pragma unroll
@@ -352,11 +358,11 @@ fem_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ fid, const int*
     }
 #pragma unroll
     for (int e = 0; e < 9; ++e) {
-      F[e] = Fd[(size_t)e * n_faces + f];
+      F[e] = Fd[(size_t)e * n_faces + j];
       Cm[e] = C[(size_t)e * N + sf];
     }
 #pragma unroll
-    for (int e = 0; e < 4; ++e) Dmi[e] = Dm_inv[(size_t)e * n_faces + f];
+    for (int e = 0; e < 4; ++e) Dmi[e] = Dm_inv[(size_t)e * n_faces + j];
     const T volume = vol[sf];
     // ---- indices of this thread's next faces (in flight during the math below)
     cur = level2(ids_n);                 // ids_n arrived during the previous iteration
@@ -392,7 +398,7 @@ fem_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ fid, const int*
       ctF[d * 3 + 1] = a * Dmi[1] + b * Dmi[3];
     }
 #pragma unroll
-    for (int e = 0; e < 9; ++e) Fd[(size_t)e * n_faces + f] = ctF[e];
+    for (int e = 0; e < 9; ++e) Fd[(size_t)e * n_faces + j] = ctF[e];
 
     T VP[9];
     cloth_pk1(k, ctF, VP);

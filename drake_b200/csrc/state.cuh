@@ -180,6 +180,7 @@ struct State {
   bool halo_window_ipc[kHaloMaxPeers]{};         // opened with cudaIpcOpenMemHandle (to be closed)
   uint8_t* halo_sharers[2]{};                    // sharer set of each listed block
   bool halo_sent = false;
+  bool fem_reverse = std::getenv("GMPM_FEM_FORWARD") == nullptr;  // fem_kernel: walk the face records from the end
 
   std::vector<void*> allocs;
   size_t device_bytes = 0;
@@ -558,7 +559,7 @@ struct State {
       launch("fem");
       const uint32_t ctas = std::min<uint32_t>(blocks_for(n_faces, kFemThreads), persistent_ctas(fem_ctas_per_sm));
       fem_kernel<T><<<ctas, kFemThreads, 0, stream>>>((uint32_t)n_faces, (uint32_t)N, fid, tri, slot_of_pid, vol[cur], C[cur],
-                                                      Dm_inv, pos[cur], vel[cur], Fd, forces, taus, key, dt, k);
+                                                      Dm_inv, pos[cur], vel[cur], Fd, forces, taus, key, dt, k, fem_reverse);
       GMPM_CUDA(cudaGetLastError());
       bin_valid = false;  // face particles moved to their centroids
     }
