@@ -32,8 +32,10 @@ struct DevCounters {
   uint32_t n_big;          // work records of blocks with more particles than the average (front of pb_work)
   uint32_t n_small;        // ... the others (back of pb_work, growing down)
   uint32_t n_tiles;        // P2G tiles handed out (one per work record)
-  uint32_t win_lo[3];      // bounding box of the particle blocks (binning window), reset by the binning kernel
-  uint32_t win_hi[3];
+  uint32_t win_lo[3];      // bounding box of the particle blocks of the LAST binning (dilated Morton fields), from
+  uint32_t win_hi[3];      // which the next binning predicts its sort window; lo = 0xFFFFFFFF: none yet
+  uint32_t win_violation;  // a key fell outside the predicted window (the sort fell back to absolute keys)
+  uint32_t win_fallbacks;  // how often that happened (instrumentation)
   uint32_t sort_passes;    // passes the last binning sort ran (instrumentation)
   uint32_t phase_ns[8];    // binning kernel: ns from start to the end of window / sort / ranges / records (block 0)
 };
@@ -178,57 +180,76 @@ __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs 
   const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
   SortWindow win{};
   if (a.window) {
-    // bounding box of the particle blocks, per axis on the DILATED fields of the Morton block id (dilation is
-    // monotonic, so min / max need no decoding); ctr->win_* are reset at the end of the kernel
-    uint32_t lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0u, 0u, 0u};
-    for (uint32_t i = tid; i < a.N; i += nth) {
-      const uint32_t b = __ldcg(a.sort.keys_in + i) >> 6;
-      const uint32_t c[3] = {b & kMortonX, b & kMortonY, b & kMortonZ};
+    // Sort window = bounding box of the particle blocks, per axis on the DILATED fields of the Morton block id
+    // (dilation is monotonic, so min / max need no decoding).  Normally it is PREDICTED: the box of the previous
+    // binning (left in ctr->win_* by its last phase) grown by one block -- a particle moves less than a cell per
+    // substep -- which costs no pass over the keys and no barrier; pass 0 of the sort verifies it and falls back to
+    // the absolute keys if a key lies outside.  Only the first binning of a state measures the box up front.
+    const int axis_bits = (a.key_bits - 6) / 3;
+    const uint32_t axis_max = (1u << axis_bits) - 1u;
+    uint32_t lo_i[3], hi_i[3];
+    const bool predicted = __ldcg(&a.ctr->win_lo[0]) != 0xFFFFFFFFu;  // written by the previous launch
+    if (predicted) {
 #pragma unroll
       for (int d = 0; d < 3; ++d) {
-        lo[d] = min(lo[d], c[d]);
-        hi[d] = max(hi[d], c[d]);
+        const uint32_t l = contract_bits(__ldcg(&a.ctr->win_lo[d]) >> (2 - d));
+        const uint32_t h = contract_bits(__ldcg(&a.ctr->win_hi[d]) >> (2 - d));
+        lo_i[d] = l > 0u ? l - 1u : 0u;
+        hi_i[d] = h < axis_max ? h + 1u : axis_max;
       }
-    }
-    __shared__ uint32_t s_lo[3], s_hi[3];
-    if (threadIdx.x < 3) {
-      s_lo[threadIdx.x] = 0xFFFFFFFFu;
-      s_hi[threadIdx.x] = 0u;
-    }
-    __syncthreads();
+    } else {
+      uint32_t lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0u, 0u, 0u};
+      for (uint32_t i = tid; i < a.N; i += nth) {
+        const uint32_t b = __ldcg(a.sort.keys_in + i) >> 6;
+        const uint32_t c[3] = {b & kMortonX, b & kMortonY, b & kMortonZ};
 #pragma unroll
-    for (int d = 0; d < 3; ++d) {
-      lo[d] = __reduce_min_sync(kFullMask, lo[d]);
-      hi[d] = __reduce_max_sync(kFullMask, hi[d]);
-      if ((threadIdx.x & 31) == 0) {
-        atomicMin(&s_lo[d], lo[d]);
-        atomicMax(&s_hi[d], hi[d]);
+        for (int d = 0; d < 3; ++d) {
+          lo[d] = min(lo[d], c[d]);
+          hi[d] = max(hi[d], c[d]);
+        }
+      }
+      __shared__ uint32_t s_lo[3], s_hi[3];
+      if (threadIdx.x < 3) {
+        s_lo[threadIdx.x] = 0xFFFFFFFFu;
+        s_hi[threadIdx.x] = 0u;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        lo[d] = __reduce_min_sync(kFullMask, lo[d]);
+        hi[d] = __reduce_max_sync(kFullMask, hi[d]);
+        if ((threadIdx.x & 31) == 0) {
+          atomicMin(&s_lo[d], lo[d]);
+          atomicMax(&s_hi[d], hi[d]);
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x < 3) {  // one pair of global atomics per CTA and axis
+        atomicMin(&a.ctr->win_lo[threadIdx.x], s_lo[threadIdx.x]);
+        atomicMax(&a.ctr->win_hi[threadIdx.x], s_hi[threadIdx.x]);
+      }
+      grid.sync();
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        lo_i[d] = contract_bits(__ldcg(&a.ctr->win_lo[d]) >> (2 - d));
+        hi_i[d] = contract_bits(__ldcg(&a.ctr->win_hi[d]) >> (2 - d));
       }
     }
-    __syncthreads();
-    if (threadIdx.x < 3) {  // one pair of global atomics per CTA and axis
-      atomicMin(&a.ctr->win_lo[threadIdx.x], s_lo[threadIdx.x]);
-      atomicMax(&a.ctr->win_hi[threadIdx.x], s_hi[threadIdx.x]);
-    }
-    grid.sync();
     uint32_t ext = 1;
-    uint32_t lo_d[3];
 #pragma unroll
-    for (int d = 0; d < 3; ++d) {
-      lo_d[d] = __ldcg(&a.ctr->win_lo[d]);
-      const uint32_t hi_d = __ldcg(&a.ctr->win_hi[d]);
-      ext = max(ext, contract_bits(hi_d >> (2 - d)) - contract_bits(lo_d[d] >> (2 - d)) + 1u);
-    }
+    for (int d = 0; d < 3; ++d) ext = max(ext, hi_i[d] - lo_i[d] + 1u);
     int w = 0;
     while ((1u << w) < ext) ++w;
     const int rel_bits = 3 * w + 6;
     if (rel_bits < a.key_bits) {
       win.on = true;
-      win.ox = lo_d[0];
-      win.oy = lo_d[1];
-      win.oz = lo_d[2];
+      win.ox = morton3(lo_i[0], 0u, 0u);
+      win.oy = morton3(0u, lo_i[1], 0u);
+      win.oz = morton3(0u, 0u, lo_i[2]);
       win.n_passes = plan_sort_passes(rel_bits, win.pass);
       win.final_buf = (a.sort.n_passes - 1) & 1;
+      win.rel_bits = rel_bits;
+      win.violation = predicted ? &a.ctr->win_violation : nullptr;
       if (win.n_passes >= a.sort.n_passes) win.on = false;  // no pass saved: keep the absolute keys
     }
   }
@@ -239,9 +260,13 @@ __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs 
   if (stamp) a.ctr->phase_ns[1] = (uint32_t)(global_ns() - t_begin);
   const uint32_t* sorted_key = a.sort.keys[r];
   if (blockIdx.x == 0 && threadIdx.x == 0) a.ctr->sort_passes = win.on ? win.n_passes : a.sort.n_passes;
-  if (a.window && blockIdx.x == 0 && threadIdx.x < 3) {  // everyone has read the window: reset for the next launch
-    a.ctr->win_lo[threadIdx.x] = 0xFFFFFFFFu;
+  if (a.window && blockIdx.x == 0 && threadIdx.x < 3) {  // everyone has read the window: reset the accumulators
+    a.ctr->win_lo[threadIdx.x] = 0xFFFFFFFFu;            // (the last phase below leaves the new box in them)
     a.ctr->win_hi[threadIdx.x] = 0u;
+    if (threadIdx.x == 0 && a.ctr->win_violation) {
+      a.ctr->win_violation = 0u;
+      ++a.ctr->win_fallbacks;
+    }
   }
   // ---- block ranges + list of particle blocks (uniform trip count: the warp-aggregated append needs all lanes)
   for (uint32_t i0 = 0; i0 < a.N; i0 += nth) {
@@ -270,8 +295,31 @@ __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs 
   }
   grid.sync();
   if (stamp) a.ctr->phase_ns[2] = (uint32_t)(global_ns() - t_begin);
-  // ---- chunked work records
+  // ---- chunked work records (+ the bounding box of the particle blocks, for the next launch's window)
   const uint32_t n_pb = a.ctr->n_pblocks;
+  if (a.window) {
+    uint32_t lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0u, 0u, 0u};
+    for (uint32_t t = tid; t < n_pb; t += nth) {
+      const uint32_t b = a.pb_list[t];
+      const uint32_t c[3] = {b & kMortonX, b & kMortonY, b & kMortonZ};
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        lo[d] = min(lo[d], c[d]);
+        hi[d] = max(hi[d], c[d]);
+      }
+    }
+    if (tid - (threadIdx.x & 31) < n_pb) {  // warps that saw a block
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        lo[d] = __reduce_min_sync(kFullMask, lo[d]);
+        hi[d] = __reduce_max_sync(kFullMask, hi[d]);
+        if ((threadIdx.x & 31) == 0) {
+          atomicMin(&a.ctr->win_lo[d], lo[d]);
+          atomicMax(&a.ctr->win_hi[d], hi[d]);
+        }
+      }
+    }
+  }
   for (uint32_t t = tid; t < n_pb; t += nth) {
     const uint32_t blk = a.pb_list[t];
     const uint32_t b = a.pb_start[blk], e = a.pb_end[blk];

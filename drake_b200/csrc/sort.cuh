@@ -85,6 +85,11 @@ struct SortWindow {
   int final_buf;         // buffer pair the result must end up in (the host's expectation)
   uint32_t* stamp_out;   // instrumentation: ns since t0 at the end of hist / scan / scatter of pass 0 (or null)
   unsigned long long t0;
+  // A window PREDICTED from the previous sort (its bounding box grown by one block) is not guaranteed to hold
+  // every key: pass 0 checks each relative key against rel_bits and raises *violation; after the barrier that
+  // follows its histogram the whole grid then falls back to the absolute keys (on = false on return).
+  int rel_bits;
+  uint32_t* violation;   // null for an exact window
 };
 // Morton bit positions of the three axes inside a block id (x most significant of each triple).
 constexpr uint32_t kMortonZ = 0x09249249u, kMortonY = kMortonZ << 1, kMortonX = kMortonZ << 2;
@@ -107,14 +112,15 @@ __device__ __forceinline__ uint32_t window_block_abs(uint32_t rel_block, const S
 // One full sort; every thread of the cooperative grid calls it.  `smem` = kSortSmemBytes.
 // Returns the index (0 or 1) of the buffer pair that holds the result.
 __device__ __forceinline__ int radix_sort_device(const SortArgs& a, uint32_t* smem,
-                                                 cooperative_groups::grid_group& grid,
-                                                 const SortWindow* win = nullptr) {
-  const bool windowed = win != nullptr && win->on;
-  const uint32_t wox = windowed ? win->ox : 0u, woy = windowed ? win->oy : 0u, woz = windowed ? win->oz : 0u;
-  const int n_passes = windowed ? win->n_passes : a.n_passes;
+                                                 cooperative_groups::grid_group& grid, SortWindow* win = nullptr) {
+  bool windowed = win != nullptr && win->on;
+  uint32_t wox = windowed ? win->ox : 0u, woy = windowed ? win->oy : 0u, woz = windowed ? win->oz : 0u;
+  int n_passes = windowed ? win->n_passes : a.n_passes;
   const SortPass* passes = windowed ? win->pass : a.pass;
   // pass p writes buffer pair (p + first) & 1; `first` makes the last pass land where the host expects it
-  const int first = windowed ? ((win->final_buf - (n_passes - 1)) & 1) : 0;
+  int first = windowed ? ((win->final_buf - (n_passes - 1)) & 1) : 0;
+  uint32_t* violation = windowed ? win->violation : nullptr;
+  const int rel_bits = windowed ? win->rel_bits : 32;
   uint32_t* wh = smem;                                   // [kSortWarps][radix]
   uint32_t* sbase = smem + (size_t)kSortWarps * kMaxRadix;  // [radix] digit bases
   __shared__ uint32_t s_part[kSortWarps];
@@ -137,7 +143,10 @@ __device__ __forceinline__ int radix_sort_device(const SortArgs& a, uint32_t* sm
       for (int r = 0; r < kSortItemsPerLane; ++r) {  // all loads first: one memory round trip
         const uint32_t i = wbase + r * 32 + lane;
         hk[r] = i < a.n ? __ldcg(src_k + i) : 0u;
-        if (remap) hk[r] = window_key(hk[r], wox, woy, woz);
+        if (remap) {
+          hk[r] = window_key(hk[r], wox, woy, woz);
+          if (violation && i < a.n && (hk[r] >> rel_bits)) atomicOr(violation, 1u);  // outside the predicted window
+        }
       }
 #pragma unroll
       for (int r = 0; r < kSortItemsPerLane; ++r) {
@@ -152,6 +161,19 @@ __device__ __forceinline__ int radix_sort_device(const SortArgs& a, uint32_t* sm
       __syncthreads();
     }
     grid.sync();
+    if (violation && p == 0 && __ldcg(violation)) {
+      // the predicted window missed a key (the state was replaced, or a particle outran the CFL bound): every
+      // thread sees the flag after the barrier and restarts this pass on the absolute keys
+      windowed = false;
+      win->on = false;
+      violation = nullptr;
+      wox = woy = woz = 0u;
+      n_passes = a.n_passes;
+      passes = a.pass;
+      first = 0;
+      p = -1;
+      continue;
+    }
     if (win && win->stamp_out && p == 0 && blockIdx.x == 0 && threadIdx.x == 0) {
       unsigned long long t;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));

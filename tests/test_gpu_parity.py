@@ -347,6 +347,39 @@ def test_grid512_equals_grid128_in_the_same_cells():
         assert np.max(np.abs(a[n] - b[n])) <= 1e-11 * max(1.0, np.max(np.abs(a[n]))), n
 
 
+def test_predicted_sort_window_falls_back_when_the_state_jumps():
+    """On grids whose keys need three radix passes the binning sorts keys relative to a window PREDICTED from the
+    previous binning (its bounding box grown by a block).  Replacing the particle state under it (load_state of a
+    scene shifted by many blocks) must be caught by the device-side check: the sort falls back to absolute keys
+    for that substep and the run continues exactly like a fresh state would."""
+    dtype = np.float64
+    params = {"domain_bits": 8, "dx": 1.0 / 128}
+    base = small_scene(dtype, res=30, warm=True)
+    shifted = [(p + np.array([0.9, 0.7, 0.8]), v, t) for p, v, t in base]
+
+    def fresh(sheets):
+        st = GpuMpmState(dtype, **params)
+        for pos, vel, tri in sheets:
+            st.AddQRCloth(pos, vel, tri)
+        st.Finalize()
+        return st
+
+    sv = GpuMpmSolver()
+    a, b, src = fresh(base), fresh(shifted), fresh(shifted)
+    sv.RunSubsteps(a, 4, 1e-3, -1, 0)                  # a's window now sits around the unshifted scene
+    assert a.dev_counters()["sort_passes"] == 2 and a.dev_counters()["win_fallbacks"] == 0
+    a.load_state(src.save_state())                     # ... and its particles jump to the shifted one
+    sv.RunSubsteps(a, 3, 1e-3, -1, 0)
+    sv.RunSubsteps(b, 3, 1e-3, -1, 0)
+    c = a.dev_counters()
+    assert c["win_fallbacks"] == 1 and c["sort_passes"] == 2      # one fallback, then predicted windows again
+    for n in ("positions", "velocities", "affine_matrices"):
+        x, y = a.read(n), b.read(n)
+        assert np.max(np.abs(x - y)) <= 1e-11 * max(1.0, np.max(np.abs(x))), n
+    for s in (a, b, src):
+        s.Destroy()
+
+
 def test_near_walls_and_block_corners():
     """Particles whose stencils straddle block corners and the 3-cell sticky walls."""
     dtype = np.float64
