@@ -34,6 +34,7 @@ struct DevCounters {
   uint32_t n_tiles;        // P2G tiles handed out (one per work record)
   uint32_t win_lo[3];      // bounding box of the particle blocks of the LAST binning (dilated Morton fields), from
   uint32_t win_hi[3];      // which the next binning predicts its sort window; lo = 0xFFFFFFFF: none yet
+  uint32_t win_valid;      // win_lo / win_hi hold the box of a finished binning (written only by its last phase)
   uint32_t win_violation;  // a key fell outside the predicted window (the sort fell back to absolute keys)
   uint32_t win_fallbacks;  // how often that happened (instrumentation)
   uint32_t sort_passes;    // passes the last binning sort ran (instrumentation)
@@ -188,7 +189,9 @@ __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs 
     const int axis_bits = (a.key_bits - 6) / 3;
     const uint32_t axis_max = (1u << axis_bits) - 1u;
     uint32_t lo_i[3], hi_i[3];
-    const bool predicted = __ldcg(&a.ctr->win_lo[0]) != 0xFFFFFFFFu;  // written by the previous launch
+    // win_valid is written by the last phase of a launch only: every thread of this one reads the same value
+    // (win_lo / win_hi themselves are accumulators that the measuring path below updates while CTAs still start)
+    const bool predicted = __ldcg(&a.ctr->win_valid) != 0u;
     if (predicted) {
 #pragma unroll
       for (int d = 0; d < 3; ++d) {
@@ -308,6 +311,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs 
         hi[d] = max(hi[d], c[d]);
       }
     }
+    if (tid == 0) a.ctr->win_valid = n_pb ? 1u : 0u;
     if (tid - (threadIdx.x & 31) < n_pb) {  // warps that saw a block
 #pragma unroll
       for (int d = 0; d < 3; ++d) {

@@ -327,15 +327,15 @@ class GpuMpmState:
     # --- instrumentation
     def dev_counters(self):
         """The device-side counters (csrc/kernels.cuh DevCounters) as a dict."""
-        out = np.zeros(26, np.uint32)
+        out = np.zeros(28, np.uint32)
         w = C.c_size_t()
         check(self._f("read")(self._h, b"dev_counters", _ptr(out), out.nbytes, C.byref(w)))
         names = ["n_pblocks", "n_touched", "n_touched_prev", "work_p2g", "work_g2p", "work_grid", "n_big", "n_small",
-                 "n_tiles", "win_lo_x", "win_lo_y", "win_lo_z", "win_hi_x", "win_hi_y", "win_hi_z", "win_violation", "win_fallbacks",
+                 "n_tiles", "win_lo_x", "win_lo_y", "win_lo_z", "win_hi_x", "win_hi_y", "win_hi_z", "win_valid", "win_violation", "win_fallbacks",
                  "sort_passes"]
         d = dict(zip(names, (int(v) for v in out)))
-        d["bin_phase_ns"] = [int(v) for v in out[18:22]]   # window, sort, block ranges, work records (cumulative)
-        d["sort_pass0_ns"] = [int(v) for v in out[22:25]]  # end of hist / scan / scatter of pass 0 (cumulative)
+        d["bin_phase_ns"] = [int(v) for v in out[19:23]]   # window, sort, block ranges, work records (cumulative)
+        d["sort_pass0_ns"] = [int(v) for v in out[23:26]]  # end of hist / scan / scatter of pass 0 (cumulative)
         return d
 
     def kernel_launches(self):
