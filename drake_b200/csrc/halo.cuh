@@ -151,6 +151,15 @@ halo_pack_kernel(uint32_t n, const uint32_t* __restrict__ list, const uint32_t* 
   }
 }
 
+// index[list[i]] = i (set) or kHaloNoIndex (clear) for the first min(*n, cap) entries of a planned list: the
+// grid block -> list position map the fused exchange (grid_kernel HALO = 1 / 2) looks its blocks up in.
+__global__ void halo_index_kernel(const uint32_t* __restrict__ n_ptr, uint32_t cap, const uint32_t* __restrict__ list,
+                                  uint32_t* __restrict__ index, bool set) {
+  const uint32_t n = min(*n_ptr, cap);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    index[list[i]] = set ? i : kHaloNoIndex;
+}
+
 // mark[list[i]] = value for the first n entries (the blocks of the current exchange).
 __global__ void halo_mark_kernel(uint32_t n, const uint32_t* __restrict__ list, uint8_t value,
                                  uint8_t* __restrict__ mark) {
@@ -176,53 +185,6 @@ __global__ void halo_mark_kernel(uint32_t n, const uint32_t* __restrict__ list, 
 // The two window halves alternate: a rank can be at most one exchange ahead of a neighbour (its next recv
 // needs the neighbour's next send, which follows the neighbour's current recv in stream order).
 // ------------------------------------------------------------------------------------------------
-constexpr int kHaloMaxPeers = 8;
-constexpr int kHaloPeerThreads = 128;                              // one CTA per listed block, two values per thread
-constexpr unsigned long long kHaloPeerTimeoutNs = 5000000000ull;  // a delivery takes microseconds
-constexpr uint32_t kHaloPeerTimeoutCode = 1u << 16;               // added to the error word the next exchange checks
-__device__ __forceinline__ unsigned long long global_timer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-struct HaloWindows {
-  unsigned char* base[kHaloMaxPeers];
-};
-// Window layout: flag[64] | present[2][world][cap] | (256-byte aligned) data[2][world][cap][256]
-__host__ __device__ inline size_t halo_window_data_offset(uint32_t world, uint32_t cap) {
-  return (256 + sizeof(uint32_t) * 2 * (size_t)world * cap + 255) & ~(size_t)255;
-}
-template <typename T>
-__host__ __device__ inline size_t halo_window_bytes(uint32_t world, uint32_t cap) {
-  return halo_window_data_offset(world, cap) + sizeof(T) * 256 * 2 * (size_t)world * cap;
-}
-__device__ __forceinline__ uint32_t* halo_window_present(unsigned char* base, uint32_t parity, uint32_t world,
-                                                         uint32_t src, uint32_t cap, uint32_t i) {
-  return reinterpret_cast<uint32_t*>(base + 256) + ((size_t)parity * world + src) * cap + i;
-}
-template <typename T>
-__device__ __forceinline__ T* halo_window_data(unsigned char* base, uint32_t parity, uint32_t world, uint32_t src,
-                                               uint32_t cap, uint32_t i) {
-  return reinterpret_cast<T*>(base + halo_window_data_offset(world, cap)) + (((size_t)parity * world + src) * cap + i) * 256;
-}
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-template <typename T> struct Pair;
-template <> struct Pair<float> { using type = float2; };
-template <> struct Pair<double> { using type = double2; };
-// the 256 values of a block, [mass 64 | momentum 3 x 64], as 128 pairs: pair t of block g
-template <typename T>
-__device__ __forceinline__ typename Pair<T>::type* halo_block_pair(T* g_mass, T* g_vel, uint32_t g, uint32_t t) {
-  T* p = t < 32u ? g_mass + (size_t)g * 64 + 2u * t : g_vel + (size_t)g * 192 + 2u * (t - 32u);
-  return reinterpret_cast<typename Pair<T>::type*>(p);
-}
-
 // One CTA per listed block.  A block this rank did not touch sends nothing: its `present` word keeps an older
 // exchange number and the receivers read it as zeros.
 template <typename T>
@@ -242,20 +204,8 @@ halo_peer_send_kernel(uint32_t n, const uint32_t* __restrict__ list, const uint8
         reinterpret_cast<P2*>(halo_window_data<T>(win.base[q], xchg & 1u, world, rank, cap, i))[threadIdx.x] = v;
         if (threadIdx.x == 0) *halo_window_present(win.base[q], xchg & 1u, world, rank, cap, i) = xchg;
       }
-    __threadfence_system();  // this CTA's stores before its arrival below
   }
-  // all stores of all CTAs before the delivery flags (threadFenceReduction pattern at system scope)
-  __syncthreads();
-  __shared__ bool s_last;
-  if (threadIdx.x == 0) s_last = atomicAdd(done, 1u) == gridDim.x - 1;
-  __syncthreads();
-  if (!s_last) return;
-  if (threadIdx.x == 0) *done = 0;
-  const uint32_t peers = *union_mask & ~(1u << rank);
-  if (threadIdx.x < world && ((peers >> threadIdx.x) & 1u)) {
-    __threadfence_system();
-    st_release_sys(reinterpret_cast<uint32_t*>(win.base[threadIdx.x]) + rank, xchg);
-  }
+  halo_signal_peers(win, rank, world, xchg, union_mask, done);
 }
 
 template <typename T>
@@ -270,17 +220,7 @@ halo_peer_recv_kernel(uint32_t n, const uint32_t* __restrict__ list, const uint8
   if (touched_epoch[g] != epoch) return;  // not this rank's block now (the list is the dilated set)
   const uint32_t who = sharers[i];
   // wait for the deliveries of this block's other sharers
-  if (threadIdx.x < world && threadIdx.x != rank && ((who >> threadIdx.x) & 1u)) {
-    const uint32_t* flag = reinterpret_cast<const uint32_t*>(window) + threadIdx.x;
-    const unsigned long long t0 = global_timer_ns();
-    while ((int32_t)(ld_acquire_sys(flag) - xchg) < 0) {
-      __nanosleep(32);
-      if (global_timer_ns() - t0 > kHaloPeerTimeoutNs) {  // a peer died or the call order differs between ranks
-        atomicAdd(err, kHaloPeerTimeoutCode);
-        break;
-      }
-    }
-  }
+  if (threadIdx.x < 32) halo_wait_sharers(window, who, rank, world, xchg, err);
   __syncthreads();
   P2* cell = halo_block_pair<T>(g_mass, g_vel, g, threadIdx.x);
   P2 acc;

@@ -15,6 +15,7 @@
 #include "common.cuh"
 #include "math.cuh"
 #include "sort.cuh"
+#include "halo_window.cuh"
 
 namespace gmpm {
 
@@ -850,13 +851,17 @@ __device__ __forceinline__ void apply_boundary_and_colliders(const Consts<T>& k,
   }
 }
 
-template <typename T, bool ASSEMBLE, bool UPDATE>
+// HALO (multi-GPU, peer windows, halo.cuh): 1 = the assembly also SENDS -- a block of the shared-block list is stored
+// into its other sharers' windows as soon as it is summed, and the kernel ends by raising the delivery flags;
+// 2 = the update also RECEIVES -- a listed block waits for its sharers' flags and adds their values in rank order
+// before it is updated.  Saves the two exchange kernels and their launches between assembly and update.
+template <typename T, bool ASSEMBLE, bool UPDATE, int HALO = 0>
 __global__ void __launch_bounds__(kThreads)
 grid_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __restrict__ ctr,
             const T* __restrict__ tiles, const uint2* __restrict__ pb_tile, const uint32_t* __restrict__ pb_epoch,
             uint32_t epoch, T* __restrict__ g_mass, T* __restrict__ g_vel, T* __restrict__ g_vstar, int bc,
             Consts<T> k, uint32_t* __restrict__ nbr_list = nullptr, const uint8_t* __restrict__ mark = nullptr,
-            int want = -1) {
+            int want = -1, HaloFuse<T> hf = HaloFuse<T>{}) {
   // mark / want (multi-GPU): only blocks with mark[g] == want (0: not exchanged, 1: exchanged with other ranks)
   const uint32_t n_touched = ctr->n_touched;
   const uint32_t l = threadIdx.x & 63u;
@@ -917,12 +922,55 @@ grid_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __rest
         g_vel[vbase] = p[0];
         g_vel[vbase + 64] = p[1];
         g_vel[vbase + 128] = p[2];
+        if (HALO == 1) {
+          const uint32_t i = hf.index[g];
+          if (i != kHaloNoIndex) {
+            const uint32_t who = hf.sharers[i] & ~(1u << hf.rank);
+            for (uint32_t q = 0; q < hf.world; ++q)
+              if ((who >> q) & 1u) {
+                T* d = halo_window_data<T>(hf.win.base[q], hf.xchg & 1u, hf.world, hf.rank, hf.cap, i);
+                d[l] = m;
+                d[64 + l] = p[0];
+                d[128 + l] = p[1];
+                d[192 + l] = p[2];
+                if (l == 0) *halo_window_present(hf.win.base[q], hf.xchg & 1u, hf.world, hf.rank, hf.cap, i) = hf.xchg;
+              }
+          }
+        }
       }
     } else {
       m = g_mass[cell];
       p[0] = g_vel[vbase];
       p[1] = g_vel[vbase + 64];
       p[2] = g_vel[vbase + 128];
+      if (HALO == 2) {
+        const uint32_t i = hf.index[g];
+        if (i != kHaloNoIndex) {
+          const uint32_t who = hf.sharers[i];
+          unsigned char* window = hf.win.base[hf.rank];
+          halo_wait_sharers(window, who, hf.rank, hf.world, hf.xchg, hf.err);  // both warps of the block's group
+          T am = T(0), ap[3] = {T(0), T(0), T(0)};
+          bool first = true;
+          for (uint32_t q = 0; q < hf.world; ++q) {  // ascending rank order: the same bits on every sharer
+            if (!((who >> q) & 1u)) continue;
+            T vm = T(0), vp[3] = {T(0), T(0), T(0)};
+            if (q == hf.rank) {
+              vm = m; vp[0] = p[0]; vp[1] = p[1]; vp[2] = p[2];
+            } else if (__ldcg(halo_window_present(window, hf.xchg & 1u, hf.world, q, hf.cap, i)) == hf.xchg) {
+              const T* d = halo_window_data<T>(window, hf.xchg & 1u, hf.world, q, hf.cap, i);
+              vm = __ldcg(d + l); vp[0] = __ldcg(d + 64 + l); vp[1] = __ldcg(d + 128 + l); vp[2] = __ldcg(d + 192 + l);
+            }
+            if (first) {
+              am = vm; ap[0] = vp[0]; ap[1] = vp[1]; ap[2] = vp[2];
+              first = false;
+            } else {
+              am += vm; ap[0] += vp[0]; ap[1] += vp[1]; ap[2] += vp[2];
+            }
+          }
+          m = am; p[0] = ap[0]; p[1] = ap[1]; p[2] = ap[2];
+          g_mass[cell] = m;  // the exchanged sums are what the grid holds from here on (getters, contact)
+        }
+      }
     }
     if (UPDATE) {
       if (m > T(0)) {
@@ -938,6 +986,7 @@ grid_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __rest
       g_vel[vbase + 128] = p[2];
     }
   }
+  if (HALO == 1) halo_signal_peers(hf.win, hf.rank, hf.world, hf.xchg, hf.peers, hf.done);
 }
 
 // Zero the blocks that were touched by the previous P2G but not by this one (the reference zeroes

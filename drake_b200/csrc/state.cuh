@@ -179,6 +179,9 @@ struct State {
   HaloWindows halo_windows{};                    // every rank's window as mapped into this process
   bool halo_window_ipc[kHaloMaxPeers]{};         // opened with cudaIpcOpenMemHandle (to be closed)
   uint8_t* halo_sharers[2]{};                    // sharer set of each listed block
+  uint32_t* halo_index[2]{};                     // grid block -> list position, per plan slot (fused exchange)
+  bool halo_fused = std::getenv("GMPM_HALO_UNFUSED") == nullptr;  // send in the grid assembly, receive in the update
+  bool halo_recv_pending = false;                // halo_peer_recv was called: the next UpdateGrid receives
   bool halo_sent = false;
   bool fem_reverse = std::getenv("GMPM_FEM_FORWARD") == nullptr;  // fem_kernel: walk the face records from the end
 
@@ -595,6 +598,7 @@ struct State {
   }
 
   void assemble_momentum() {  // observable P2G result (grid_masses / grid_momentum before UpdateGrid)
+    if (halo_recv_pending) halo_recv_now();  // somebody other than UpdateGrid wants the exchanged sums
     if (stage != GridStage::kTiles) return;
     if (halo_nbr) halo_nbr_epoch = halo_nbr_zeroed_epoch == p2g_epoch ? p2g_epoch : 0;
     launch("grid_assemble");
@@ -613,6 +617,12 @@ struct State {
       launch("grid_assemble_update");
       grid_kernel<T, true, true><<<persistent_ctas(4), kThreads, 0, stream>>>(
           touched_list[tl_cur], ctr, tiles, pb_tile, pb_epoch, bin_epoch, g_mass, g_vel, g_vstar, bc, k);
+    } else if (halo_recv_pending) {
+      halo_recv_pending = false;
+      launch("grid_recv_update");
+      grid_kernel<T, false, true, 2><<<persistent_ctas(4), kThreads, 0, stream>>>(
+          touched_list[tl_cur], ctr, tiles, pb_tile, pb_epoch, bin_epoch, g_mass, g_vel, g_vstar, bc, k, nullptr, nullptr,
+          -1, halo_fuse_args());
     } else {
       launch("grid_update");
       grid_kernel<T, false, true><<<persistent_ctas(4), kThreads, 0, stream>>>(
@@ -660,6 +670,7 @@ struct State {
     assemble_momentum();
     if (stage != GridStage::kMomentum) throw std::invalid_argument("update_grid_part must follow ParticleToGrid");
     if (!halo_mark) halo_init();
+    if (halo_recv_pending) halo_recv_now();
     halo_set_marks();
     launch(part ? "grid_update_shared" : "grid_update_interior");
     grid_kernel<T, false, true><<<persistent_ctas(4), kThreads, 0, stream>>>(
@@ -786,13 +797,19 @@ struct State {
   }
   void halo_compact_into(int slot, cudaStream_t st) {
     const uint32_t ctas = (k.n_blocks + kHaloBlocksPerCta - 1) / kHaloBlocksPerCta;
+    if (halo_peer)  // forget the list this slot held two exchanges ago (its count is still in the device word)
+      halo_index_kernel<<<8, kThreads, 0, st>>>(halo_dev_words + slot, (uint32_t)halo_cap, halo_list[slot],
+                                                halo_index[slot], false);
     halo_count_kernel<<<ctas, kHaloThreads, 0, st>>>(k.n_blocks, halo_flags_d, halo_cta_counts, halo_peer,
                                                     halo_dev_words + 4 + slot);
     halo_compact_kernel<<<ctas, kHaloThreads, 0, st>>>(k.n_blocks, halo_flags_d, halo_cta_counts, halo_list[slot],
                                                       (uint32_t)halo_cap, halo_dev_words + slot, halo_peer,
                                                       halo_sharers[slot], halo_dev_words + 4 + slot, halo_rank);
+    if (halo_peer)
+      halo_index_kernel<<<8, kThreads, 0, st>>>(halo_dev_words + slot, (uint32_t)halo_cap, halo_list[slot],
+                                                halo_index[slot], true);
     GMPM_CUDA(cudaGetLastError());
-    launches += 2;
+    launches += halo_peer ? 4 : 2;
   }
   // flags now hold the sum over the ranks: build the shared-block list of the next exchange on the side
   // stream; its count lands in pinned memory and is picked up by the next halo_pack.
@@ -821,7 +838,7 @@ struct State {
   bool halo_plan_pending = false;
   // Start of an exchange: picks up the list planned for it (count through pinned memory), checks containment,
   // assembles the block sums and marks the listed blocks.  Returns the number of shared blocks.
-  uint32_t halo_begin_exchange(const char* what) {
+  uint32_t halo_begin_exchange(const char* what, bool assemble = true) {
     require_finalized();
     require_after_p2g(what);
     if (!halo_plan_pending) throw std::invalid_argument(std::string(what) + " without a plan (halo_flags / halo_plan first)");
@@ -844,7 +861,7 @@ struct State {
     halo_plan_pending = false;
     halo_n = n;
     GMPM_CUDA(cudaStreamWaitEvent(stream, ev_halo_plan, 0));
-    assemble_momentum();
+    if (assemble) assemble_momentum();
     return n;
   }
   // mark[b] = 1 for the blocks of the exchange in flight: only the part-wise UpdateGrid / G2P read them, so they
@@ -907,6 +924,11 @@ struct State {
     GMPM_CUDA(cudaMalloc((void**)&halo_window, halo_window_bytes));
     GMPM_CUDA(cudaMemsetAsync(halo_window, 0, halo_window_bytes, stream));
     GMPM_CUDA(cudaStreamSynchronize(stream));
+    for (int i = 0; i < 2; ++i) {
+      halo_index[i] = dalloc<uint32_t>(k.n_blocks, false);
+      GMPM_CUDA(cudaMemsetAsync(halo_index[i], 0xFF, sizeof(uint32_t) * k.n_blocks, stream));  // kHaloNoIndex
+    }
+    GMPM_CUDA(cudaStreamSynchronize(stream));
     halo_rank = rank;
     halo_world = world;
     halo_windows.base[rank] = halo_window;
@@ -949,11 +971,23 @@ struct State {
     for (uint32_t q = 0; q < halo_world; ++q)
       if (!halo_windows.base[q]) throw std::invalid_argument("halo_peer_send: not every peer window is attached");
     if (halo_sent) throw std::invalid_argument("halo_peer_send: the previous exchange was not received");
-    const uint32_t n = halo_begin_exchange("halo_peer_send");
+    // fused: the grid assembly stores each listed block into its sharers' windows as soon as it is summed
+    const bool fuse = halo_fused && stage == GridStage::kTiles;
+    const uint32_t n = halo_begin_exchange("halo_peer_send", !fuse);
     if (n > halo_win_cap)
       throw std::runtime_error("halo_peer_send: more shared blocks than the peer windows were sized for (halo_peer_init cap_blocks)");
     ++halo_xchg;
-    if (n) {
+    halo_send_fused = fuse && n;
+    if (fuse && !n) assemble_momentum();
+    if (halo_send_fused) {
+      if (halo_nbr) halo_nbr_epoch = halo_nbr_zeroed_epoch == p2g_epoch ? p2g_epoch : 0;
+      launch("grid_assemble_send");
+      grid_kernel<T, true, false, 1><<<persistent_ctas(4), kThreads, 0, stream>>>(
+          touched_list[tl_cur], ctr, tiles, pb_tile, pb_epoch, bin_epoch, g_mass, g_vel, g_vstar, -1, k,
+          halo_nbr_epoch == p2g_epoch ? halo_nbr : nullptr, nullptr, -1, halo_fuse_args());
+      GMPM_CUDA(cudaGetLastError());
+      stage = GridStage::kMomentum;
+    } else if (n) {
       launch("halo_peer_send");
       halo_peer_send_kernel<T><<<n, kHaloPeerThreads, 0, stream>>>(
           n, halo_list[halo_cur], halo_sharers[halo_cur], touched_epoch, p2g_epoch, g_mass, g_vel, halo_windows, halo_rank,
@@ -967,6 +1001,31 @@ struct State {
   void halo_peer_recv() {
     require_peer("halo_peer_recv");
     if (!halo_sent) throw std::invalid_argument("halo_peer_recv without halo_peer_send");
+    halo_sent = false;
+    if (halo_n && halo_fused) {  // the next UpdateGrid waits for the sharers block by block and adds their values
+      halo_recv_pending = true;
+      return;
+    }
+    halo_recv_now();
+  }
+  bool halo_send_fused = false;
+  HaloFuse<T> halo_fuse_args() const {
+    HaloFuse<T> hf{};
+    hf.index = halo_index[halo_cur];
+    hf.sharers = halo_sharers[halo_cur];
+    hf.win = halo_windows;
+    hf.rank = halo_rank;
+    hf.world = halo_world;
+    hf.cap = halo_win_cap;
+    hf.xchg = halo_xchg;
+    hf.peers = halo_dev_words + 4 + halo_cur;
+    hf.done = halo_dev_words + 3;
+    hf.err = halo_dev_words + 2;
+    return hf;
+  }
+  // the receive as a kernel of its own (unfused mode, or a consumer other than UpdateGrid needs the sums)
+  void halo_recv_now() {
+    halo_recv_pending = false;
     if (halo_n) {
       launch("halo_peer_recv");
       halo_peer_recv_kernel<T><<<halo_n, kHaloPeerThreads, 0, stream>>>(
@@ -974,7 +1033,6 @@ struct State {
           halo_world, halo_win_cap, halo_xchg, halo_dev_words + 2);
       GMPM_CUDA(cudaGetLastError());
     }
-    halo_sent = false;
   }
 
   cudaEvent_t timers[16]{};
