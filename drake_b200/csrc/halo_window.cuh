@@ -59,6 +59,10 @@ constexpr uint32_t kHaloNoIndex = 0xFFFFFFFFu;
 template <typename T>
 struct HaloFuse {
   const uint32_t* index;     // grid block -> position in the shared-block list of this exchange, or kHaloNoIndex
+  const uint32_t* list;      // the shared-block list (ascending block ids) and its length
+  uint32_t n_list;
+  const uint32_t* touched_epoch;  // touched_epoch[g] == p2g_epoch: this rank's P2G reached block g
+  uint32_t p2g_epoch;
   const uint8_t* sharers;    // sharer set per list position
   HaloWindows win;           // every rank's window
   uint32_t rank, world, cap, xchg;
@@ -100,6 +104,27 @@ __device__ __forceinline__ void halo_signal_peers(const HaloWindows& win, uint32
   if (threadIdx.x < world && ((peers >> threadIdx.x) & 1u)) {
     __threadfence_system();
     st_release_sys(reinterpret_cast<uint32_t*>(win.base[threadIdx.x]) + rank, xchg);
+  }
+}
+
+// The same per WARP and without a CTA barrier, for a sender that has other work to do afterwards (the grid
+// assembly): a warp that stored to a peer fences, every warp of the grid arrives once, the last one raises the flags.
+// Warps that sent nothing pass straight through; the fence of the others is hidden by the rest of the SM.
+__device__ __forceinline__ void halo_signal_peers_warp(const HaloWindows& win, uint32_t rank, uint32_t world,
+                                                       uint32_t xchg, const uint32_t* peers_mask, uint32_t* done,
+                                                       bool sent) {
+  if (__any_sync(0xFFFFFFFFu, sent)) __threadfence_system();
+  __syncwarp();
+  const uint32_t lane = threadIdx.x & 31u;
+  uint32_t last = 0;
+  if (lane == 0) last = atomicAdd(done, 1u) == gridDim.x * (blockDim.x >> 5) - 1u ? 1u : 0u;
+  last = __shfl_sync(0xFFFFFFFFu, last, 0);
+  if (!last) return;
+  if (lane == 0) *done = 0;
+  const uint32_t peers = *peers_mask & ~(1u << rank);
+  if (lane < world && ((peers >> lane) & 1u)) {
+    __threadfence_system();
+    st_release_sys(reinterpret_cast<uint32_t*>(win.base[lane]) + rank, xchg);
   }
 }
 

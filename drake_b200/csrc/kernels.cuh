@@ -851,8 +851,8 @@ __device__ __forceinline__ void apply_boundary_and_colliders(const Consts<T>& k,
   }
 }
 
-// HALO (multi-GPU, peer windows, halo.cuh): 1 = the assembly also SENDS -- a block of the shared-block list is stored
-// into its other sharers' windows as soon as it is summed, and the kernel ends by raising the delivery flags;
+// HALO (multi-GPU, peer windows, halo.cuh): 1 = the assembly also SENDS -- it starts with the blocks of the shared-block
+// list, stores them into their other sharers' windows and raises the delivery flags, then assembles the grid;
 // 2 = the update also RECEIVES -- a listed block waits for its sharers' flags and adds their values in rank order
 // before it is updated.  Saves the two exchange kernels and their launches between assembly and update.
 template <typename T, bool ASSEMBLE, bool UPDATE, int HALO = 0>
@@ -866,6 +866,63 @@ grid_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __rest
   const uint32_t n_touched = ctr->n_touched;
   const uint32_t l = threadIdx.x & 63u;
   const uint32_t lx = (l >> 4) & 3u, ly = (l >> 2) & 3u, lz = l & 3u;
+  // mass and momentum of this thread's cell of grid block (gx, gy, gz): sum of the P2G tiles that overlap it
+  auto sum_tiles = [&](uint32_t gx, uint32_t gy, uint32_t gz, T& m, T* p) {
+    m = T(0); p[0] = T(0); p[1] = T(0); p[2] = T(0);
+    // resolve the <= 8 source particle blocks first (independent loads in flight together) ...
+    uint2 tr[8];
+    uint32_t node[8];
+#pragma unroll
+    for (int d = 0; d < 8; ++d) {
+      const uint32_t ddx = (d >> 2) & 1u, ddy = (d >> 1) & 1u, ddz = d & 1u;
+      // tile of particle block g - delta covers local cells [4 delta, 4 delta + 6): needs l < 2 where delta = 1
+      const bool skip = (ddx && (lx >= 2u || gx == 0u)) || (ddy && (ly >= 2u || gy == 0u)) || (ddz && (lz >= 2u || gz == 0u));
+      tr[d] = make_uint2(0u, 0u);
+      node[d] = (lx + 4u * ddx) * 36u + (ly + 4u * ddy) * 6u + (lz + 4u * ddz);
+      if (!skip) {
+        const uint32_t src = morton3(gx - ddx, gy - ddy, gz - ddz);
+        if (pb_epoch[src] == epoch) tr[d] = pb_tile[src];
+      }
+    }
+    // ... then sum their chunks' tiles in a fixed order (delta, then chunk): reproducible
+#pragma unroll
+    for (int d = 0; d < 8; ++d) {
+      const T* tl = tiles + (size_t)tr[d].x * (4 * kTileNodes) + node[d];
+      for (uint32_t c = 0; c < tr[d].y; ++c, tl += 4 * kTileNodes) {
+        m += tl[0];
+        p[0] += tl[kTileNodes];
+        p[1] += tl[2 * kTileNodes];
+        p[2] += tl[3 * kTileNodes];
+      }
+    }
+  };
+  if (HALO == 1) {
+    // The blocks of the shared-block list FIRST: summed, stored into their other sharers' windows, and the
+    // delivery flags raised -- the system-scope fence and the NVLink round trip of that (~15 us) then run under
+    // the assembly of the whole grid below, and the peers' data is there long before the update asks for it.
+    // (The main loop sums these few blocks a second time, for the grid arrays and the neighbour masks.)
+    bool sent = false;
+    for (uint32_t i = blockIdx.x * 4u + (threadIdx.x >> 6); i < hf.n_list; i += gridDim.x * 4u) {
+      const uint32_t g = hf.list[i];
+      if (hf.touched_epoch[g] != hf.p2g_epoch) continue;  // not this rank's block now: nothing to send
+      sent = true;
+      uint32_t gx, gy, gz;
+      block_coords(g, gx, gy, gz);
+      T m, p[3];
+      sum_tiles(gx, gy, gz, m, p);
+      const uint32_t who = hf.sharers[i] & ~(1u << hf.rank);
+      for (uint32_t q = 0; q < hf.world; ++q)
+        if ((who >> q) & 1u) {
+          T* d = halo_window_data<T>(hf.win.base[q], hf.xchg & 1u, hf.world, hf.rank, hf.cap, i);
+          d[l] = m;
+          d[64 + l] = p[0];
+          d[128 + l] = p[1];
+          d[192 + l] = p[2];
+          if (l == 0) *halo_window_present(hf.win.base[q], hf.xchg & 1u, hf.world, hf.rank, hf.cap, i) = hf.xchg;
+        }
+    }
+    halo_signal_peers_warp(hf.win, hf.rank, hf.world, hf.xchg, hf.peers, hf.done, sent);
+  }
   for (uint32_t it = blockIdx.x * 4u + (threadIdx.x >> 6); it < n_touched; it += gridDim.x * 4u) {
     const uint32_t g = touched_list[it];
     if (want >= 0 && (int)mark[g] != want) continue;
@@ -875,33 +932,7 @@ grid_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __rest
     const size_t cell = (size_t)g * 64 + l;
     const size_t vbase = (size_t)g * 192 + l;
     if (ASSEMBLE) {
-      m = T(0); p[0] = T(0); p[1] = T(0); p[2] = T(0);
-      // resolve the <= 8 source particle blocks first (independent loads in flight together) ...
-      uint2 tr[8];
-      uint32_t node[8];
-#pragma unroll
-      for (int d = 0; d < 8; ++d) {
-        const uint32_t ddx = (d >> 2) & 1u, ddy = (d >> 1) & 1u, ddz = d & 1u;
-        // tile of particle block g - delta covers local cells [4 delta, 4 delta + 6): needs l < 2 where delta = 1
-        const bool skip = (ddx && (lx >= 2u || gx == 0u)) || (ddy && (ly >= 2u || gy == 0u)) || (ddz && (lz >= 2u || gz == 0u));
-        tr[d] = make_uint2(0u, 0u);
-        node[d] = (lx + 4u * ddx) * 36u + (ly + 4u * ddy) * 6u + (lz + 4u * ddz);
-        if (!skip) {
-          const uint32_t src = morton3(gx - ddx, gy - ddy, gz - ddz);
-          if (pb_epoch[src] == epoch) tr[d] = pb_tile[src];
-        }
-      }
-      // ... then sum their chunks' tiles in a fixed order (delta, then chunk): reproducible
-#pragma unroll
-      for (int d = 0; d < 8; ++d) {
-        const T* tl = tiles + (size_t)tr[d].x * (4 * kTileNodes) + node[d];
-        for (uint32_t c = 0; c < tr[d].y; ++c, tl += 4 * kTileNodes) {
-          m += tl[0];
-          p[0] += tl[kTileNodes];
-          p[1] += tl[2 * kTileNodes];
-          p[2] += tl[3 * kTileNodes];
-        }
-      }
+      sum_tiles(gx, gy, gz, m, p);
       if (nbr_list) {
         // multi-GPU planning (halo.cuh): towards which of the 26 neighbour blocks does this block hold mass
         // in its outermost cell layer?  Only those can be reached by its particles in the next substep.
@@ -922,21 +953,6 @@ grid_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __rest
         g_vel[vbase] = p[0];
         g_vel[vbase + 64] = p[1];
         g_vel[vbase + 128] = p[2];
-        if (HALO == 1) {
-          const uint32_t i = hf.index[g];
-          if (i != kHaloNoIndex) {
-            const uint32_t who = hf.sharers[i] & ~(1u << hf.rank);
-            for (uint32_t q = 0; q < hf.world; ++q)
-              if ((who >> q) & 1u) {
-                T* d = halo_window_data<T>(hf.win.base[q], hf.xchg & 1u, hf.world, hf.rank, hf.cap, i);
-                d[l] = m;
-                d[64 + l] = p[0];
-                d[128 + l] = p[1];
-                d[192 + l] = p[2];
-                if (l == 0) *halo_window_present(hf.win.base[q], hf.xchg & 1u, hf.world, hf.rank, hf.cap, i) = hf.xchg;
-              }
-          }
-        }
       }
     } else {
       m = g_mass[cell];
@@ -986,7 +1002,6 @@ grid_kernel(const uint32_t* __restrict__ touched_list, const DevCounters* __rest
       g_vel[vbase + 128] = p[2];
     }
   }
-  if (HALO == 1) halo_signal_peers(hf.win, hf.rank, hf.world, hf.xchg, hf.peers, hf.done);
 }
 
 // Zero the blocks that were touched by the previous P2G but not by this one (the reference zeroes

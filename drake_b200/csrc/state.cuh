@@ -1012,6 +1012,10 @@ struct State {
   HaloFuse<T> halo_fuse_args() const {
     HaloFuse<T> hf{};
     hf.index = halo_index[halo_cur];
+    hf.list = halo_list[halo_cur];
+    hf.n_list = halo_n;
+    hf.touched_epoch = touched_epoch;
+    hf.p2g_epoch = p2g_epoch;
     hf.sharers = halo_sharers[halo_cur];
     hf.win = halo_windows;
     hf.rank = halo_rank;
