@@ -52,9 +52,27 @@ def reachable_blocks(mass):
     return out[bx, by, bz]
 
 
+_WINDOWS = {}   # "device pointer" -> window of an oracle backend in peer mode (same-process attach)
+
+
+class _Window:
+    """CPU stand-in for a peer-memory receive window (csrc/halo_window.cuh): flag[world], present and data
+    [2][world][cap]."""
+
+    def __init__(self, world, cap, dtype):
+        self.flag = np.zeros(world, np.uint32)
+        self.present = np.zeros((2, world, cap), np.uint32)
+        self.data = np.zeros((2, world, cap, 4, 64), dtype)
+
+
 class OracleHaloBackend:
+    """Also mirrors the peer-mode calls of GpuMpmState (halo_peer_init / window / attach / send / recv), with
+    numpy windows shared by reference, so that slab.InProcessExchange(peer=True) runs on the CPU."""
+
     def __init__(self, orc):
         self.orc = orc
+        self.state = self           # slab.py reaches the peer set-up calls through backend.state
+        self.peer = False
         self.planned_own = None     # own dilated flags of the previous plan (containment check)
         self.next_shared = None
         self.shared = None
@@ -74,11 +92,82 @@ class OracleHaloBackend:
             self.planned_own = touched | reachable_blocks(self.own_mass)
         else:                   # start-up (no assembled masses yet): full block dilation
             self.planned_own = dilate_blocks(touched)
-        self._flags = torch.from_numpy(self.planned_own.astype(np.uint8))
+        contribution = (1 << self.rank) if self.peer else 1
+        self._flags = torch.from_numpy(self.planned_own.astype(np.uint8) * np.uint8(contribution))
         return self._flags
 
     def halo_plan_async(self):
-        self.next_shared = np.nonzero(self._flags.numpy() > 1)[0]     # ascending block ids
+        f = self._flags.numpy()
+        if self.peer:               # flags = sharer set: shared = more than one bit
+            self.next_shared = np.nonzero((f & (f - 1)) != 0)[0]
+            self.next_sharers = f[self.next_shared].copy()
+        else:
+            self.next_shared = np.nonzero(f > 1)[0]                   # ascending block ids
+
+    # ---- peer mode (csrc/halo.cuh, second half) ------------------------------------------------------
+    def halo_peer_init(self, rank, world, cap_blocks=8192):
+        assert not self.peer and 1 <= world <= 8 and rank < world
+        self.peer, self.rank, self.world, self.cap, self.xchg = True, rank, world, cap_blocks, 0
+        self.windows = [None] * world
+        self.windows[rank] = _Window(world, cap_blocks, self.orc.dtype)
+        _WINDOWS[id(self.windows[rank])] = self.windows[rank]
+
+    def halo_peer_window(self):
+        return b"\0" * 64, id(self.windows[self.rank])
+
+    def halo_peer_attach(self, peer, ipc_handle=None, pointer=None):
+        assert self.peer and peer != self.rank and self.windows[peer] is None and pointer is not None
+        self.windows[peer] = _WINDOWS[pointer]
+
+    def halo_peer_send(self):
+        assert all(w is not None for w in self.windows), "not every peer window is attached"
+        self.shared, self.sharers = self.next_shared, self.next_sharers
+        assert self.shared.size <= self.cap
+        self.own = self._touched()
+        self.own_mass = self.orc.view("grid_masses").copy()
+        self.have_mass = True
+        self.xchg += 1
+        par = self.xchg & 1
+        mass = self.orc.view("grid_masses").reshape(-1, 64)
+        mom = self.orc.view("grid_momentum").reshape(-1, 64, 3)
+        peers = 0
+        for i, g in enumerate(self.shared):
+            who = int(self.sharers[i])
+            if who >> self.rank & 1:
+                peers |= who
+            if not self.own[g]:
+                continue                                  # an untouched block sends nothing
+            for q in range(self.world):
+                if q != self.rank and who >> q & 1:
+                    w = self.windows[q]
+                    w.data[par, self.rank, i, 0] = mass[g]
+                    w.data[par, self.rank, i, 1:] = mom[g].T
+                    w.present[par, self.rank, i] = self.xchg
+        for q in range(self.world):
+            if q != self.rank and peers >> q & 1:
+                self.windows[q].flag[self.rank] = self.xchg
+        return int(self.shared.size)
+
+    def halo_peer_recv(self):
+        par, w = self.xchg & 1, self.windows[self.rank]
+        mass = self.orc.view("grid_masses").reshape(-1, 64)
+        mom = self.orc.view("grid_momentum").reshape(-1, 64, 3)
+        for i, g in enumerate(self.shared):
+            if not self.own[g]:
+                continue
+            who = int(self.sharers[i])
+            acc = None
+            for q in range(self.world):                   # ascending rank order: the same bits on every sharer
+                if not who >> q & 1:
+                    continue
+                if q == self.rank:
+                    v = np.concatenate([mass[g][None, :], mom[g].T])
+                else:
+                    assert w.flag[q] >= self.xchg, "receive before the sharer delivered"
+                    v = w.data[par, q, i] if w.present[par, q, i] == self.xchg else np.zeros((4, 64), self.orc.dtype)
+                acc = v.copy() if acc is None else acc + v
+            mass[g] = acc[0]
+            mom[g] = acc[1:].T
 
     def halo_pack(self):
         self.shared = self.next_shared

@@ -123,6 +123,50 @@ def test_gloo_world2_oracle_backend_matches_single():
         assert ret[0][1] == ret[1][1]          # every rank planned the same shared-block lists
 
 
+@pytest.mark.parametrize("n_ranks", [2, 3])
+def test_peer_window_protocol_on_the_oracle(n_ranks):
+    """slab.InProcessExchange(peer=True) over oracle backends with numpy windows: sharer-set flags, sends into the
+    sharers' windows, rank-ordered sums.  A scene split over the ranks reproduces the single-oracle run and the
+    ranks hold identical bits on the blocks they share (3 ranks: some blocks have three sharers)."""
+    dtype = np.float64
+    sheets = sheets_scene(dtype, n_sheets=6, res=16)
+    if n_ranks == 3:     # 1.2 dx apart instead of 2.7: the outer ranks' stencils meet inside the middle rank's blocks
+        sheets = [(p - np.array([0.0, 0.0, 0.012 * s]), v, t) for s, (p, v, t) in enumerate(sheets)]
+    full = make_oracle(dtype, sheets)
+    parts = slab.partition_meshes(len(sheets), n_ranks)
+    orcs = [make_oracle(dtype, [sheets[i] for i in p]) for p in parts]
+    backs = [OracleHaloBackend(o) for o in orcs]
+    ex = slab.InProcessExchange(backs, peer=True, peer_cap_blocks=4096)
+    shared = 0
+    for it in range(8):
+        sort = it == 3
+        full.substep(DT, -1, sort)
+        for o in orcs:
+            o.RebuildMapping(sort)
+            o.CalcFemStateAndForce(DT)
+            o.ParticleToGrid(DT)
+        shared += ex.exchange()
+        if it == 7:      # identical bits on every pair of sharers, checked on the exchanged sums
+            for a in range(n_ranks):
+                for b in range(a + 1, n_ranks):
+                    both = np.repeat(backs[a].own & backs[b].own, 64)
+                    ma, mb = orcs[a].view("grid_masses"), orcs[b].view("grid_masses")
+                    assert np.array_equal(ma[both], mb[both])
+                    pa, pb = orcs[a].view("grid_momentum").reshape(-1, 3), orcs[b].view("grid_momentum").reshape(-1, 3)
+                    assert np.array_equal(pa[both], pb[both])
+        for o in orcs:
+            o.UpdateGrid(-1)
+            o.GridToParticle(DT)
+    assert shared > 0
+    if n_ranks == 3:
+        assert np.any(np.array([bin(int(s)).count("1") for s in backs[0].sharers]) == 3)
+    ref, _ = full.DumpCpuState()
+    for o, p in zip(orcs, parts):
+        lo, hi = vert_range(sheets, p)
+        got, _ = o.DumpCpuState()
+        assert np.max(np.abs(got - ref[lo:hi])) <= 1e-12 * np.max(np.abs(ref))
+
+
 # ---- device side ----------------------------------------------------------------------------------
 def make_state(dtype, sheets, **params):
     from drake_b200.gpu_mpm import GpuMpmState
@@ -250,6 +294,8 @@ def test_peer_window_exchange_matches_single_state(n_states, overlap):
     import torch
     dtype = np.float64
     sheets = sheets_scene(dtype, n_sheets=6, res=40)
+    if n_states == 3:    # 1.2 dx apart: the outer states' stencils meet inside the middle state's blocks
+        sheets = [(p - np.array([0.0, 0.0, 0.012 * s]), v, t) for s, (p, v, t) in enumerate(sheets)]
     sv = GpuMpmSolver()
     full = make_state(dtype, sheets)
     parts = slab.partition_meshes(len(sheets), n_states)
@@ -298,6 +344,11 @@ def test_peer_window_exchange_matches_single_state(n_states, overlap):
     assert both.any()
     np.testing.assert_array_equal(m[0][both], m[1][both])
     np.testing.assert_array_equal(v[0].reshape(-1, 3)[both], v[1].reshape(-1, 3)[both])
+    if n_states == 3:                          # blocks all three states touched: identical bits on all of them
+        all3 = np.repeat((tf[0] > 0) & (tf[1] > 0) & (tf[2] > 0), 64)
+        assert all3.any()
+        np.testing.assert_array_equal(m[0][all3], m[2][all3])
+        np.testing.assert_array_equal(v[1].reshape(-1, 3)[all3], v[2].reshape(-1, 3)[all3])
     with pytest.raises(Exception):
         sts[0].halo_pack()                     # a peer-mode state has no packed buffer to all-reduce
 
