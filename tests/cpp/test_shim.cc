@@ -26,6 +26,18 @@ static double rel(const std::vector<T>& a, const T* b) {
   return num / std::fmax(den, 1e-300);
 }
 
+// Compile-time coverage of the extension methods for both scalars (their run-time parity is in
+// tests/test_gpu_contact.py and tests/test_gpu_parity.py, through the same C ABI entry points).
+template <typename S>
+void instantiate_extensions(GpuMpmState<S>* st, const GpuMpmSolver<S>& sv) {
+  std::vector<gmpm_analytic_geometry> geoms;
+  sv.GenerateContactPairs(st, geoms);
+  sv.RunDriverSubsteps(st, 1, S(1e-3), geoms, -1, 0, 1, S(0), S(0), S(0), false);
+  st->LoadState(st->SaveState());
+}
+template void instantiate_extensions<float>(GpuMpmState<float>*, const GpuMpmSolver<float>&);
+template void instantiate_extensions<double>(GpuMpmState<double>*, const GpuMpmSolver<double>&);
+
 int main(int argc, char** argv) {
   const int res = argc > 1 ? atoi(argv[1]) : 40;
   const int substeps = argc > 2 ? atoi(argv[2]) : 30;
