@@ -8,7 +8,7 @@ namespace gmpm {
 
 constexpr int kHaloMaxPeers = 8;
 constexpr int kHaloPeerThreads = 128;                              // one CTA per listed block, two values per thread
-constexpr unsigned long long kHaloPeerTimeoutNs = 5000000000ull;  // a delivery takes microseconds
+constexpr unsigned long long kHaloPeerTimeoutNs = 20000000000ull;  // 20 s; a delivery takes microseconds
 constexpr uint32_t kHaloPeerTimeoutCode = 1u << 16;               // added to the error word the next exchange checks
 __device__ __forceinline__ unsigned long long global_timer_ns() {
   unsigned long long t;

@@ -845,7 +845,7 @@ struct State {
     GMPM_CUDA(cudaEventSynchronize(ev_halo_plan));  // issued a whole substep ago (or just now at start-up)
     const int slot = halo_next_slot;
     if (h_halo_words[2 * slot + 1] >= kHaloPeerTimeoutCode)
-      throw std::runtime_error("halo exchange: a rank waited 5 s for a peer's block values (peer-memory windows): a peer "
+      throw std::runtime_error("halo exchange: a rank waited 20 s for a peer's block values (peer-memory windows): a peer "
                                "stopped, or the ranks do not issue the same sequence of exchanges");
     if (h_halo_words[2 * slot + 1] != 0)
       throw std::runtime_error("halo exchange: a particle block appeared outside the dilated block set planned one "
