@@ -89,11 +89,16 @@ __device__ __forceinline__ void halo_wait_sharers(const unsigned char* window, u
   __syncwarp();
 }
 
-// End of a sending kernel: after the stores of ALL its CTAs (threadFenceReduction pattern at system scope) the
-// last CTA raises flag[rank] = xchg in the window of every peer.  Call with all threads of the CTA.
+// End of a sending kernel: after the stores of ALL its CTAs (threadFenceReduction pattern) the last CTA raises
+// flag[rank] = xchg in the window of every peer.  Call with all threads of the CTA.
+// Scopes: the storing threads fence at GPU scope only -- a system-scope fence per warp costs ~20 us per kernel even
+// with purely local stores (measured with two states on one GPU, tools/probe_exchange.py: they serialise) -- and
+// arrive on a GPU-scope counter; the single last arriver then fences at SYSTEM scope before its release stores.
+// PTX causality order is cumulative across scopes: store -> fence.gpu -> arrive  synchronises with  last arrive ->
+// fence.sys -> st.release.sys flag  synchronises with the receiver's ld.acquire.sys, so the data is visible there.
 __device__ __forceinline__ void halo_signal_peers(const HaloWindows& win, uint32_t rank, uint32_t world, uint32_t xchg,
                                                   const uint32_t* peers_mask, uint32_t* done) {
-  __threadfence_system();
+  __threadfence();
   __syncthreads();
   __shared__ bool s_halo_last;
   if (threadIdx.x == 0) s_halo_last = atomicAdd(done, 1u) == gridDim.x - 1;
@@ -113,7 +118,7 @@ __device__ __forceinline__ void halo_signal_peers(const HaloWindows& win, uint32
 __device__ __forceinline__ void halo_signal_peers_warp(const HaloWindows& win, uint32_t rank, uint32_t world,
                                                        uint32_t xchg, const uint32_t* peers_mask, uint32_t* done,
                                                        bool sent) {
-  if (__any_sync(0xFFFFFFFFu, sent)) __threadfence_system();
+  if (__any_sync(0xFFFFFFFFu, sent)) __threadfence();  // GPU scope; the last arriver fences at system scope
   __syncwarp();
   const uint32_t lane = threadIdx.x & 31u;
   uint32_t last = 0;
