@@ -44,6 +44,38 @@ def partition_meshes(n_meshes, world):
     return out
 
 
+def partition_meshes_by_size(sizes, world):
+    """Contiguous split of meshes with UNEQUAL particle counts `sizes` over `world` ranks that minimises the
+    largest rank (the substep time of the job is that of its fullest rank): the classic linear-partition
+    dynamic programme, O(world * n^2).  Contiguity keeps the ranks spatial slabs for stacked scenes, which is
+    what keeps the shared-block set small.  Returns a list of `range`s like partition_meshes; ranks beyond the
+    number of meshes get empty ranges."""
+    n = len(sizes)
+    if n == 0 or world <= 0:
+        return [range(0, 0) for _ in range(max(world, 0))]
+    k = min(world, n)
+    pre = np.concatenate([[0], np.cumsum(np.asarray(sizes, dtype=np.int64))])
+    inf = np.iinfo(np.int64).max
+    best = np.full((k + 1, n + 1), inf, dtype=np.int64)   # best[j][i]: min over splits of the first i meshes into j parts
+    cut = np.zeros((k + 1, n + 1), dtype=np.int64)
+    best[0][0] = 0
+    for j in range(1, k + 1):
+        for i in range(j, n + 1):
+            for s in range(j - 1, i):
+                if best[j - 1][s] == inf:
+                    continue
+                cost = max(int(best[j - 1][s]), int(pre[i] - pre[s]))
+                if cost < best[j][i]:
+                    best[j][i], cut[j][i] = cost, s
+    bounds, i = [n], n
+    for j in range(k, 0, -1):
+        i = int(cut[j][i])
+        bounds.append(i)
+    bounds.reverse()
+    out = [range(bounds[r], bounds[r + 1]) for r in range(k)]
+    return out + [range(n, n) for _ in range(world - k)]
+
+
 class _DevArray:
     """Zero-copy view of a raw device pointer for torch.as_tensor (CUDA array interface v2)."""
 

@@ -123,6 +123,25 @@ def test_gloo_world2_oracle_backend_matches_single():
         assert ret[0][1] == ret[1][1]          # every rank planned the same shared-block lists
 
 
+def test_partition_by_size_minimises_the_fullest_rank():
+    import itertools
+    rng = np.random.default_rng(5)
+    for n, world in [(1, 1), (3, 2), (7, 3), (9, 4), (5, 8), (12, 5)]:
+        sizes = rng.integers(1, 50, size=n)
+        parts = slab.partition_meshes_by_size(sizes, world)
+        assert len(parts) == world
+        assert [i for p in parts for i in p] == list(range(n))          # contiguous cover, in order
+        got = max((sum(sizes[i] for i in p) for p in parts), default=0)
+        k = min(world, n)
+        brute = min(max(sum(sizes[a:b]) for a, b in zip((0,) + c, c + (n,)))
+                    for c in itertools.combinations(range(1, n), k - 1)) if k > 1 else sum(sizes)
+        assert got == brute, (n, world, got, brute)
+    assert slab.partition_meshes_by_size([], 3) == [range(0, 0)] * 3
+    # equal sizes: the same load balance as the plain split
+    eq = slab.partition_meshes_by_size([10] * 8, 4)
+    assert sorted(len(p) for p in eq) == [2, 2, 2, 2]
+
+
 @pytest.mark.parametrize("n_ranks", [2, 3])
 def test_peer_window_protocol_on_the_oracle(n_ranks):
     """slab.InProcessExchange(peer=True) over oracle backends with numpy windows: sharer-set flags, sends into the
