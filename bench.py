@@ -58,16 +58,60 @@ def build_scene(cls_factory, dtype, rank=0, world=1):
     sheets reach common grid blocks, which the ranks sum every substep), columns sit 1.0 apart in x / y."""
     from drake_b200 import scenes
     st = cls_factory()
-    col, lvl = rank // 2, rank % 2
-    ox, oy = (float(col % 2), float(col // 2)) if world > 1 else (0.0, 0.0)
-    z0 = 0.15 + lvl * N_SHEETS * 0.02
-    for pos, vel, tri in scenes.stacked_sheets(N_SHEETS, z0=z0, dtype=dtype, seed=scenes.SEED + rank):
-        pos = pos.astype(np.float64)
-        pos[:, 0] += ox
-        pos[:, 1] += oy
-        st.AddQRCloth(pos.astype(dtype), vel, tri)
+    for r in (rank if isinstance(rank, (list, tuple)) else [rank]):   # a list: the stacks of several ranks in ONE state
+        col, lvl = r // 2, r % 2
+        ox, oy = (float(col % 2), float(col // 2)) if world > 1 else (0.0, 0.0)
+        z0 = 0.15 + lvl * N_SHEETS * 0.02
+        for pos, vel, tri in scenes.stacked_sheets(N_SHEETS, z0=z0, dtype=dtype, seed=scenes.SEED + r):
+            pos = pos.astype(np.float64)
+            pos[:, 0] += ox
+            pos[:, 1] += oy
+            st.AddQRCloth(pos.astype(dtype), vel, tri)
     st.Finalize()
     return st
+
+
+def _rel(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.max(np.abs(a - b)) / max(float(np.max(np.abs(b))), 1e-300))
+
+
+def parity_single(st, dtype, steps):
+    """N = 1: the state the product just computed (`steps` substeps from the fresh scene, re-sort on the first)
+    against the CPU oracle (strict -O2 -ffp-contract=off build) run over the same substeps.  Checker only."""
+    import oracle_py as O
+    from drake_b200 import scenes
+    orc = O.OracleMpm(dtype)
+    for pos, vel, tri in scenes.stacked_sheets(N_SHEETS, dtype=dtype):
+        orc.AddQRCloth(pos, vel, tri)
+    orc.Finalize()
+    cores = os.cpu_count() or 1
+    orc.RebuildMapping(True)
+    for _ in range(steps):
+        orc.substep_omp(DT, -1, cores)
+    out = {"against": "CPU oracle (oracle/gmpm_oracle.c, strict build), same scene, same substeps", "steps": steps,
+           "max_rel_positions": _rel(st.read("positions"), orc.read("positions")),
+           "max_rel_velocities": _rel(st.read("velocities"), orc.read("velocities")),
+           "pids_equal": bool(np.array_equal(st.read("pids"), orc.read("pids")))}
+    orc.close()
+    return out
+
+
+def parity_multi(st, dtype, steps, rank, world, local, make_state):
+    """N > 1: this rank's vertices after `steps` substeps of the multi-rank path (fused peer-window exchange)
+    against ONE state holding the merged scene of its column (this rank's stack and its pile partner's: the
+    columns are a metre apart and never interact), stepped on this GPU without any exchange."""
+    from drake_b200.gpu_mpm import GpuMpmSolver
+    partner = rank ^ 1
+    both = sorted((rank, partner))
+    merged = build_scene(make_state, dtype, both, world)
+    GpuMpmSolver().RunSubsteps(merged, steps, DT, -1, SORT_EVERY)
+    mv, _ = merged.DumpCpuState()
+    mine, _ = st.DumpCpuState()
+    v = mine.shape[0]
+    ref = mv[:v] if rank == both[0] else mv[mv.shape[0] - v:]
+    merged.Destroy()
+    return _rel(mine, ref)
 
 
 def scene_params(world):
@@ -141,7 +185,9 @@ def cpu_baseline(dtype, budget_s=12.0):
     import oracle_py as O
     from drake_b200 import scenes
     cores = os.cpu_count() or 1
-    orc = O.OracleMpm(dtype)
+    # timing-only build of the oracle sources: -O3 -march=native, contraction allowed, compiled on this host
+    # (the bit-exact -O2 -ffp-contract=off build is the parity checker, never the timed one)
+    orc = O.OracleMpm(dtype, fast=True)
     for pos, vel, tri in scenes.stacked_sheets(N_SHEETS, dtype=dtype):
         orc.AddQRCloth(pos, vel, tri)
     orc.Finalize()
@@ -157,8 +203,9 @@ def cpu_baseline(dtype, budget_s=12.0):
     el = time.perf_counter() - t0
     orc.close()
     return {"value": n * steps / el, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": "%d substeps of the full %d-particle scene, %.1f s, OpenMP x%d (oracle/gmpm_oracle.c)" % (steps, n, el, cores),
-            "ms_per_step": el / steps * 1e3}
+            "sample": "%d substeps of the full %d-particle scene, %.1f s, OpenMP x%d (oracle/gmpm_oracle.c, gcc %s)"
+                      % (steps, n, el, cores, " ".join(O.FAST_FLAGS)),
+            "flags": " ".join(O.FAST_FLAGS), "ms_per_step": el / steps * 1e3}
 
 
 def run_reference_arm(args, rank, world):
@@ -173,7 +220,7 @@ def run_reference_arm(args, rank, world):
             "config": {"workload": WORKLOAD, "sort_every": SORT_EVERY,
                        "note": "the reference ships this path only as CUDA; this arm is its CPU restatement "
                                "(oracle/, pinned against the reference's own kernels) on the host cores"},
-            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "flags")},
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
     emit(line)
@@ -202,6 +249,62 @@ def reference_gpu(dtype, steps):
         el = time.perf_counter() - t0
         out["fast_math" if fast else "precise"] = {"value": n * steps / el, "ms_per_step": el / steps * 1e3}
         ref.close()
+    return out
+
+
+def kernel_table(prof, steps, N, n_faces, touched, T, peak):
+    """Per-kernel times of a profiled pass -> us/launch, share, achieved GB/s on SURVEY 8d's algorithmic bytes."""
+    c = touched * 64.0 / N
+    alg = {"p2g_tile": (28 * T + 4 + 8 * T * c) * N,     # SURVEY 8d: P2G = 28T + 4 + 8T c per particle
+           "g2p": (18 * T + 3 * T * c) * N,              # G2P = 18T + 3T c
+           "fem": (28 + 83 * T) * n_faces}               # FEM per face
+    kern = {}
+    tot_ms = sum(v[0] for v in prof.values())
+    for name, (tms, cnt) in prof.items():
+        per = tms / max(cnt, 1)
+        kern[name] = {"us_per_launch": per * 1e3, "launches_per_step": cnt / steps, "share": tms / tot_ms}
+        if name in alg:
+            kern[name]["achieved_gbs"] = alg[name] / (per * 1e-3) / 1e9
+            kern[name]["frac_of_measured_peak"] = kern[name]["achieved_gbs"] / peak
+    return kern, alg, c
+
+
+def f32_line(local, peak, steps):
+    """The reference's PRODUCT dtype (settings.h:37 `using GpuT = float`, built with -use_fast_math,
+    tools/skylark/cuda.bzl:66-86) on the same scene: device-timed value, per-kernel table, parity of the first
+    20 substeps against the fp32 CPU oracle, and the reference's own fp32 kernels on this GPU."""
+    from drake_b200.gpu_mpm import GpuMpmSolver, GpuMpmState
+    dtype = np.float32
+    st = build_scene(lambda: GpuMpmState(dtype, device=local), dtype)
+    sv = GpuMpmSolver()
+    N = st.n_particles()
+    sv.RunSubsteps(st, 20, DT, -1, SORT_EVERY)
+    sv.GpuSync(st)
+    par = parity_single(st, dtype, 20)
+    par["tolerance"] = 5e-4
+    par["ok"] = bool(max(par["max_rel_positions"], par["max_rel_velocities"]) <= 5e-4)
+    sv.RunSubsteps(st, 60, DT, -1, SORT_EVERY)
+    sv.GpuSync(st)
+    st.timer_mark(0)
+    sv.RunSubsteps(st, steps, DT, -1, SORT_EVERY)
+    st.timer_mark(1)
+    sv.GpuSync(st)
+    ms = st.timer_elapsed_ms(0, 1)
+    Kp = min(steps, 200)
+    st.set_profiling(True)
+    sv.RunSubsteps(st, Kp, DT, -1, SORT_EVERY)
+    sv.GpuSync(st)
+    prof = st.profile_report()
+    st.set_profiling(False)
+    _, touched = st.block_counts()
+    kern, _, c = kernel_table(prof, Kp, N, st.n_faces(), touched, 4, peak)
+    out = {"dtype": "f32", "value": N * steps / (ms * 1e-3), "unit": UNIT, "steps": steps, "ms_per_step": ms / steps,
+           "touched_cells_per_particle": c, "kernels": kern, "parity": par}
+    st.Destroy()
+    try:
+        out["reference_gpu"] = reference_gpu(dtype, 100)
+    except Exception as e:
+        out["reference_gpu"] = {"unavailable": repr(e)}
     return out
 
 
@@ -243,8 +346,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=80)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"])
+    ap.add_argument("--parity-steps", type=int, default=20,
+                    help="substeps of the fresh scene checked against the oracle before the timed region (0 = off)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-gpu", action="store_true")
+    ap.add_argument("--no-f32", action="store_true", help="skip the fp32 (reference product dtype) sub-line")
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--overlap", action="store_true",
                     help="N>1: UpdateGrid/G2P in two parts around the exchange (interior work hides the all-reduce)")
@@ -318,6 +424,28 @@ def main():
             plan_wait[0] += time.perf_counter() - t
             return r
         ex.begin = timed_begin
+
+    # ---- parity pass: the first substeps of the fresh scene, checked (not timed); they double as warm-up ----
+    parity = None
+    P = max(0, args.parity_steps)
+    if P > 0:
+        run_substeps(P)
+        sv.GpuSync(st)
+        tol = 1e-7 if args.dtype == "f64" else 5e-4     # north_star: 1e-9 per step, 1e-6 after 100 (fp64)
+        if world == 1:
+            parity = parity_single(st, dtype, P)
+            worst = max(parity["max_rel_positions"], parity["max_rel_velocities"])
+            parity["tolerance"] = tol
+            parity["ok"] = bool(worst <= tol and parity["pids_equal"])
+        else:
+            mine = parity_multi(st, dtype, P, rank, world, local,
+                                lambda: GpuMpmState(dtype, device=local, **scene_params(world)))
+            t = torch.tensor([mine], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            parity = {"against": "one state per column holding the merged scene of both sharers, no exchange",
+                      "steps": P, "max_rel_vertex_positions": float(t[0]), "ranks_checked": world,
+                      "tolerance": tol, "ok": bool(float(t[0]) <= tol)}
+        print("[bench] rank %d parity: %s" % (rank, parity), file=sys.stderr)
 
     sampler = ClockSampler(local)
     sampler.start()
@@ -417,18 +545,7 @@ def main():
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "MEASURED_PEAKS.json hbm_gbs (measured copy, burst)" if "hbm_gbs" in peaks else "fallback 6.65 TB/s"
-        c = touched * 64.0 / N
-        alg = {"p2g_tile": (28 * T + 4 + 8 * T * c) * N,     # P2G = 28T + 4 + 8T c per particle
-               "g2p": (18 * T + 3 * T * c) * N,              # G2P = 18T + 3T c
-               "fem": (28 + 83 * T) * st.n_faces()}          # FEM per face
-        kern = {}
-        tot_ms = sum(v[0] for v in prof.values())
-        for name, (tms, cnt) in prof.items():
-            per = tms / max(cnt, 1)
-            kern[name] = {"us_per_launch": per * 1e3, "launches_per_step": cnt / Kp, "share": tms / tot_ms}
-            if name in alg:
-                kern[name]["achieved_gbs"] = alg[name] / (per * 1e-3) / 1e9
-                kern[name]["frac_of_measured_peak"] = kern[name]["achieved_gbs"] / peak
+        kern, alg, c = kernel_table(prof, Kp, N, st.n_faces(), touched, T, peak)
         dom = max(alg, key=lambda n: prof.get(n, (0, 1))[0])
         traffic = None
         try:
@@ -459,16 +576,27 @@ def main():
                                 "positions -> pinned host mirror, copy overlapped with the next 4 solver calls), "
                                 "positions_host() wait + host read, CopyContactPairs (0 pairs), 5 solver calls"},
                 "gpu_launches": launches_all, "gpu_launches_per_step": launches_all / K / world,
-                "roofline": roofline, "kernels": kern}
+                "roofline": roofline, "kernels": kern, "parity": parity}
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_baseline(dtype)
-            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "flags")}
             line["speedup_vs_cpu_port"] = {"device": line["value"] / cb["value"], "e2e": line["e2e"]["value"] / cb["value"]}
         if world == 1 and not args.no_ref_gpu:
             try:
                 line["reference_gpu"] = reference_gpu(dtype, 100)
             except Exception as e:  # checker library missing or failed: not fatal for the product line
                 line["reference_gpu"] = {"unavailable": repr(e)}
+        if world == 1 and args.dtype == "f64" and not args.no_f32:
+            try:
+                line["f32"] = f32_line(local, peak, min(K, 400))
+            except Exception as e:
+                line["f32"] = {"unavailable": repr(e)}
+        if world == 1 and "reference_gpu" in line and "fast_math" in line.get("reference_gpu", {}):
+            line["vs_existing_kernel"] = {
+                "f64": line["value"] / line["reference_gpu"]["fast_math"]["value"],
+                "f32": (line["f32"]["value"] / line["f32"]["reference_gpu"]["fast_math"]["value"]
+                        if "fast_math" in line.get("f32", {}).get("reference_gpu", {}) else None),
+                "what": "device-timed value / the reference's own kernels (as shipped: -use_fast_math) on this GPU"}
         emit(line)
     st.Destroy()
     if dist is not None:

@@ -81,9 +81,24 @@ void State<T>::load_state(const void* in, size_t bytes) {
   if (h.scalar_bytes != sizeof(T) || h.N != N || h.n_verts != n_verts || h.n_faces != n_faces ||
       h.domain_bits != (uint32_t)k.domain_bits || bytes != checkpoint_bytes())
     throw std::invalid_argument("gmpm_load_state: the checkpoint was taken from a different scene (sizes, scalar or grid)");
+  if (std::fabs(h.dx - (double)k.dx) > 1e-12 * std::fabs((double)k.dx))
+    throw std::invalid_argument("gmpm_load_state: the checkpoint was taken with a different cell size dx");
   if (N == 0) return;
   const uint32_t n = (uint32_t)N, F = (uint32_t)n_faces;
   const char* p = static_cast<const char*>(in) + sizeof(h);
+  {
+    // pids drive scattered device writes: they must be a permutation of 0..N-1 that keeps face particles (pid <
+    // n_faces) distinguishable -- checked on the host, where the blob already is
+    const int* hp = reinterpret_cast<const int*>(p + sizeof(T) * (16 * N + 13 * n_faces));
+    std::vector<uint8_t> seen(N, 0);
+    for (size_t v = 0; v < N; ++v) {
+      int q;
+      std::memcpy(&q, hp + v, sizeof(int));
+      if (q < 0 || (size_t)q >= N || seen[(size_t)q])
+        throw std::invalid_argument("gmpm_load_state: corrupt checkpoint (pids are not a permutation of 0..N-1)");
+      seen[(size_t)q] = 1;
+    }
+  }
   // one staging upload, then layout conversion on the device (slot = visible index)
   const size_t payload = bytes - sizeof(h);
   char* stage = static_cast<char*>(io(payload));
@@ -124,6 +139,8 @@ void State<T>::load_state(const void* in, size_t bytes) {
   cb_valid = false;
   g2p_queue_ready = false;
   halo_planned = halo_plan_pending = halo_flags_out = halo_own_valid = halo_packed_out = false;
+  halo_sent = halo_recv_pending = false;
+  this->stage = GridStage::kClean;   // whatever the grid held belongs to the replaced particles: the next P2G starts over
 }
 
 }  // namespace gmpm

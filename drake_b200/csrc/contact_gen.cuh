@@ -224,7 +224,7 @@ void State<T>::run_driver_substeps(int n, T dt, int bc, int sort_every, const gm
     if (query) {
       for (size_t g = 0; g < n_geoms; ++g)
         for (int d = 0; d < 3; ++d) {
-          const double shift = geoms[g].velocity[d] * (double)dt * i;
+          const double shift = driver_geometry_frozen ? 0.0 : geoms[g].velocity[d] * (double)dt * i;
           moved[g].lo[d] = geoms[g].lo[d] + shift;
           if (geoms[g].kind == GMPM_GEOM_BOX) moved[g].hi[d] = geoms[g].hi[d] + shift;
           moved[g].p_WB[d] = geoms[g].p_WB[d] + shift;

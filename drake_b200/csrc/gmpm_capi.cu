@@ -189,6 +189,9 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
                                 exact != 0, max_it, stats);                                                    \
     });                                                                                                        \
   }                                                                                                            \
+  int gmpm_set_driver_geometry_frozen_##SUF(gmpm_state_##SUF* s, int frozen) {                                 \
+    return guarded([&] { s->st.driver_geometry_frozen = frozen != 0; });                                       \
+  }                                                                                                            \
   int gmpm_update_contact_##SUF(gmpm_state_##SUF* s, T dt, T mu, T stiffness, T damping, int exact, int max_it,\
                                 gmpm_contact_stats* stats) {                                                   \
     return guarded([&] { s->st.update_contact(dt, mu, stiffness, damping, exact != 0, max_it, stats); });      \

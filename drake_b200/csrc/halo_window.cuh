@@ -17,6 +17,11 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
 }
 struct HaloWindows {
   unsigned char* base[kHaloMaxPeers];
+  // false (default): every thread that stored into a peer window fences at SYSTEM scope itself -- the documented
+  // requirement for peer visibility.  true (GMPM_HALO_GPU_SCOPE_FENCE=1): the storers fence at GPU scope and only the
+  // last arriver fences at system scope (valid under PTX cross-scope cumulativity; ~8 us faster per substep; kept
+  // behind the switch until the multi-rank stress test has run on it, tests/test_slab.py).
+  uint32_t gpu_scope_fence;
 };
 // Window layout: flag[64] | present[2][world][cap] | (256-byte aligned) data[2][world][cap][256]
 __host__ __device__ inline size_t halo_window_data_offset(uint32_t world, uint32_t cap) {
@@ -91,14 +96,15 @@ __device__ __forceinline__ void halo_wait_sharers(const unsigned char* window, u
 
 // End of a sending kernel: after the stores of ALL its CTAs (threadFenceReduction pattern) the last CTA raises
 // flag[rank] = xchg in the window of every peer.  Call with all threads of the CTA.
-// Scopes: the storing threads fence at GPU scope only -- a system-scope fence per warp costs ~20 us per kernel even
+// Scopes (win.gpu_scope_fence = 1 only; by default every storer fences at system scope): the storing threads fence
+// at GPU scope only -- a system-scope fence per warp costs ~20 us per kernel even
 // with purely local stores (measured with two states on one GPU, tools/probe_exchange.py: they serialise) -- and
 // arrive on a GPU-scope counter; the single last arriver then fences at SYSTEM scope before its release stores.
 // PTX causality order is cumulative across scopes: store -> fence.gpu -> arrive  synchronises with  last arrive ->
 // fence.sys -> st.release.sys flag  synchronises with the receiver's ld.acquire.sys, so the data is visible there.
 __device__ __forceinline__ void halo_signal_peers(const HaloWindows& win, uint32_t rank, uint32_t world, uint32_t xchg,
                                                   const uint32_t* peers_mask, uint32_t* done) {
-  __threadfence();
+  if (win.gpu_scope_fence) __threadfence(); else __threadfence_system();
   __syncthreads();
   __shared__ bool s_halo_last;
   if (threadIdx.x == 0) s_halo_last = atomicAdd(done, 1u) == gridDim.x - 1;
@@ -118,7 +124,10 @@ __device__ __forceinline__ void halo_signal_peers(const HaloWindows& win, uint32
 __device__ __forceinline__ void halo_signal_peers_warp(const HaloWindows& win, uint32_t rank, uint32_t world,
                                                        uint32_t xchg, const uint32_t* peers_mask, uint32_t* done,
                                                        bool sent) {
-  if (__any_sync(0xFFFFFFFFu, sent)) __threadfence();  // GPU scope; the last arriver fences at system scope
+  if (__any_sync(0xFFFFFFFFu, sent)) {
+    if (win.gpu_scope_fence) __threadfence();  // GPU scope; the last arriver fences at system scope
+    else __threadfence_system();
+  }
   __syncwarp();
   const uint32_t lane = threadIdx.x & 31u;
   uint32_t last = 0;

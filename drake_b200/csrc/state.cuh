@@ -147,6 +147,7 @@ struct State {
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_gather = nullptr, ev_copy = nullptr;
   bool copy_pending = false;
+  bool driver_geometry_frozen = false;  // run_driver_substeps: keep the rigid poses for all substeps (reference driver)
   bool snapshot_valid = false;  // pos_stage holds the positions of the current substep (cleared by g2p)
   // device-side contact generation (contact_gen.cuh)
   uint32_t* gen_counts = nullptr;
@@ -509,6 +510,7 @@ struct State {
     GMPM_CUDA(cudaGetLastError());
     vis_cur ^= 1;
     vis_keys_valid = true;
+    snapshot_valid = false;  // pos_stage is in the visible order that has just been renumbered
   }
 
   void materialize_visible_keys() {
@@ -851,6 +853,9 @@ struct State {
       throw std::runtime_error("halo exchange: a particle block appeared outside the dilated block set planned one "
                                "substep earlier (a particle moved more than one grid block in a substep)");
     uint32_t n = h_halo_words[2 * slot];
+    if (halo_peer && n > halo_win_cap)  // the windows are fixed at halo_peer_init: refuse BEFORE touching any list
+      throw std::runtime_error("halo exchange: " + std::to_string(n) + " shared blocks, more than the peer windows were "
+                               "sized for (" + std::to_string(halo_win_cap) + "): raise cap_blocks in halo_peer_init");
     if (n > halo_cap) {  // rare: the lists were too short; grow and redo the compaction (flags still hold the sums)
       halo_reserve(n);
       halo_compact_into(slot, stream);
@@ -932,6 +937,7 @@ struct State {
     halo_rank = rank;
     halo_world = world;
     halo_windows.base[rank] = halo_window;
+    halo_windows.gpu_scope_fence = std::getenv("GMPM_HALO_GPU_SCOPE_FENCE") != nullptr ? 1u : 0u;
     halo_peer = true;
     halo_own_valid = false;
     halo_xchg = 0;

@@ -446,12 +446,15 @@ class GpuMpmSolver:
         return arr
 
     def RunDriverSubsteps(self, state, n, dt, geometries=(), mpm_bc=-1, sort_every=0, contact_query_frequency=1,
-                          friction_mu=0.0, stiffness=0.0, damping=0.0, exact_line_search=False, max_iterations=0):
+                          friction_mu=0.0, stiffness=0.0, damping=0.0, exact_line_search=False, max_iterations=0,
+                          freeze_geometry=False):
         """n substeps of the DeformableDriver loop (deformable_driver.h:240-260) in one ABI call, contact pairs
         from analytic geometry generated on the device every `contact_query_frequency` substeps
         (MpmConfigParams::contact_query_frequency).  Geometries move with their velocity.  -> DriverStats."""
         geometries = list(geometries)
         arr = self._geometry_array(geometries)
+        # freeze_geometry: the reference driver's behaviour (rigid poses constant over the substeps of a frame)
+        check(state._f("set_driver_geometry_frozen")(state._h, 1 if freeze_geometry else 0))
         st = _lib.DriverStats()
         ct = state._ct
         check(state._f("run_driver_substeps")(state._h, int(n), ct(dt), int(mpm_bc), int(sort_every), arr, len(geometries),

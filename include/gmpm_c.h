@@ -154,6 +154,10 @@ int gmpm_device_sync(void);
                                      int contact_query_frequency, T friction_mu, T stiffness,       \
                                      T damping, int exact_line_search, int max_iterations,          \
                                      gmpm_driver_stats* stats);                                     \
+  /* frozen != 0: gmpm_run_driver_substeps keeps the geometries at the given pose for all n substeps */ \
+  /* (the reference driver's behaviour: the rigid poses of deformable_driver.h:240-260 are those of   */\
+  /* the frame's context, constant over its substeps).  Default 0: they advance by velocity*dt.       */\
+  int gmpm_set_driver_geometry_frozen_##SUF(gmpm_state_##SUF* s, int frozen);                       \
   /* GpuMpmSolver<T>::UpdateContact, cuda_mpm_solver.cu:215-621.  max_iterations <= 0 -> 2000. */   \
   int gmpm_update_contact_##SUF(gmpm_state_##SUF* s, T dt, T friction_mu, T stiffness, T damping,   \
                                 int exact_line_search, int max_iterations,                          \

@@ -81,6 +81,7 @@ template <typename T> struct Abi;
     static constexpr auto update_contact = gmpm_update_contact_##SUF;                                \
     static constexpr auto generate_contact_pairs = gmpm_generate_contact_pairs_##SUF;                \
     static constexpr auto run_driver_substeps = gmpm_run_driver_substeps_##SUF;                      \
+    static constexpr auto set_driver_geometry_frozen = gmpm_set_driver_geometry_frozen_##SUF;        \
     static constexpr auto reallocate_external_bodies = gmpm_reallocate_external_bodies_##SUF;        \
     static constexpr auto external_body_force_to_host = gmpm_external_body_force_to_host_##SUF;      \
     static constexpr auto dump_cpu_state = gmpm_dump_cpu_state_##SUF;                                \

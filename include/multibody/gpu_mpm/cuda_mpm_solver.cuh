@@ -82,8 +82,10 @@ class GpuMpmSolver {
   gmpm_driver_stats RunDriverSubsteps(GpuMpmState<T>* state, int n, const T& dt,
                                       const std::vector<gmpm_analytic_geometry>& geometries, int mpm_bc, int sort_every,
                                       int contact_query_frequency, const T& friction_mu, const T& stiffness,
-                                      const T& damping, bool exact_line_search) const {
+                                      const T& damping, bool exact_line_search, bool freeze_geometry = false) const {
     gmpm_driver_stats stats{};
+    // freeze_geometry = true is the reference driver: rigid poses constant over the substeps of a frame
+    internal::Check(Abi::set_driver_geometry_frozen(state->raw(), freeze_geometry ? 1 : 0), "RunDriverSubsteps");
     internal::Check(Abi::run_driver_substeps(state->raw(), n, dt, mpm_bc, sort_every, geometries.data(),
                                              geometries.size(), contact_query_frequency, friction_mu, stiffness, damping,
                                              exact_line_search ? 1 : 0, 0, &stats),

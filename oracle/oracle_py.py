@@ -55,11 +55,42 @@ def build(force=False):
     return _LIB_PATH
 
 
+FAST_FLAGS = ["-std=c11", "-O3", "-march=native", "-fopenmp", "-fno-math-errno"]
+
+
+def build_fast():
+    """Timing-only build of the SAME sources (`-O3 -march=native`, FMA contraction allowed) for bench.py's
+    cpu_baseline / --impl reference.  The bit-exact `-O2 -ffp-contract=off` library stays the oracle
+    of the parity tests.  `-march=native` binds the file to the host CPU, so it is compiled where it runs (the GPU
+    box has gcc) and named after that CPU's feature flags."""
+    import hashlib
+    try:
+        flags = next(l for l in open("/proc/cpuinfo") if l.startswith("flags"))
+    except Exception:
+        flags = "unknown"
+    tag = hashlib.sha1(flags.encode()).hexdigest()[:10]
+    out_dir = os.path.join(_HERE, "_fast")
+    path = os.path.join(out_dir, "libgmpm_oracle_fast_%s.so" % tag)
+    srcs = [os.path.join(_HERE, f) for f in ("gmpm_oracle.c", "gmpm_oracle_impl.inc", "gmpm_oracle.h")]
+    if os.path.exists(path) and os.path.getmtime(path) >= max(os.path.getmtime(s) for s in srcs):
+        return path
+    os.makedirs(out_dir, exist_ok=True)
+    cc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else "gcc"   # the image's CC wrapper lacks libgomp.spec
+    subprocess.check_call([cc, *FAST_FLAGS, "-shared", "-fPIC", srcs[0], "-o", path, "-lm"])
+    return path
+
+
 _lib = None
+_lib_fast = None
 
 
-def lib():
-    global _lib
+def lib(fast=False):
+    global _lib, _lib_fast
+    if fast:
+        if _lib_fast is None:
+            _lib_fast = C.CDLL(build_fast())
+            _declare(_lib_fast)
+        return _lib_fast
     if _lib is None:
         build()
         _lib = C.CDLL(_LIB_PATH)
@@ -146,12 +177,13 @@ _VIEWS = {
 class OracleMpm:
     """Same call sequence as the reference's GpuMpmState/GpuMpmSolver, on the CPU restatement."""
 
-    def __init__(self, dtype=np.float64, params=None):
+    def __init__(self, dtype=np.float64, params=None, fast=False):
+        """fast=True: the timing-only `-O3 -march=native` build (bench.py only; never a parity checker)."""
         self.dtype = np.dtype(dtype)
         self.suf = "f32" if self.dtype == np.float32 else "f64"
         self.ct = C.c_float if self.suf == "f32" else C.c_double
         self.params = params if params is not None else default_params()
-        self._L = lib()
+        self._L = lib(fast)
         self.h = self._f("create")(C.byref(self.params))
 
     def _f(self, name):

@@ -465,7 +465,12 @@ def test_oracle_pinned_against_reference_kernels(dtype, tol1, tol20):
         orc.RebuildMapping(True)
         sv.RebuildMapping(st, True)
         rk = ref.read("sort_keys", N, np.uint32)
-        if np.array_equal(np.sort(orc.read("sort_keys")), np.sort(rk)):
+        same = np.array_equal(np.sort(orc.read("sort_keys")), np.sort(rk))
+        if not warm and dtype == np.float64:
+            # cold scene, fp64: positions agree to 1e-7 and no particle sits on a cell boundary -> the key
+            # multisets ARE equal; anything else is a failure, not a skip
+            assert same, "cold fp64 scene: oracle and reference kernels disagree on the cell keys"
+        if same:
             for name in ("sort_keys", "sort_ids"):
                 r = ref.read(name, N, np.uint32)
                 assert np.array_equal(orc.read(name), r), name
@@ -475,7 +480,18 @@ def test_oracle_pinned_against_reference_kernels(dtype, tol1, tol20):
                 assert np.array_equal(orc.read(name), r), name
                 assert np.array_equal(st.read(name), r), name
         else:
-            assert not warm or steps > 1
+            # a last-ulp position difference moved a particle across a cell boundary (allowed by the tolerance
+            # on positions): the sort itself is then checked on the reference's OWN keys
+            import ctypes as C
+            ids = np.arange(N, dtype=np.uint32)
+            ref.RebuildMapping(False)
+            keys = ref.read("sort_keys", N, np.uint32)
+            ref.RebuildMapping(True)
+            eko, eio = np.zeros(N, np.uint32), np.zeros(N, np.uint32)
+            p = lambda a: a.ctypes.data_as(C.c_void_p)
+            O.lib().ogmpm_stable_sort_low_bits(p(keys), p(ids), N, 16, p(eko), p(eio))
+            assert np.array_equal(ref.read("sort_keys", N, np.uint32), eko)
+            print("key multisets differ (%s, warm=%s): sort checked on the reference's own keys" % (np.dtype(dtype).name, warm))
         ref.close()
 
 
