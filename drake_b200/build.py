@@ -39,6 +39,7 @@ def build(force=False, verbose=False):
     os.makedirs(LIB_DIR, exist_ok=True)
     cmd = [_nvcc(), *ARCH, "-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-shared",
            "-I" + os.path.join(ROOT, "include"), os.path.join(CSRC, "gmpm_capi.cu"), "-o", LIB]
+    cmd[1:1] = os.environ.get("GMPM_NVCC_FLAGS", "").split()   # development A/B switches (-DGMPM_CHUNK=120 ...)
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd))

@@ -20,7 +20,10 @@
 namespace gmpm {
 
 constexpr int kThreads = 256;
-constexpr int kChunk = 128;  // particles per unit of work (a particle block is split into chunks of <= kChunk)
+#ifndef GMPM_CHUNK
+#define GMPM_CHUNK 128
+#endif
+constexpr int kChunk = GMPM_CHUNK;  // particles per unit of work (a particle block is split into chunks of <= kChunk)
 
 // Device-resident counters (no host round trips inside a substep).
 struct DevCounters {
@@ -1071,7 +1074,7 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __rest
   const T scale = T(4) * k.dx_inv;
   const T ca = (k.v_blend + T(1)) * T(.5), cb = (k.v_blend - T(1)) * T(.5);
   constexpr uint32_t kNone = 0xFFFFFFFFu;
-  static_assert(kChunk == 128, "the slot-index rotation below assumes 4 batches per chunk");
+  static_assert(kChunk <= 128 && kChunk > 96, "the slot-index rotation below assumes 4 batches per chunk");
 
   uint32_t* queue = want == 1 ? &ctr->work_grid : &ctr->work_g2p;  // the second part has a counter of its own
   auto ticket = [&]() -> uint32_t {

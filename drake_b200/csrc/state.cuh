@@ -12,6 +12,7 @@
 #include "common.cuh"
 #include "halo.cuh"
 #include "kernels.cuh"
+#include "p2g_col.cuh"
 #include "sort.cuh"
 
 namespace gmpm {
@@ -191,6 +192,9 @@ struct State {
   uint64_t launches = 0;
   Profiler prof;
   int sm_count = 148;
+  static constexpr int kP2GDefault = 0;  // 0 tile (default: fastest at fp32, within 3 % at fp64), 1 column, 2 column + bulk tile store (profiles/r02_p2g_ab.txt)
+  int p2g_variant = kP2GDefault;
+  size_t p2g_smem = 0;
   int p2g_ctas_per_sm = 1, g2p_ctas_per_sm = 1, fem_ctas_per_sm = 1, bin_ctas = 0, sort_ctas = 0;
   bool g2p_queue_ready = false;
   bool forces_zero = true;      // forces[] is all zeros (fresh allocation, or g2p just wrote the zeros)
@@ -404,11 +408,16 @@ struct State {
                                                                       vol[0], Dm_inv, Fd, k.dx);
       GMPM_CUDA(cudaGetLastError());
     }
-    GMPM_CUDA(cudaFuncSetAttribute(p2g_tile_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)sizeof(P2GSmem<T>)));
-    GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p2g_ctas_per_sm, p2g_tile_kernel<T>, kP2GThreads,
-                                                            sizeof(P2GSmem<T>)));
-    if (p2g_ctas_per_sm < 1) throw CudaError(cudaErrorLaunchOutOfResources, "p2g_tile_kernel does not fit on an SM");
+    {
+      const char* v = std::getenv("GMPM_P2G");  // A/B switch: "tile" (round-1 kernel), "col", "colbulk"
+      p2g_variant = !v ? kP2GDefault : !std::strcmp(v, "tile") ? 0 : !std::strcmp(v, "col") ? 1 : 2;
+      const void* fn = p2g_variant == 0 ? (const void*)p2g_tile_kernel<T>
+                       : p2g_variant == 1 ? (const void*)p2g_col_kernel<T, false> : (const void*)p2g_col_kernel<T, true>;
+      p2g_smem = p2g_variant == 0 ? sizeof(P2GSmem<T>) : sizeof(P2GColSmem<T>);
+      GMPM_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p2g_smem));
+      GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p2g_ctas_per_sm, fn, kP2GThreads, p2g_smem));
+      if (p2g_ctas_per_sm < 1) throw CudaError(cudaErrorLaunchOutOfResources, "the P2G kernel does not fit on an SM");
+    }
     GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g2p_ctas_per_sm, g2p_kernel<T>, kG2PWarps * 32, 0));
     g2p_ctas_per_sm = std::max(1, std::min(g2p_ctas_per_sm, 8));
     GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fem_ctas_per_sm, fem_kernel<T>, kFemThreads, 0));
@@ -510,7 +519,10 @@ struct State {
     GMPM_CUDA(cudaGetLastError());
     vis_cur ^= 1;
     vis_keys_valid = true;
-    snapshot_valid = false;  // pos_stage is in the visible order that has just been renumbered
+    // pos_stage (SyncParticleStateToCpu -> device-side contact query) is in the visible order that has just been
+    // renumbered: gather it again (nothing has moved since the snapshot if the caller follows the driver's order;
+    // the HOST mirror keeps the numbering the host saw, as upstream, whose driver never sorts inside this loop)
+    if (snapshot_valid) snapshot_positions_device();
   }
 
   void materialize_visible_keys() {
@@ -587,10 +599,16 @@ struct State {
     prologue_done = false;
     halo_nbr_zeroed_epoch = halo_nbr ? p2g_epoch : 0;  // the tile kernel zeroes the entries it appends
     launch("p2g_tile");
-    p2g_tile_kernel<T><<<persistent_ctas(p2g_ctas_per_sm), kP2GThreads, sizeof(P2GSmem<T>), stream>>>(
-        (uint32_t)N, (uint32_t)n_faces, order(), sorted_keys(), pb_work, (uint32_t)work_cap, pos[cur], vel[cur],
-        vol[cur], C[cur], pid[cur], forces, taus, tiles, touched_epoch, touched_list[tl_cur], p2g_epoch, ctr, dt, k,
-        halo_nbr);
+#define GMPM_P2G_ARGS                                                                                            \
+  (uint32_t) N, (uint32_t)n_faces, order(), sorted_keys(), pb_work, (uint32_t)work_cap, pos[cur], vel[cur], vol[cur], \
+      C[cur], pid[cur], forces, taus, tiles, touched_epoch, touched_list[tl_cur], p2g_epoch, ctr, dt, k, halo_nbr
+    if (p2g_variant == 0)
+      p2g_tile_kernel<T><<<persistent_ctas(p2g_ctas_per_sm), kP2GThreads, p2g_smem, stream>>>(GMPM_P2G_ARGS);
+    else if (p2g_variant == 1)
+      p2g_col_kernel<T, false><<<persistent_ctas(p2g_ctas_per_sm), kP2GThreads, p2g_smem, stream>>>(GMPM_P2G_ARGS);
+    else
+      p2g_col_kernel<T, true><<<persistent_ctas(p2g_ctas_per_sm), kP2GThreads, p2g_smem, stream>>>(GMPM_P2G_ARGS);
+#undef GMPM_P2G_ARGS
     g2p_queue_ready = true;  // the prologue reset both work queues
     launch("clean_stale_blocks");
     clean_stale_blocks_kernel<T><<<persistent_ctas(2), kThreads, 0, stream>>>(touched_list[tl_cur ^ 1], ctr,

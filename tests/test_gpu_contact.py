@@ -286,8 +286,8 @@ def test_device_generated_pairs_equal_the_host_path(dtype):
         st.ReallocateExternelBodies(3)
         sv = GpuMpmSolver()
         for it in range(3):
-            sv.SyncParticleStateToCpu(st)
-            sv.RebuildMapping(st, it == 1)
+            sv.RebuildMapping(st, it == 1)     # the snapshot follows the re-sort: pair indices are visible indices
+            sv.SyncParticleStateToCpu(st)      # (upstream's driver never sorts inside this loop)
             sv.CalcFemStateAndForce(st, DT)
             sv.ParticleToGrid(st, DT)
             sv.UpdateGrid(st, -1)
@@ -378,3 +378,36 @@ def test_library_side_driver_loop_equals_the_call_by_call_loop():
     assert rel(f.read("positions"), e.read("positions")) <= 1e-12
     for s in (a, b, c, e, f):
         s.Destroy()
+
+
+def test_device_pairs_follow_a_resort_issued_after_the_snapshot():
+    """SyncParticleStateToCpu -> RebuildMapping(sort=true) -> ... -> GenerateContactPairs.  The re-sort
+    renumbers the visible order after the snapshot was taken; the device-side query must still pair the particles that
+    are inside the geometry (same physical pairs as with the snapshot taken after the re-sort)."""
+    dtype = np.float64
+    geoms = [{"kind": "box", "rigid_id": 1, "lo": BOX[0], "hi": BOX[1], "velocity": (0.0, 0.0, 0.05)}]
+    got = []
+    for sync_first in (True, False):
+        st = GpuMpmState(dtype)
+        for pos, vel, tri in sheet_over_box(dtype):
+            st.AddQRCloth(pos, vel, tri)
+        st.Finalize()
+        st.ReallocateExternelBodies(2)
+        sv = GpuMpmSolver()
+        sv.RunSubsteps(st, 3, DT, -1, 0)          # particles move: the 16-bit sort below really permutes
+        if sync_first:
+            sv.SyncParticleStateToCpu(st)
+            sv.RebuildMapping(st, True)
+        else:
+            sv.RebuildMapping(st, True)
+            sv.SyncParticleStateToCpu(st)
+        sv.CalcFemStateAndForce(st, DT); sv.ParticleToGrid(st, DT); sv.UpdateGrid(st, -1)
+        n = sv.GenerateContactPairs(st, geoms)
+        assert n > 50
+        pids = st.read("pids")
+        got.append((pids[st.read("contact_mpm_id")], st.read("contact_pos").reshape(-1, 3)))
+        # every pair's stored position is the visible particle's position
+        vis_pos = st.read("positions").reshape(-1, 3)
+        st.Destroy()
+    assert np.array_equal(got[0][0], got[1][0])
+    assert np.array_equal(got[0][1], got[1][1])
