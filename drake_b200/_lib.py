@@ -43,7 +43,7 @@ PLAIN_SYMBOLS = ["gmpm_default_params", "gmpm_last_error", "gmpm_version", "gmpm
                  "gmpm_morton_code", "gmpm_cell_index", "gmpm_inverse_cell_index", "gmpm_radix_sort_pairs"]
 TYPED_SYMBOLS = ["create", "destroy", "add_qr_cloth", "finalize", "rebuild_mapping", "calc_fem", "p2g",
                  "update_grid", "g2p", "sync", "sync_particle_state_to_cpu", "sync_particle_state_to_cpu_async",
-                 "positions_host", "halo_flags", "halo_plan_async", "halo_pack", "halo_unpack", "halo_peer_init", "halo_peer_window", "halo_peer_attach", "halo_peer_send", "halo_peer_recv", "update_grid_part", "g2p_part", "stream", "halo_stream", "copy_contact_pairs",
+                 "positions_host", "set_query_bounds", "clear_query_bounds", "snapshot_d2h_bytes", "halo_flags", "halo_plan_async", "halo_pack", "halo_unpack", "halo_peer_init", "halo_peer_window", "halo_peer_attach", "halo_peer_send", "halo_peer_recv", "update_grid_part", "g2p_part", "stream", "halo_stream", "copy_contact_pairs",
                  "generate_contact_pairs", "run_driver_substeps", "set_driver_geometry_frozen", "update_contact", "reallocate_external_bodies", "external_body_force_to_host",
                  "dump_cpu_state", "n_verts", "n_faces", "n_particles", "n_cells", "num_contacts",
                  "grid_touched_cnt_host", "read", "checkpoint_bytes", "save_state", "load_state", "run_substeps", "kernel_launches", "set_profiling",
@@ -120,6 +120,9 @@ def _declare(L):
         g("run_driver_substeps").argtypes = [vp, C.c_int, ct, C.c_int, C.c_int, C.POINTER(AnalyticGeometry), sz, C.c_int,
                                              ct, ct, ct, C.c_int, C.c_int, C.POINTER(DriverStats)]
         g("set_driver_geometry_frozen").argtypes = [vp, C.c_int]
+        g("set_query_bounds").argtypes = [vp, vp, sz]
+        g("clear_query_bounds").argtypes = [vp]
+        g("snapshot_d2h_bytes").argtypes = [vp, C.POINTER(C.c_uint64)]
         g("reallocate_external_bodies").argtypes = [vp, sz]
         g("external_body_force_to_host").argtypes = [vp, vp, vp]
         g("dump_cpu_state").argtypes = [vp, vp, vp]

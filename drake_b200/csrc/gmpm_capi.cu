@@ -163,6 +163,15 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
   int gmpm_sync_particle_state_to_cpu_async_##SUF(gmpm_state_##SUF* s) {                                       \
     return guarded([&] { s->st.positions_async(); });                                                          \
   }                                                                                                            \
+  int gmpm_set_query_bounds_##SUF(gmpm_state_##SUF* s, const T* lo_hi, size_t n) {                             \
+    return guarded([&] { s->st.set_query_bounds(lo_hi, n); });                                                 \
+  }                                                                                                            \
+  int gmpm_clear_query_bounds_##SUF(gmpm_state_##SUF* s) {                                                     \
+    return guarded([&] { s->st.clear_query_bounds(); });                                                       \
+  }                                                                                                            \
+  int gmpm_snapshot_d2h_bytes_##SUF(gmpm_state_##SUF* s, uint64_t* bytes) {                                    \
+    return guarded([&] { if (bytes) *bytes = s->st.snapshot_d2h_bytes; });                                     \
+  }                                                                                                            \
   int gmpm_positions_host_##SUF(gmpm_state_##SUF* s, const T** out) {                                          \
     return guarded([&] {                                                                                       \
       if (!out) throw std::invalid_argument("null out pointer");                                               \

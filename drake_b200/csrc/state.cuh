@@ -68,6 +68,49 @@ struct Profiler {
 enum class GridStage { kClean, kTiles, kMomentum, kVelocity };
 template <typename T> struct ContactScalars;  // contact.cuh
 
+// SyncParticleStateToCpu with declared query bounds (gmpm_set_query_bounds): positions in the reference's layout and
+// visible order go to pos_stage as always (device-side consumers), and the particles inside at least one of the
+// axis-aligned boxes are appended -- visible index + position -- to the candidate list that crosses PCIe.
+constexpr int kMaxQueryBounds = 64;
+template <typename T>
+struct QueryBounds {
+  T lo[kMaxQueryBounds][3], hi[kMaxQueryBounds][3];
+  int n;
+};
+template <typename T>
+__global__ void cull_positions_kernel(uint32_t N, const T* __restrict__ src, const int* __restrict__ pid_of_vis,
+                                      const int* __restrict__ slot_of_pid, T* __restrict__ pos_stage,
+                                      const QueryBounds<T>* __restrict__ qb, uint32_t* __restrict__ count,
+                                      uint32_t* __restrict__ cand_idx, T* __restrict__ cand_pos) {
+  const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+  bool hit = false;
+  T x[3] = {T(0), T(0), T(0)};
+  if (v < N) {
+    const int s = slot_of_pid[pid_of_vis[v]];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      x[c] = src[(size_t)c * N + s];
+      pos_stage[(size_t)v * 3 + c] = x[c];
+    }
+    const int n = qb->n;
+    for (int b = 0; b < n && !hit; ++b)
+      hit = x[0] >= qb->lo[b][0] && x[0] <= qb->hi[b][0] && x[1] >= qb->lo[b][1] && x[1] <= qb->hi[b][1] &&
+            x[2] >= qb->lo[b][2] && x[2] <= qb->hi[b][2];
+  }
+  const uint32_t m = __ballot_sync(0xFFFFFFFFu, hit);
+  if (!m) return;
+  const int lane = threadIdx.x & 31;
+  uint32_t base = 0;
+  if (lane == __ffs(m) - 1) base = atomicAdd(count, (uint32_t)__popc(m));
+  base = __shfl_sync(0xFFFFFFFFu, base, __ffs(m) - 1);
+  if (hit) {
+    const uint32_t o = base + __popc(m & ((1u << lane) - 1u));
+    cand_idx[o] = v;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) cand_pos[(size_t)o * 3 + c] = x[c];
+  }
+}
+
 template <typename T>
 struct State {
   gmpm_params prm{};
@@ -148,6 +191,18 @@ struct State {
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_gather = nullptr, ev_copy = nullptr;
   bool copy_pending = false;
+  // culled snapshot (gmpm_set_query_bounds)
+  bool cull_on = false, cull_pending = false;
+  QueryBounds<T>* d_qb = nullptr;
+  uint32_t* cand_count = nullptr;   // device
+  uint32_t* cand_idx = nullptr;
+  T* cand_pos = nullptr;
+  uint32_t* h_cand_count = nullptr; // pinned
+  uint32_t* h_cand_idx = nullptr;
+  T* h_cand_pos = nullptr;
+  std::vector<uint32_t> h_prev_idx; // mirror entries that currently hold a real position
+  cudaEvent_t ev_count = nullptr;
+  uint64_t snapshot_d2h_bytes = 0;  // bytes the last snapshot moved to the host (instrumentation)
   bool driver_geometry_frozen = false;  // run_driver_substeps: keep the rigid poses for all substeps (reference driver)
   bool snapshot_valid = false;  // pos_stage holds the positions of the current substep (cleared by g2p)
   // device-side contact generation (contact_gen.cuh)
@@ -297,6 +352,15 @@ struct State {
     }
     if (h_pos_mirror) cudaFreeHost(h_pos_mirror);
     h_pos_mirror = nullptr;
+    if (h_cand_count) cudaFreeHost(h_cand_count);
+    if (h_cand_idx) cudaFreeHost(h_cand_idx);
+    if (h_cand_pos) cudaFreeHost(h_cand_pos);
+    h_cand_count = h_cand_idx = nullptr;
+    h_cand_pos = nullptr;
+    d_qb = nullptr;  // device buffers are released with the allocation list
+    cull_on = cull_pending = false;
+    if (ev_count) cudaEventDestroy(ev_count);
+    ev_count = nullptr;
     if (ev_gather) cudaEventDestroy(ev_gather);
     if (ev_copy) cudaEventDestroy(ev_copy);
     ev_gather = ev_copy = nullptr;
@@ -1143,14 +1207,77 @@ struct State {
     GMPM_CUDA(cudaGetLastError());
     snapshot_valid = true;
   }
+  void ensure_copy_stream() {
+    if (copy_stream) return;
+    GMPM_CUDA(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
+    GMPM_CUDA(cudaEventCreateWithFlags(&ev_gather, cudaEventDisableTiming));
+    GMPM_CUDA(cudaEventCreateWithFlags(&ev_copy, cudaEventDisableTiming));
+    GMPM_CUDA(cudaEventCreateWithFlags(&ev_count, cudaEventDisableTiming));
+    GMPM_CUDA(cudaHostAlloc((void**)&h_pos_mirror, sizeof(T) * 3 * N, cudaHostAllocDefault));
+  }
+  static constexpr double kFarAway = 1e30;  // positions_host() of a particle outside every declared query bound
+  // Declares the bounds of the rigid geometry the host contact query tests against (n axis-aligned boxes, lo/hi
+  // interleaved: 6 scalars each, inflated by the caller as it sees fit).  From now on the snapshot moves only the
+  // particles inside one of them to the host; positions_host() of every other particle reads kFarAway, for which any
+  // signed-distance query is positive, so the host loop (deformable_driver.h:138-190) builds the pairs it would have
+  // built from the full snapshot.  n = 0: nothing but a count crosses PCIe.
+  void set_query_bounds(const T* lo_hi, size_t n) {
+    require_finalized();
+    if (n > (size_t)kMaxQueryBounds) throw std::invalid_argument("set_query_bounds: at most 64 boxes");
+    if (n && !lo_hi) throw std::invalid_argument("set_query_bounds: null bounds");
+    if (N == 0) return;
+    ensure_copy_stream();
+    wait_positions();
+    if (!d_qb) {
+      d_qb = dalloc<QueryBounds<T>>(1);
+      cand_count = dalloc<uint32_t>(1);
+      cand_idx = dalloc<uint32_t>(N, false);
+      cand_pos = dalloc<T>(3 * N, false);
+      GMPM_CUDA(cudaHostAlloc((void**)&h_cand_count, sizeof(uint32_t), cudaHostAllocDefault));
+      GMPM_CUDA(cudaHostAlloc((void**)&h_cand_idx, sizeof(uint32_t) * N, cudaHostAllocDefault));
+      GMPM_CUDA(cudaHostAlloc((void**)&h_cand_pos, sizeof(T) * 3 * N, cudaHostAllocDefault));
+    }
+    QueryBounds<T> h{};
+    h.n = (int)n;
+    for (size_t b = 0; b < n; ++b)
+      for (int c = 0; c < 3; ++c) {
+        h.lo[b][c] = lo_hi[b * 6 + c];
+        h.hi[b][c] = lo_hi[b * 6 + 3 + c];
+      }
+    GMPM_CUDA(cudaMemcpyAsync(d_qb, &h, sizeof(h), cudaMemcpyHostToDevice, stream));
+    GMPM_CUDA(cudaStreamSynchronize(stream));  // h is a stack object
+    if (!cull_on) {
+      for (size_t i = 0; i < 3 * N; ++i) h_pos_mirror[i] = T(kFarAway);
+      h_prev_idx.clear();
+    }
+    cull_on = true;
+  }
+  void clear_query_bounds() {
+    if (cull_on) wait_positions();
+    cull_on = false;
+  }
   void positions_async() {
     require_finalized();
     if (N == 0) return;
-    if (!copy_stream) {
-      GMPM_CUDA(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
-      GMPM_CUDA(cudaEventCreateWithFlags(&ev_gather, cudaEventDisableTiming));
-      GMPM_CUDA(cudaEventCreateWithFlags(&ev_copy, cudaEventDisableTiming));
-      GMPM_CUDA(cudaHostAlloc((void**)&h_pos_mirror, sizeof(T) * 3 * N, cudaHostAllocDefault));
+    ensure_copy_stream();
+    if (cull_on) {
+      if (cull_pending) wait_positions();  // the previous candidate list was never consumed
+      if (!pos_stage) pos_stage = dalloc<T>(3 * N, false);
+      if (copy_pending) GMPM_CUDA(cudaStreamWaitEvent(stream, ev_copy, 0));
+      GMPM_CUDA(cudaMemsetAsync(cand_count, 0, sizeof(uint32_t), stream));
+      launch("cull_positions");
+      cull_positions_kernel<T><<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, pos[cur], pid_of_vis[vis_cur], slot_of_pid,
+                                                                      pos_stage, d_qb, cand_count, cand_idx, cand_pos);
+      GMPM_CUDA(cudaGetLastError());
+      GMPM_CUDA(cudaEventRecord(ev_gather, stream));
+      GMPM_CUDA(cudaStreamWaitEvent(copy_stream, ev_gather, 0));
+      GMPM_CUDA(cudaMemcpyAsync(h_cand_count, cand_count, sizeof(uint32_t), cudaMemcpyDeviceToHost, copy_stream));
+      GMPM_CUDA(cudaEventRecord(ev_count, copy_stream));
+      GMPM_CUDA(cudaEventRecord(ev_copy, copy_stream));
+      copy_pending = true;
+      cull_pending = true;
+      snapshot_valid = true;
+      return;
     }
     snapshot_positions_device();
     GMPM_CUDA(cudaEventRecord(ev_gather, stream));
@@ -1159,10 +1286,35 @@ struct State {
     GMPM_CUDA(cudaEventRecord(ev_copy, copy_stream));
     copy_pending = true;
     snapshot_valid = true;
+    snapshot_d2h_bytes = sizeof(T) * 3 * N;
   }
   // Blocks until the last positions_async() copy has landed; returns the pinned mirror (3N, visible order).
   const T* wait_positions() {
     require_finalized();
+    if (cull_pending) {
+      // the count is long there (the driver asks four solver calls later): fetch exactly that many candidates
+      GMPM_CUDA(cudaEventSynchronize(ev_count));
+      const uint32_t n = *h_cand_count;
+      if (n) {
+        GMPM_CUDA(cudaMemcpyAsync(h_cand_idx, cand_idx, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, copy_stream));
+        GMPM_CUDA(cudaMemcpyAsync(h_cand_pos, cand_pos, sizeof(T) * 3 * n, cudaMemcpyDeviceToHost, copy_stream));
+      }
+      GMPM_CUDA(cudaEventRecord(ev_copy, copy_stream));
+      GMPM_CUDA(cudaEventSynchronize(ev_copy));
+      for (uint32_t i : h_prev_idx)
+        h_pos_mirror[3 * (size_t)i] = h_pos_mirror[3 * (size_t)i + 1] = h_pos_mirror[3 * (size_t)i + 2] = T(kFarAway);
+      h_prev_idx.assign(h_cand_idx, h_cand_idx + n);
+      for (uint32_t j = 0; j < n; ++j) {
+        const size_t i = h_cand_idx[j];
+        h_pos_mirror[3 * i] = h_cand_pos[3 * (size_t)j];
+        h_pos_mirror[3 * i + 1] = h_cand_pos[3 * (size_t)j + 1];
+        h_pos_mirror[3 * i + 2] = h_cand_pos[3 * (size_t)j + 2];
+      }
+      snapshot_d2h_bytes = sizeof(uint32_t) + (uint64_t)n * (sizeof(uint32_t) + 3 * sizeof(T));
+      cull_pending = false;
+      copy_pending = false;
+      return h_pos_mirror;
+    }
     if (copy_pending) {
       GMPM_CUDA(cudaEventSynchronize(ev_copy));
       copy_pending = false;

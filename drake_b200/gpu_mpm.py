@@ -269,6 +269,21 @@ class GpuMpmState:
             self._positions_pending = False
         return self._positions_host
 
+    def SetContactQueryBounds(self, boxes):
+        """Extension: axis-aligned bounds [(lo, hi), ...] of the rigid geometry the host contact query tests against.
+        The async snapshot then moves only the particles inside one of them to the host; positions_host() of the
+        others reads 1e30.  `None` restores the full copy."""
+        if boxes is None:
+            check(self._f("clear_query_bounds")(self._h))
+            return
+        arr = np.ascontiguousarray([list(lo) + list(hi) for lo, hi in boxes], self.dtype).reshape(-1, 6)
+        check(self._f("set_query_bounds")(self._h, _ptr(arr) if arr.size else None, arr.shape[0]))
+
+    def snapshot_d2h_bytes(self):
+        n = C.c_uint64()
+        check(self._f("snapshot_d2h_bytes")(self._h, C.byref(n)))
+        return n.value
+
     def external_forces_host(self):
         return self._external_forces_host
 

@@ -129,6 +129,16 @@ int gmpm_device_sync(void);
   /* on a copy stream into a library-owned PINNED mirror while later solver calls run (the driver   */\
   /* reads positions_host() only when it builds the contact pairs, deformable_driver.h:243 vs :247).*/\
   int gmpm_sync_particle_state_to_cpu_async_##SUF(gmpm_state_##SUF* s);                             \
+  /* Extension: declares the axis-aligned bounds of the rigid geometry the host   */\
+  /* contact query (deformable_driver.h:120-194) tests against: n boxes, 6 scalars each (lo xyz, hi   */\
+  /* xyz), inflated by the caller as it sees fit.  While bounds are set the ASYNC snapshot moves only  */\
+  /* the particles inside one of them over PCIe; positions_host() of every other particle reads 1e30  */\
+  /* (any signed-distance query is positive there), so the host loop builds the same pairs as from    */\
+  /* the full snapshot.  n = 0: only a count crosses.  *d2h_bytes (may be null) of                     */\
+  /* gmpm_positions_host_info <- bytes the last snapshot moved.  clear restores the full copy.        */\
+  int gmpm_set_query_bounds_##SUF(gmpm_state_##SUF* s, const T* lo_hi, size_t n_boxes);             \
+  int gmpm_clear_query_bounds_##SUF(gmpm_state_##SUF* s);                                           \
+  int gmpm_snapshot_d2h_bytes_##SUF(gmpm_state_##SUF* s, uint64_t* bytes);                          \
   /* positions_host(): waits for the last async snapshot; *out = pinned mirror, 3N scalars, visible */\
   /* order, valid until the next snapshot or destroy (NULL before the first snapshot).              */\
   int gmpm_positions_host_##SUF(gmpm_state_##SUF* s, const T** out);                                \

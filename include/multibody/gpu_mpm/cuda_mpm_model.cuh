@@ -82,6 +82,8 @@ template <typename T> struct Abi;
     static constexpr auto generate_contact_pairs = gmpm_generate_contact_pairs_##SUF;                \
     static constexpr auto run_driver_substeps = gmpm_run_driver_substeps_##SUF;                      \
     static constexpr auto set_driver_geometry_frozen = gmpm_set_driver_geometry_frozen_##SUF;        \
+    static constexpr auto set_query_bounds = gmpm_set_query_bounds_##SUF;                            \
+    static constexpr auto clear_query_bounds = gmpm_clear_query_bounds_##SUF;                        \
     static constexpr auto reallocate_external_bodies = gmpm_reallocate_external_bodies_##SUF;        \
     static constexpr auto external_body_force_to_host = gmpm_external_body_force_to_host_##SUF;      \
     static constexpr auto dump_cpu_state = gmpm_dump_cpu_state_##SUF;                                \
@@ -160,6 +162,13 @@ struct GpuMpmState {
     internal::Check(Abi::dump_cpu_state(raw(), reinterpret_cast<T*>(pos.data()), tri.data()), "DumpCpuState");
     return std::make_tuple(std::move(pos), std::move(tri));
   }
+
+  // Extension: bounds (lo xyz, hi xyz per box) of the rigid geometry the host contact query tests against; the
+  // async snapshot then moves only the particles inside one of them over PCIe (see gmpm_set_query_bounds).
+  void SetContactQueryBounds(const std::vector<T>& lo_hi) {
+    internal::Check(Abi::set_query_bounds(raw(), lo_hi.data(), lo_hi.size() / 6), "SetContactQueryBounds");
+  }
+  void ClearContactQueryBounds() { internal::Check(Abi::clear_query_bounds(raw()), "ClearContactQueryBounds"); }
 
   // cuda_mpm_model.cu:320-345
   void ReallocateExternelBodies(size_t n) {

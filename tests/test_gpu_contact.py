@@ -411,3 +411,45 @@ def test_device_pairs_follow_a_resort_issued_after_the_snapshot():
         st.Destroy()
     assert np.array_equal(got[0][0], got[1][0])
     assert np.array_equal(got[0][1], got[1][1])
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_culled_snapshot_gives_the_host_query_the_same_pairs(dtype):
+    """gmpm_set_query_bounds: only the particles inside the declared bounds cross PCIe; positions_host() of the others
+    reads 1e30.  The host query (box_contacts, standing in for ComputeSignedDistanceToPoint) must build the same pairs
+    from the culled snapshot as from the full one, substep after substep (particles enter and leave the bounds)."""
+    st = GpuMpmState(dtype)
+    for pos, vel, tri in sheet_over_box(dtype):
+        st.AddQRCloth(pos, vel, tri)
+    st.Finalize()
+    sv = GpuMpmSolver()
+    N = st.n_particles()
+    pad = 0.004
+    st.SetContactQueryBounds([(BOX[0] - pad, BOX[1] + pad)])
+    seen = set()
+    for it in range(6):
+        sv.RebuildMapping(st, it == 3)
+        full = np.zeros((N, 3), dtype)
+        sv.SyncParticleStateToCpu(st, full)                  # blocking form: always the full snapshot
+        sv.SyncParticleStateToCpu(st)                        # async form: culled
+        ph = st.positions_host()
+        inside = np.all((full >= (BOX[0] - pad).astype(dtype)) & (full <= (BOX[1] + pad).astype(dtype)), axis=1)
+        assert 0 < inside.sum() < N
+        assert np.array_equal(ph[inside], full[inside])
+        assert np.all(ph[~inside] == dtype(1e30))
+        assert st.snapshot_d2h_bytes() == 4 + int(inside.sum()) * (4 + 3 * np.dtype(dtype).itemsize)
+        a = scenes.box_contacts(ph, *BOX, rigid_id=1)
+        b = scenes.box_contacts(full, *BOX, rigid_id=1)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)
+        seen.add(int(inside.sum()))
+        sv.CalcFemStateAndForce(st, DT); sv.ParticleToGrid(st, DT); sv.UpdateGrid(st, -1); sv.GridToParticle(st, DT)
+    assert len(seen) > 1                                     # the candidate set changed over the run
+    st.SetContactQueryBounds([])                             # no rigid geometry: nothing but the count crosses
+    sv.SyncParticleStateToCpu(st)
+    assert np.all(st.positions_host() == dtype(1e30)) and st.snapshot_d2h_bytes() == 4
+    st.SetContactQueryBounds(None)                           # back to the full copy
+    sv.SyncParticleStateToCpu(st)
+    assert np.array_equal(st.positions_host().reshape(-1), st.read("positions"))
+    assert st.snapshot_d2h_bytes() == 3 * N * np.dtype(dtype).itemsize
+    st.Destroy()
