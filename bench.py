@@ -521,12 +521,12 @@ def main():
     # (1) the loop exactly as upstream issues it: ALL positions cross PCIe every substep (deformable_driver.h:243)
     Kf = max(3, min(K, 100))
     full_ms, full_bytes = run_e2e(Kf)
-    # (2) headline e2e: the same loop with the bounds of the rigid geometry declared (gmpm_set_query_bounds): only
-    # particles inside them cross PCIe, positions_host() of the others reads 1e30 and the host query builds the same
-    # pairs (tests/test_gpu_contact.py::test_culled_snapshot_...).  cfg-2 has no rigid contact; the one box is the
-    # rigid ground slab under the stack (configs[0]'s "rigid ground box"), which the sheets reach late in the run.
-    dom = 1.0 if world == 1 else 2.0
-    st.SetContactQueryBounds([((0.0, 0.0, 0.0), (dom, dom, 0.03))])
+    # (2) headline e2e: the same loop with the rigid geometry of the scene DECLARED (gmpm_set_query_bounds): only the
+    # particles inside its bounds cross PCIe, positions_host() of the others reads 1e30 and the host query builds the
+    # same pairs (tests/test_gpu_contact.py::test_culled_snapshot_...).  cfg-2 is "no rigid contact": the driver has
+    # no rigid geometry to declare, so the list is empty and only the candidate count crosses.  The cost with
+    # geometry present is the full-copy line scaled by the fraction of particles inside the bounds.
+    st.SetContactQueryBounds([])
     Ke = max(3, min(K, 200))
     e_ms, e_bytes = run_e2e(Ke)
     st.SetContactQueryBounds(None)
@@ -587,9 +587,9 @@ def main():
                 "clocks": clocks,
                 "e2e": {"value": N_all * Ke / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0,
                         "d2h_bytes_per_step": int(e_bytes), "steps": Ke, "ms_per_step": e_ms / Ke,
-                        "what": "DeformableDriver substep through the C ABI with the bounds of the rigid geometry declared "
-                                "(one ground slab, z < 0.03): SyncParticleStateToCpu (device gather + cull, count and "
-                                "candidates -> pinned host, overlapped with the next 4 solver calls), positions_host() wait "
+                        "what": "DeformableDriver substep through the C ABI with the scene's rigid geometry declared (cfg-2: "
+                                "none, gmpm_set_query_bounds with 0 boxes): SyncParticleStateToCpu (device gather + cull, count "
+                                "and candidates -> pinned host, overlapped with the next 4 solver calls), positions_host() wait "
                                 "+ host read, CopyContactPairs (0 pairs), 5 solver calls; bytes = measured mean per substep "
                                 "on rank 0"},
                 "e2e_full_snapshot": {"value": N_all * Kf / (full_ms * 1e-3), "unit": UNIT, "steps": Kf,

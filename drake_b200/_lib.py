@@ -27,6 +27,15 @@ class AnalyticGeometry(C.Structure):
                 ("velocity", C.c_double * 3), ("p_WB", C.c_double * 3)]
 
 
+class Material(C.Structure):
+    """Mirror of gmpm_material (volumetric materials, extension)."""
+    _fields_ = [("model", C.c_int), ("reserved", C.c_int), ("youngs", C.c_double), ("poisson", C.c_double),
+                ("friction_angle_deg", C.c_double), ("cohesion", C.c_double)]
+
+
+MATERIAL_MODELS = {"fixed_corotated": 1, "stvk_hencky": 2, "drucker_prager": 3}
+
+
 class DriverStats(C.Structure):
     """Mirror of gmpm_driver_stats."""
     _fields_ = [("substeps", C.c_int), ("contact_queries", C.c_int), ("newton_iterations", C.c_int),
@@ -43,7 +52,7 @@ PLAIN_SYMBOLS = ["gmpm_default_params", "gmpm_last_error", "gmpm_version", "gmpm
                  "gmpm_morton_code", "gmpm_cell_index", "gmpm_inverse_cell_index", "gmpm_radix_sort_pairs"]
 TYPED_SYMBOLS = ["create", "destroy", "add_qr_cloth", "finalize", "rebuild_mapping", "calc_fem", "p2g",
                  "update_grid", "g2p", "sync", "sync_particle_state_to_cpu", "sync_particle_state_to_cpu_async",
-                 "positions_host", "set_query_bounds", "clear_query_bounds", "snapshot_d2h_bytes", "halo_flags", "halo_plan_async", "halo_pack", "halo_unpack", "halo_peer_init", "halo_peer_window", "halo_peer_attach", "halo_peer_send", "halo_peer_recv", "update_grid_part", "g2p_part", "stream", "halo_stream", "copy_contact_pairs",
+                 "positions_host", "set_query_bounds", "add_particles", "n_volumetric", "clear_query_bounds", "snapshot_d2h_bytes", "halo_flags", "halo_plan_async", "halo_pack", "halo_unpack", "halo_peer_init", "halo_peer_window", "halo_peer_attach", "halo_peer_send", "halo_peer_recv", "update_grid_part", "g2p_part", "stream", "halo_stream", "copy_contact_pairs",
                  "generate_contact_pairs", "run_driver_substeps", "set_driver_geometry_frozen", "update_contact", "reallocate_external_bodies", "external_body_force_to_host",
                  "dump_cpu_state", "n_verts", "n_faces", "n_particles", "n_cells", "num_contacts",
                  "grid_touched_cnt_host", "read", "checkpoint_bytes", "save_state", "load_state", "run_substeps", "kernel_launches", "set_profiling",
@@ -87,6 +96,9 @@ def _declare(L):
         g("create").argtypes = [C.POINTER(Params), C.POINTER(vp)]
         g("destroy").argtypes = [vp]
         g("add_qr_cloth").argtypes = [vp, vp, vp, sz, vp, sz]
+        g("add_particles").argtypes = [vp, vp, vp, vp, sz, C.POINTER(Material)]
+        g("n_volumetric").argtypes = [vp]
+        g("n_volumetric").restype = sz
         g("finalize").argtypes = [vp]
         g("rebuild_mapping").argtypes = [vp, C.c_int]
         g("calc_fem").argtypes = [vp, ct]

@@ -4,7 +4,7 @@
 // DumpCpuState returns vertex positions and indices only (cuda_mpm_model.cu:245-265) -- velocities, the
 // affine matrices and the deformation gradients are lost.  A checkpoint here is one host blob in the
 // REFERENCE's layout and visible particle order (so it does not depend on the physical order the library
-// happens to keep): header, positions[3N] velocities[3N] volumes[N] affine[9N] F[9F] Dm_inv[4F] pids[N].
+// happens to keep): header, positions[3N] velocities[3N] volumes[N] affine[9N] F[9F] Dm_inv[4F] particle_F[9Nv] pids[N].
 // Loading needs a finalized state built from the same meshes (same N, F, scalar); the run then continues
 // with the same arithmetic on a different physical order, i.e. equal to summation-order rounding.
 #pragma once
@@ -13,10 +13,10 @@
 namespace gmpm {
 
 struct CheckpointHeader {
-  char magic[8];          // "GMPMCKP1"
+  char magic[8];          // "GMPMCKP2"
   uint32_t scalar_bytes;  // 4 or 8
   uint32_t domain_bits;
-  uint64_t N, n_verts, n_faces;
+  uint64_t N, n_verts, n_faces, n_vol;
   double dx;
 };
 
@@ -45,7 +45,7 @@ __global__ void iota_kernel(uint32_t n, int* __restrict__ out) {
 
 template <typename T>
 size_t State<T>::checkpoint_bytes() const {
-  return sizeof(CheckpointHeader) + sizeof(T) * (16 * N + 13 * n_faces) + sizeof(int) * N;
+  return sizeof(CheckpointHeader) + sizeof(T) * (16 * N + 13 * n_faces + 9 * n_vol) + sizeof(int) * N;
 }
 
 template <typename T>
@@ -54,18 +54,19 @@ size_t State<T>::save_state(void* out, size_t cap) {
   const size_t total = checkpoint_bytes();
   if (!out || cap < total) throw std::invalid_argument("gmpm_save_state: buffer too small (see gmpm_checkpoint_bytes)");
   CheckpointHeader h{};
-  std::memcpy(h.magic, "GMPMCKP1", 8);
+  std::memcpy(h.magic, "GMPMCKP2", 8);
   h.scalar_bytes = sizeof(T);
   h.domain_bits = (uint32_t)k.domain_bits;
   h.N = N;
   h.n_verts = n_verts;
   h.n_faces = n_faces;
+  h.n_vol = n_vol;
   h.dx = (double)k.dx;
   char* p = static_cast<char*>(out);
   std::memcpy(p, &h, sizeof(h));
   p += sizeof(h);
   for (const char* name : {"positions", "velocities", "volumes", "affine_matrices", "deformation_gradients",
-                           "Dm_inverses", "pids"})
+                           "Dm_inverses", "particle_F", "pids"})
     p += read(name, p, cap - (size_t)(p - static_cast<char*>(out)));
   if ((size_t)(p - static_cast<char*>(out)) != total) throw std::runtime_error("gmpm_save_state: size mismatch");
   return total;
@@ -77,8 +78,8 @@ void State<T>::load_state(const void* in, size_t bytes) {
   if (!in || bytes < sizeof(CheckpointHeader)) throw std::invalid_argument("gmpm_load_state: not a checkpoint");
   CheckpointHeader h;
   std::memcpy(&h, in, sizeof(h));
-  if (std::memcmp(h.magic, "GMPMCKP1", 8) != 0) throw std::invalid_argument("gmpm_load_state: bad magic");
-  if (h.scalar_bytes != sizeof(T) || h.N != N || h.n_verts != n_verts || h.n_faces != n_faces ||
+  if (std::memcmp(h.magic, "GMPMCKP2", 8) != 0) throw std::invalid_argument("gmpm_load_state: bad magic");
+  if (h.scalar_bytes != sizeof(T) || h.N != N || h.n_verts != n_verts || h.n_faces != n_faces || h.n_vol != n_vol ||
       h.domain_bits != (uint32_t)k.domain_bits || bytes != checkpoint_bytes())
     throw std::invalid_argument("gmpm_load_state: the checkpoint was taken from a different scene (sizes, scalar or grid)");
   if (std::fabs(h.dx - (double)k.dx) > 1e-12 * std::fabs((double)k.dx))
@@ -89,7 +90,7 @@ void State<T>::load_state(const void* in, size_t bytes) {
   {
     // pids drive scattered device writes: they must be a permutation of 0..N-1 that keeps face particles (pid <
     // n_faces) distinguishable -- checked on the host, where the blob already is
-    const int* hp = reinterpret_cast<const int*>(p + sizeof(T) * (16 * N + 13 * n_faces));
+    const int* hp = reinterpret_cast<const int*>(p + sizeof(T) * (16 * N + 13 * n_faces + 9 * n_vol));
     std::vector<uint8_t> seen(N, 0);
     for (size_t v = 0; v < N; ++v) {
       int q;
@@ -109,7 +110,8 @@ void State<T>::load_state(const void* in, size_t bytes) {
   const T* s_C = s_vol + N;
   const T* s_F = s_C + 9 * N;
   const T* s_Dm = s_F + 9 * n_faces;
-  const int* s_pid = reinterpret_cast<const int*>(s_Dm + 4 * n_faces);  // ints last: every T array stays aligned
+  const T* s_Fv = s_Dm + 4 * n_faces;
+  const int* s_pid = reinterpret_cast<const int*>(s_Fv + 9 * n_vol);  // ints last: every T array stays aligned
   launch("restore_particles");
   scatter_particle_field_kernel<T><<<blocks_for(n), kThreads, 0, stream>>>(n, 3, s_pos, pos[cur]);
   scatter_particle_field_kernel<T><<<blocks_for(n), kThreads, 0, stream>>>(n, 3, s_vel, vel[cur]);
@@ -128,6 +130,8 @@ void State<T>::load_state(const void* in, size_t bytes) {
     scatter_particle_field_kernel<T><<<blocks_for(F), kThreads, 0, stream>>>(F, 4, s_Dm, Dm_inv);
     launches += 3;
   }
+  if (n_vol)  // deformation gradients of the volumetric particles: by particle id on both sides
+    GMPM_CUDA(cudaMemcpyAsync(Fv, s_Fv, sizeof(T) * 9 * n_vol, cudaMemcpyDeviceToDevice, stream));
   launches += 4;
   GMPM_CUDA(cudaGetLastError());
   GMPM_CUDA(cudaStreamSynchronize(stream));  // the host blob and ht are borrowed

@@ -82,11 +82,12 @@ size_t State<T>::read(const char* name, void* out, size_t cap) {
     T* buf = static_cast<T*>(io(bytes));
     launch("gather_taus");
     gather_taus_kernel<T><<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, (uint32_t)n_faces, taus,
-                                                                 pid_of_vis[vis_cur], slot_of_pid, buf);
+                                                                 pid_of_vis[vis_cur], slot_of_pid, buf, n_cloth());
     GMPM_CUDA(cudaGetLastError());
     to_host(out, buf, bytes);
     return bytes;
   }
+  if (n == "particle_F") return plain(Fv, sizeof(T) * 9 * n_vol);  // volumetric particles, by particle id (extension)
   if (n == "dev_counters") return plain(ctr, sizeof(DevCounters));  // instrumentation (tools/)
   if (n == "pids") return plain(pid_of_vis[vis_cur], sizeof(int) * N);
   if (n == "index_mappings") return plain(vis_of_pid, sizeof(int) * N);

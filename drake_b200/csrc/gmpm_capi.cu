@@ -148,6 +148,10 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
                               size_t nt) {                                                                     \
     return guarded([&] { s->st.add_qr_cloth(pos, vel, nv, tri, nt); });                                        \
   }                                                                                                            \
+  int gmpm_add_particles_##SUF(gmpm_state_##SUF* s, const T* pos, const T* vel, const T* volume, size_t n,     \
+                               const gmpm_material* mat) {                                                     \
+    return guarded([&] { s->st.add_particles(pos, vel, volume, n, mat); });                                    \
+  }                                                                                                            \
   int gmpm_finalize_##SUF(gmpm_state_##SUF* s) { return guarded([&] { s->st.finalize(); }); }                  \
   int gmpm_rebuild_mapping_##SUF(gmpm_state_##SUF* s, int sort) {                                              \
     return guarded([&] { s->st.rebuild_mapping(sort != 0); });                                                 \
@@ -217,6 +221,7 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
   size_t gmpm_n_verts_##SUF(const gmpm_state_##SUF* s) { return s->st.n_verts; }                               \
   size_t gmpm_n_faces_##SUF(const gmpm_state_##SUF* s) { return s->st.n_faces; }                               \
   size_t gmpm_n_particles_##SUF(const gmpm_state_##SUF* s) { return s->st.N; }                                 \
+  size_t gmpm_n_volumetric_##SUF(const gmpm_state_##SUF* s) { return s->st.n_vol; }                            \
   size_t gmpm_n_cells_##SUF(const gmpm_state_##SUF* s) { return s->st.k.n_cells; }                             \
   size_t gmpm_num_contacts_##SUF(const gmpm_state_##SUF* s) { return s->st.n_contacts; }                       \
   int gmpm_grid_touched_cnt_host_##SUF(gmpm_state_##SUF* s, uint32_t* out) {                                   \

@@ -527,17 +527,20 @@ struct alignas(16) Vec4 {
 template <typename T>
 struct P2GRaw {
   T p[3], v[3], vol, C[9], ex[6];
-  bool face;
+  bool face;  // carries a stress (taus): a cloth face (rank-one, two factors) or a volumetric particle (symmetric 3x3)
+  bool solid; // volumetric particle (pid >= n_cloth): ex = V0 tau (xx, yy, zz, xy, xz, yz)
 };
 
 template <typename T>
-__device__ __forceinline__ void p2g_load(P2GRaw<T>& r, bool valid, uint32_t s, uint32_t N, uint32_t n_faces,
+__device__ __forceinline__ void p2g_load(P2GRaw<T>& r, bool valid, uint32_t s, uint32_t N, uint2 n_faces_cloth,
                                          const T* __restrict__ pos, const T* __restrict__ vel,
                                          const T* __restrict__ vol, const T* __restrict__ C,
                                          const int* __restrict__ pid, const T* __restrict__ forces,
                                          const T* __restrict__ taus) {
   if (!valid) return;
-  r.face = (uint32_t)pid[s] < n_faces;
+  const uint32_t p_id = (uint32_t)pid[s];
+  r.solid = p_id >= n_faces_cloth.y;          // [faces | verts | volumetric particles]
+  r.face = p_id < n_faces_cloth.x || r.solid;
 #pragma unroll
   for (int d = 0; d < 3; ++d) {
     r.p[d] = pos[(size_t)d * N + s];
@@ -581,7 +584,13 @@ __device__ __forceinline__ uint32_t p2g_derive(const P2GRaw<T>& r, T* row, T dt,
 #pragma unroll
   for (int d = 0; d < 3; ++d)
     if (d == k.gravity_axis) a[d] += mass * k.gravity * dt;
-  if (r.face) {
+  if (r.solid) {
+    const T cs = -dt * k.d_inv;
+    B[0] += cs * r.ex[0]; B[4] += cs * r.ex[1]; B[8] += cs * r.ex[2];
+    B[1] += cs * r.ex[3]; B[3] += cs * r.ex[3];
+    B[2] += cs * r.ex[4]; B[6] += cs * r.ex[4];
+    B[5] += cs * r.ex[5]; B[7] += cs * r.ex[5];
+  } else if (r.face) {
     const T cs = -dt * k.d_inv;
 #pragma unroll
     for (int i = 0; i < 3; ++i)
@@ -627,7 +636,7 @@ __device__ __forceinline__ uint32_t p2g_derive(const P2GRaw<T>& r, T* row, T dt,
 
 template <typename T>
 __global__ void __launch_bounds__(kP2GThreads)
-p2g_tile_kernel(uint32_t N, uint32_t n_faces, const uint32_t* __restrict__ order,
+p2g_tile_kernel(uint32_t N, uint2 n_faces, const uint32_t* __restrict__ order,
                 const uint32_t* __restrict__ sorted_key, const WorkRec* __restrict__ pb_work, uint32_t work_cap,
                 const T* __restrict__ pos, const T* __restrict__ vel, const T* __restrict__ vol,
                 const T* __restrict__ C, const int* __restrict__ pid, const T* __restrict__ forces,
@@ -1064,7 +1073,7 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __rest
            const int* __restrict__ pid, T* __restrict__ pos_out, T* __restrict__ vel_out, T* __restrict__ C_out,
            T* __restrict__ vol_out, int* __restrict__ pid_out, int* __restrict__ slot_of_pid,
            uint32_t* __restrict__ key_out, T* __restrict__ forces_out, DevCounters* ctr, T dt, Consts<T> k,
-           const uint8_t* __restrict__ mark = nullptr, int want = -1) {
+           const uint8_t* __restrict__ mark = nullptr, int want = -1, uint32_t n_cloth = 0xFFFFFFFFu) {
   // mark / want (multi-GPU): want = 0 -> only chunks whose stencils stay clear of the blocks exchanged with
   // other ranks (they can run while the exchange is in flight), want = 1 -> only the others, -1 -> all.
   __shared__ T s_vel[kG2PWarps][2][3][kTileNodes];
@@ -1226,7 +1235,9 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __rest
       for (int a = 0; a < 3; ++a)
 #pragma unroll
         for (int c = 0; c < 3; ++c)
-          C_out[(size_t)(a * 3 + c) * N + i] = ca * (scale * S[a * 3 + c]) + cb * (scale * S[c * 3 + a]);
+          // cloth: the reference's blended affine matrix (:905-915); volumetric particles keep grad v itself
+          C_out[(size_t)(a * 3 + c) * N + i] = (uint32_t)p >= n_cloth ? scale * S[a * 3 + c]
+                                                                      : ca * (scale * S[a * 3 + c]) + cb * (scale * S[c * 3 + a]);
 #pragma unroll
       for (int d = 0; d < 3; ++d) {
         x[d] += nv[d] * dt;
@@ -1273,11 +1284,21 @@ __global__ void gather_particle_field_kernel(uint32_t N, int comps, const T* __r
 template <typename T>
 __global__ void gather_taus_kernel(uint32_t N, uint32_t n_faces, const T* __restrict__ taus,
                                    const int* __restrict__ pid_of_vis, const int* __restrict__ slot_of_pid,
-                                   T* __restrict__ out) {
+                                   T* __restrict__ out, uint32_t n_cloth = 0xFFFFFFFFu) {
   const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= N) return;
   const int p = pid_of_vis[v];
   const int s = slot_of_pid[p];
+  if ((uint32_t)p >= n_cloth) {  // volumetric particle: symmetric V0 tau stored as (xx, yy, zz, xy, xz, yz)
+    const T t[6] = {taus[s], taus[(size_t)N + s], taus[(size_t)2 * N + s], taus[(size_t)3 * N + s],
+                    taus[(size_t)4 * N + s], taus[(size_t)5 * N + s]};
+    T* o = out + (size_t)v * 9;
+    o[0] = t[0]; o[4] = t[1]; o[8] = t[2];
+    o[1] = o[3] = t[3];
+    o[2] = o[6] = t[4];
+    o[5] = o[7] = t[5];
+    return;
+  }
   const bool face = (uint32_t)p < n_faces;
   for (int a = 0; a < 3; ++a)
     for (int b = 0; b < 3; ++b)

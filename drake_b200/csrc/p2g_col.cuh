@@ -107,7 +107,13 @@ __device__ __forceinline__ uint32_t p2g_derive_col(const P2GRaw<T>& r, unsigned 
 #pragma unroll
   for (int d = 0; d < 3; ++d)
     if (d == k.gravity_axis) a[d] += mass * k.gravity * dt;
-  if (r.face) {
+  if (r.solid) {
+    const T cs = -dt * k.d_inv;
+    B[0] += cs * r.ex[0]; B[4] += cs * r.ex[1]; B[8] += cs * r.ex[2];
+    B[1] += cs * r.ex[3]; B[3] += cs * r.ex[3];
+    B[2] += cs * r.ex[4]; B[6] += cs * r.ex[4];
+    B[5] += cs * r.ex[5]; B[7] += cs * r.ex[5];
+  } else if (r.face) {
     const T cs = -dt * k.d_inv;
 #pragma unroll
     for (int i = 0; i < 3; ++i)
@@ -145,7 +151,7 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 
 template <typename T, bool BULK>
 __global__ void __launch_bounds__(kP2GThreads)
-p2g_col_kernel(uint32_t N, uint32_t n_faces, const uint32_t* __restrict__ order,
+p2g_col_kernel(uint32_t N, uint2 n_faces, const uint32_t* __restrict__ order,
                const uint32_t* __restrict__ sorted_key, const WorkRec* __restrict__ pb_work, uint32_t work_cap,
                const T* __restrict__ pos, const T* __restrict__ vel, const T* __restrict__ vol,
                const T* __restrict__ C, const int* __restrict__ pid, const T* __restrict__ forces,

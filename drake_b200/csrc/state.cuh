@@ -13,6 +13,7 @@
 #include "halo.cuh"
 #include "kernels.cuh"
 #include "p2g_col.cuh"
+#include "volumetric.cuh"
 #include "sort.cuh"
 
 namespace gmpm {
@@ -123,6 +124,15 @@ struct State {
   std::vector<T> h_pos, h_vel;
   std::vector<int> h_tri;
   size_t n_verts = 0, n_faces = 0, N = 0;
+  // volumetric particles (gmpm_add_particles; pids [n_faces + n_verts, N)), SURVEY 8f-4
+  size_t n_vol = 0;
+  std::vector<T> h_vpos, h_vvel, h_vvol;
+  std::vector<uint8_t> h_vmat;
+  std::vector<gmpm_material> materials;
+  T* Fv = nullptr;            // [n_vol][9] row-major, by volumetric particle id
+  uint8_t* mat_id = nullptr;  // [n_vol]
+  MaterialTable<T> mat_table{};
+  uint32_t n_cloth() const { return (uint32_t)(n_faces + n_verts); }
 
   // particles (physical slots), double buffered
   T *pos[2]{}, *vel[2]{}, *C[2]{}, *vol[2]{};
@@ -202,6 +212,7 @@ struct State {
   T* h_cand_pos = nullptr;
   std::vector<uint32_t> h_prev_idx; // mirror entries that currently hold a real position
   cudaEvent_t ev_count = nullptr;
+  uint32_t cand_last = 0, cand_fetched = 0;  // candidates of the last snapshot / fetched speculatively this time
   uint64_t snapshot_d2h_bytes = 0;  // bytes the last snapshot moved to the host (instrumentation)
   bool driver_geometry_frozen = false;  // run_driver_substeps: keep the rigid poses for all substeps (reference driver)
   bool snapshot_valid = false;  // pos_stage holds the positions of the current substep (cleared by g2p)
@@ -393,6 +404,31 @@ struct State {
     N += nv + nt;
   }
 
+  // Extension: particles that carry their own deformation gradient (F = I at setup) and one of the
+  // volumetric materials of volumetric.cuh.  `volume` is the rest volume per particle; the mass is volume * density.
+  void add_particles(const T* p, const T* v, const T* volume, size_t n, const gmpm_material* mat) {
+    if (finalized) throw std::invalid_argument("AddParticles after Finalize");
+    if (!mat) throw std::invalid_argument("AddParticles: null material");
+    if (mat->model < GMPM_MAT_FIXED_COROTATED || mat->model > GMPM_MAT_DRUCKER_PRAGER)
+      throw std::invalid_argument("AddParticles: unknown material model");
+    if (!(mat->youngs > 0) || !(mat->poisson > -1 && mat->poisson < 0.5))
+      throw std::invalid_argument("AddParticles: need youngs > 0 and -1 < poisson < 0.5");
+    if (n && (!p || !v || !volume)) throw std::invalid_argument("AddParticles: null array");
+    size_t m = 0;
+    for (; m < materials.size(); ++m)
+      if (!std::memcmp(&materials[m], mat, sizeof(gmpm_material))) break;
+    if (m == materials.size()) {
+      if (m >= (size_t)kMaxMaterials) throw std::invalid_argument("AddParticles: at most 16 distinct materials");
+      materials.push_back(*mat);
+    }
+    h_vpos.insert(h_vpos.end(), p, p + n * 3);
+    h_vvel.insert(h_vvel.end(), v, v + n * 3);
+    h_vvol.insert(h_vvol.end(), volume, volume + n);
+    h_vmat.insert(h_vmat.end(), n, (uint8_t)m);
+    n_vol += n;
+    N += n;
+  }
+
   // cuda_mpm_model.cu:36-122: every device allocation happens here.
   void finalize() {
     if (finalized) throw std::invalid_argument("Finalize called twice");
@@ -456,6 +492,36 @@ struct State {
         hp[d * N + F + v] = h_pos[v * 3 + d];
         hv[d * N + F + v] = h_vel[v * 3 + d];
       }
+    std::vector<T> hvol;
+    if (n_vol) {  // [faces | verts | volumetric]
+      const size_t B0 = F + V;
+      hvol.assign(N, T(0));
+      for (size_t q = 0; q < n_vol; ++q) {
+        for (int d = 0; d < 3; ++d) {
+          hp[d * N + B0 + q] = h_vpos[q * 3 + d];
+          hv[d * N + B0 + q] = h_vvel[q * 3 + d];
+        }
+        hvol[B0 + q] = h_vvol[q];
+      }
+      Fv = dalloc<T>(9 * n_vol, false);
+      mat_id = dalloc<uint8_t>(n_vol, false);
+      std::vector<T> hF(9 * n_vol, T(0));
+      for (size_t q = 0; q < n_vol; ++q) hF[q * 9] = hF[q * 9 + 4] = hF[q * 9 + 8] = T(1);
+      GMPM_CUDA(cudaMemcpyAsync(Fv, hF.data(), sizeof(T) * 9 * n_vol, cudaMemcpyHostToDevice, stream));
+      GMPM_CUDA(cudaMemcpyAsync(mat_id, h_vmat.data(), n_vol, cudaMemcpyHostToDevice, stream));
+      GMPM_CUDA(cudaMemcpyAsync(vol[0], hvol.data(), sizeof(T) * N, cudaMemcpyHostToDevice, stream));
+      GMPM_CUDA(cudaStreamSynchronize(stream));  // hF goes out of scope
+      for (size_t m = 0; m < materials.size(); ++m) {
+        const gmpm_material& g = materials[m];
+        MaterialDev<T>& d = mat_table.m[m];
+        d.model = g.model;
+        d.mu = (T)(g.youngs / (2.0 * (1.0 + g.poisson)));
+        d.lambda = (T)(g.youngs * g.poisson / ((1.0 + g.poisson) * (1.0 - 2.0 * g.poisson)));
+        const double sphi = std::sin(g.friction_angle_deg * 3.14159265358979323846 / 180.0);
+        d.alpha = (T)(std::sqrt(2.0 / 3.0) * 2.0 * sphi / (3.0 - sphi));
+        d.cohesion = (T)g.cohesion;
+      }
+    }
     std::vector<int> ht(3 * F), iota(N);
     for (size_t f = 0; f < F; ++f)
       for (int c = 0; c < 3; ++c) ht[c * F + f] = h_tri[f * 3 + c] + (int)F;
@@ -644,6 +710,12 @@ struct State {
       GMPM_CUDA(cudaGetLastError());
       bin_valid = false;  // face particles moved to their centroids
     }
+    if (n_vol) {
+      launch("volumetric_stress");
+      volumetric_stress_kernel<T><<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, n_cloth(), pid[cur], C[cur], vol[cur], Fv,
+                                                                         mat_id, mat_table, taus, dt);
+      GMPM_CUDA(cudaGetLastError());
+    }
     fem_valid = true;
   }
 
@@ -664,7 +736,7 @@ struct State {
     halo_nbr_zeroed_epoch = halo_nbr ? p2g_epoch : 0;  // the tile kernel zeroes the entries it appends
     launch("p2g_tile");
 #define GMPM_P2G_ARGS                                                                                            \
-  (uint32_t) N, (uint32_t)n_faces, order(), sorted_keys(), pb_work, (uint32_t)work_cap, pos[cur], vel[cur], vol[cur], \
+  (uint32_t) N, make_uint2((uint32_t)n_faces, n_cloth()), order(), sorted_keys(), pb_work, (uint32_t)work_cap, pos[cur], vel[cur], vol[cur], \
       C[cur], pid[cur], forces, taus, tiles, touched_epoch, touched_list[tl_cur], p2g_epoch, ctr, dt, k, halo_nbr
     if (p2g_variant == 0)
       p2g_tile_kernel<T><<<persistent_ctas(p2g_ctas_per_sm), kP2GThreads, p2g_smem, stream>>>(GMPM_P2G_ARGS);
@@ -731,7 +803,7 @@ struct State {
     const int nx = cur ^ 1;
     g2p_kernel<T><<<persistent_ctas(g2p_ctas_per_sm), kG2PWarps * 32, 0, stream>>>(
         (uint32_t)N, order(), pb_work, (uint32_t)work_cap, g_vel, pos[cur], vol[cur], pid[cur], pos[nx], vel[nx], C[nx],
-        vol[nx], pid[nx], slot_of_pid, key, forces, ctr, dt, k);
+        vol[nx], pid[nx], slot_of_pid, key, forces, ctr, dt, k, nullptr, -1, n_cloth());
     GMPM_CUDA(cudaGetLastError());
     halo_clear_marks();  // an exchange whose parts were started but finished with the plain calls
     forces_zero = true;
@@ -784,7 +856,7 @@ struct State {
     const int nx = cur ^ 1;
     g2p_kernel<T><<<persistent_ctas(g2p_ctas_per_sm), kG2PWarps * 32, 0, stream>>>(
         (uint32_t)N, order(), pb_work, (uint32_t)work_cap, g_vel, pos[cur], vol[cur], pid[cur], pos[nx], vel[nx], C[nx],
-        vol[nx], pid[nx], slot_of_pid, key, forces, ctr, dt, k, halo_mark, part);
+        vol[nx], pid[nx], slot_of_pid, key, forces, ctr, dt, k, halo_mark, part, n_cloth());
     GMPM_CUDA(cudaGetLastError());
     if (part == 1) {
       halo_clear_marks();  // the marks of this exchange are spent
@@ -1273,6 +1345,14 @@ struct State {
       GMPM_CUDA(cudaStreamWaitEvent(copy_stream, ev_gather, 0));
       GMPM_CUDA(cudaMemcpyAsync(h_cand_count, cand_count, sizeof(uint32_t), cudaMemcpyDeviceToHost, copy_stream));
       GMPM_CUDA(cudaEventRecord(ev_count, copy_stream));
+      // speculative fetch: the candidate set changes slowly, so as many candidates as last time (+ 1/8) are copied
+      // right away, under the solver calls that follow; wait_positions() fetches the remainder, if any
+      cand_fetched = (uint32_t)std::min<size_t>(N, (size_t)cand_last + cand_last / 8 + 64);
+      if (cand_last == 0) cand_fetched = 0;
+      if (cand_fetched) {
+        GMPM_CUDA(cudaMemcpyAsync(h_cand_idx, cand_idx, sizeof(uint32_t) * cand_fetched, cudaMemcpyDeviceToHost, copy_stream));
+        GMPM_CUDA(cudaMemcpyAsync(h_cand_pos, cand_pos, sizeof(T) * 3 * cand_fetched, cudaMemcpyDeviceToHost, copy_stream));
+      }
       GMPM_CUDA(cudaEventRecord(ev_copy, copy_stream));
       copy_pending = true;
       cull_pending = true;
@@ -1295,12 +1375,15 @@ struct State {
       // the count is long there (the driver asks four solver calls later): fetch exactly that many candidates
       GMPM_CUDA(cudaEventSynchronize(ev_count));
       const uint32_t n = *h_cand_count;
-      if (n) {
-        GMPM_CUDA(cudaMemcpyAsync(h_cand_idx, cand_idx, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, copy_stream));
-        GMPM_CUDA(cudaMemcpyAsync(h_cand_pos, cand_pos, sizeof(T) * 3 * n, cudaMemcpyDeviceToHost, copy_stream));
+      if (n > cand_fetched) {
+        const uint32_t f = cand_fetched, r = n - cand_fetched;
+        GMPM_CUDA(cudaMemcpyAsync(h_cand_idx + f, cand_idx + f, sizeof(uint32_t) * r, cudaMemcpyDeviceToHost, copy_stream));
+        GMPM_CUDA(cudaMemcpyAsync(h_cand_pos + 3 * (size_t)f, cand_pos + 3 * (size_t)f, sizeof(T) * 3 * r,
+                                  cudaMemcpyDeviceToHost, copy_stream));
+        GMPM_CUDA(cudaEventRecord(ev_copy, copy_stream));
       }
-      GMPM_CUDA(cudaEventRecord(ev_copy, copy_stream));
       GMPM_CUDA(cudaEventSynchronize(ev_copy));
+      cand_last = n;
       for (uint32_t i : h_prev_idx)
         h_pos_mirror[3 * (size_t)i] = h_pos_mirror[3 * (size_t)i + 1] = h_pos_mirror[3 * (size_t)i + 2] = T(kFarAway);
       h_prev_idx.assign(h_cand_idx, h_cand_idx + n);
@@ -1310,7 +1393,7 @@ struct State {
         h_pos_mirror[3 * i + 1] = h_cand_pos[3 * (size_t)j + 1];
         h_pos_mirror[3 * i + 2] = h_cand_pos[3 * (size_t)j + 2];
       }
-      snapshot_d2h_bytes = sizeof(uint32_t) + (uint64_t)n * (sizeof(uint32_t) + 3 * sizeof(T));
+      snapshot_d2h_bytes = sizeof(uint32_t) + (uint64_t)std::max(n, cand_fetched) * (sizeof(uint32_t) + 3 * sizeof(T));
       cull_pending = false;
       copy_pending = false;
       return h_pos_mirror;

@@ -129,6 +129,7 @@ _BUFFERS = {
     "contact_sort_keys": ("u", "Nc", 1), "contact_mpm_id": ("u", "Nc", 1), "contact_rigid_id": ("u", "Nc", 1),
     "contact_dist": ("T", "Nc", 1), "contact_normal": ("T", "Nc", 3), "contact_pos": ("T", "Nc", 3),
     "contact_rigid_v": ("T", "Nc", 3), "contact_rigid_p": ("T", "Nc", 3),
+    "particle_F": ("T", "Nv", 9),   # deformation gradients of the volumetric particles, by particle id (extension)
 }
 
 
@@ -296,6 +297,21 @@ class GpuMpmState:
             raise ValueError("pos and vel must have the same shape")
         check(self._f("add_qr_cloth")(self._h, _ptr(pos), _ptr(vel), pos.shape[0], _ptr(tri), tri.shape[0]))
 
+    def AddParticles(self, pos, vel, volume, model="fixed_corotated", youngs=1e5, poisson=0.3, friction_angle_deg=30.0,
+                     cohesion=0.0):
+        """Extension: particles with their own deformation gradient and a volumetric material
+        ("fixed_corotated", "stvk_hencky", "drucker_prager").  `volume`: rest volume per particle (scalar or array)."""
+        pos = np.ascontiguousarray(pos, self.dtype).reshape(-1, 3)
+        vel = np.ascontiguousarray(vel, self.dtype).reshape(-1, 3)
+        vol = np.ascontiguousarray(np.broadcast_to(np.asarray(volume, self.dtype), (pos.shape[0],)))
+        if vel.shape != pos.shape:
+            raise ValueError("pos and vel must have the same shape")
+        m = _lib.Material(_lib.MATERIAL_MODELS[model], 0, float(youngs), float(poisson), float(friction_angle_deg), float(cohesion))
+        check(self._f("add_particles")(self._h, _ptr(pos), _ptr(vel), _ptr(vol), pos.shape[0], C.byref(m)))
+
+    def n_volumetric(self):
+        return self._f("n_volumetric")(self._h)
+
     def Finalize(self):
         check(self._f("finalize")(self._h))
 
@@ -331,7 +347,7 @@ class GpuMpmState:
     def read(self, name):
         kind, extent, comps = _BUFFERS[name]
         n = {"N": self.n_particles(), "F": self.n_faces(), "cells": self.n_cells(), "blocks": self.n_cells() // 64,
-             "Nc": self.num_contacts()}[extent]
+             "Nc": self.num_contacts(), "Nv": self.n_volumetric() if extent == "Nv" else 0}[extent]
         dt = {"T": self.dtype, "i": np.dtype(np.int32), "u": np.dtype(np.uint32)}[kind]
         out = np.zeros(n * comps, dt)
         w = C.c_size_t()

@@ -67,3 +67,18 @@ def box_contacts(pos, lo, hi, rigid_id=1, rigid_v=(0.0, 0.0, 0.0), rigid_p_WB=No
     n = len(idx)
     return (idx.astype(np.uint32), np.full(n, rigid_id, np.uint32), dist, -grad, p,
             np.tile(np.asarray(rigid_v, np.float64), (n, 1)), np.tile(center, (n, 1)))
+
+
+def particle_block(lo, hi, per_axis=2, domain_bits=7, dx=None, jitter=0.25, seed=SEED, dtype=np.float64):
+    """Volumetric body for the particle-only API (SURVEY 8d "1M-particle volumetric block, 8 ppc, jittered lattice"):
+    `per_axis`^3 particles per grid cell inside the box [lo, hi], jittered by U(-jitter, jitter) of the particle
+    spacing.  Returns (pos, vel, volume_per_particle)."""
+    dx = dx if dx is not None else 1.0 / (1 << domain_bits)
+    h = dx / per_axis
+    lo, hi = np.asarray(lo, np.float64), np.asarray(hi, np.float64)
+    n = np.maximum(1, np.round((hi - lo) / h).astype(int))
+    g = [lo[d] + (np.arange(n[d]) + 0.5) * h for d in range(3)]
+    pos = np.stack(np.meshgrid(*g, indexing="ij"), axis=-1).reshape(-1, 3)
+    rng = np.random.default_rng(seed)
+    pos = pos + rng.uniform(-jitter, jitter, pos.shape) * h
+    return pos.astype(dtype), np.zeros_like(pos, dtype=dtype), h ** 3

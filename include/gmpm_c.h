@@ -61,6 +61,21 @@ typedef struct gmpm_params {
                        /* [0, dx * 2^domain_bits]^3 (multi-GPU scenes keep dx = 1/128 on a 256^3 grid)     */
 } gmpm_params;
 
+/* Extension (absent upstream): materials of particle-only (volumetric) bodies.  The reference has
+ * one law, the QR cloth with compile-time constants (cuda_mpm_kernels.cuh:72-181, settings.h:72-104). */
+enum gmpm_material_model {
+  GMPM_MAT_FIXED_COROTATED = 1, /* Stomakhin et al. 2013                                           */
+  GMPM_MAT_STVK_HENCKY = 2,     /* St.Venant-Kirchhoff with Hencky strain (Klar et al. 2016)       */
+  GMPM_MAT_DRUCKER_PRAGER = 3   /* StVK-Hencky + Drucker-Prager return mapping (Klar et al. 2016)  */
+};
+typedef struct gmpm_material {
+  int model;                 /* gmpm_material_model */
+  int reserved;
+  double youngs, poisson;
+  double friction_angle_deg; /* Drucker-Prager */
+  double cohesion;           /* Drucker-Prager: log-strain shift of the cone tip (0 = dry sand) */
+} gmpm_material;
+
 /* Result of one UpdateContact call (the reference prints these, cuda_mpm_solver.cu:577-582). */
 typedef struct gmpm_contact_stats {
   int iterations;        /* Newton iterations (`count`, cuda_mpm_solver.cu:241,570)            */
@@ -109,6 +124,11 @@ int gmpm_device_sync(void);
   /* GpuMpmState<T>::AddQRCloth, cuda_mpm_model.cu:16-33.  tri indexes this call's vertices. */    \
   int gmpm_add_qr_cloth_##SUF(gmpm_state_##SUF* s, const T* pos, const T* vel, size_t n_verts,      \
                               const int* tri, size_t n_tris);                                       \
+  /* Extension: n particles that carry their own deformation gradient (F = I) and a volumetric       */\
+  /* material; pos, vel 3n, rest volume n.  Mass = volume * params.density.  Generalises the          */\
+  /* AddQRCloth entry point (cuda_mpm_model.cu:16-33); their pids follow the cloth's [faces | verts]. */\
+  int gmpm_add_particles_##SUF(gmpm_state_##SUF* s, const T* pos, const T* vel, const T* volume,    \
+                               size_t n, const gmpm_material* material);                            \
   /* GpuMpmState<T>::Finalize, cuda_mpm_model.cu:36-122 (+ initialize_fem_state_kernel) */          \
   int gmpm_finalize_##SUF(gmpm_state_##SUF* s);                                                     \
   /* GpuMpmSolver<T>::RebuildMapping, cuda_mpm_solver.cu:18-70 */                                   \
@@ -182,6 +202,7 @@ int gmpm_device_sync(void);
   size_t gmpm_n_verts_##SUF(const gmpm_state_##SUF* s);                                             \
   size_t gmpm_n_faces_##SUF(const gmpm_state_##SUF* s);                                             \
   size_t gmpm_n_particles_##SUF(const gmpm_state_##SUF* s);                                         \
+  size_t gmpm_n_volumetric_##SUF(const gmpm_state_##SUF* s); /* particles added by gmpm_add_particles */\
   size_t gmpm_n_cells_##SUF(const gmpm_state_##SUF* s);                                             \
   size_t gmpm_num_contacts_##SUF(const gmpm_state_##SUF* s);                                        \
   int gmpm_grid_touched_cnt_host_##SUF(gmpm_state_##SUF* s, uint32_t* out);                         \

@@ -106,18 +106,26 @@ void ogmpm_stable_sort_low_bits(const uint32_t* keys_in, const uint32_t* ids_in,
 #define SUF f32
 #define SQRT sqrtf
 #define FABS fabsf
+#define LOG logf
+#define EXP expf
 #include "gmpm_oracle_impl.inc"
 #undef T
 #undef SUF
 #undef SQRT
 #undef FABS
+#undef LOG
+#undef EXP
 
 #define T double
 #define SUF f64
 #define SQRT sqrt
 #define FABS fabs
+#define LOG log
+#define EXP exp
 #include "gmpm_oracle_impl.inc"
 #undef T
 #undef SUF
 #undef SQRT
 #undef FABS
+#undef LOG
+#undef EXP

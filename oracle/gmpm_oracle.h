@@ -82,6 +82,16 @@ typedef struct ogmpm_contact_stats {
   /* cuda_mpm_model.cu:16-33 */                                                                 \
   void ogmpm_add_qr_cloth_##SUF(ogmpm_state_##SUF* s, const T* pos, const T* vel, size_t nv,    \
                                 const int* tri, size_t nf);                                     \
+  /* extension (gmpm_oracle_vol.inc; parity unpinned): particle-only bodies with a volumetric    */\
+  /* material; model 1 fixed corotated, 2 StVK-Hencky, 3 Drucker-Prager                          */\
+  void ogmpm_add_particles_##SUF(ogmpm_state_##SUF* s, const T* pos, const T* vel, const T* vol, \
+                                 size_t n, int model, double youngs, double poisson,             \
+                                 double friction_angle_deg, double cohesion);                    \
+  size_t ogmpm_n_volumetric_##SUF(const ogmpm_state_##SUF* s);                                   \
+  void ogmpm_svd3_##SUF(const T* F, T* U9, T* sig, T* V9);                                       \
+  void ogmpm_volumetric_update_##SUF(int model, double youngs, double poisson,                   \
+                                     double friction_angle_deg, double cohesion, const T* C,     \
+                                     T dt, T* F, T* tau9);                                       \
   /* cuda_mpm_model.cu:36-122 + cuda_mpm_kernels.cuh:13-70 */                                   \
   void ogmpm_finalize_##SUF(ogmpm_state_##SUF* s);                                              \
   /* cuda_mpm_solver.cu:18-70 */                                                                \

@@ -47,7 +47,7 @@ class ContactStats(C.Structure):
 
 def build(force=False):
     """Compile the C restatement with gcc (seconds).  Building the checker is not using it."""
-    srcs = [os.path.join(_HERE, f) for f in ("gmpm_oracle.c", "gmpm_oracle_impl.inc", "gmpm_oracle.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("gmpm_oracle.c", "gmpm_oracle_impl.inc", "gmpm_oracle_vol.inc", "gmpm_oracle.h")]
     if (not force and os.path.exists(_LIB_PATH)
             and os.path.getmtime(_LIB_PATH) >= max(os.path.getmtime(s) for s in srcs)):
         return _LIB_PATH
@@ -71,7 +71,7 @@ def build_fast():
     tag = hashlib.sha1(flags.encode()).hexdigest()[:10]
     out_dir = os.path.join(_HERE, "_fast")
     path = os.path.join(out_dir, "libgmpm_oracle_fast_%s.so" % tag)
-    srcs = [os.path.join(_HERE, f) for f in ("gmpm_oracle.c", "gmpm_oracle_impl.inc", "gmpm_oracle.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("gmpm_oracle.c", "gmpm_oracle_impl.inc", "gmpm_oracle_vol.inc", "gmpm_oracle.h")]
     if os.path.exists(path) and os.path.getmtime(path) >= max(os.path.getmtime(s) for s in srcs):
         return path
     os.makedirs(out_dir, exist_ok=True)
@@ -119,6 +119,11 @@ def _declare(L):
         g("create").restype = C.c_void_p
         g("destroy").argtypes = [C.c_void_p]
         g("add_qr_cloth").argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
+        g("add_particles").argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int] + [C.c_double] * 4
+        g("n_volumetric").argtypes = [C.c_void_p]
+        g("n_volumetric").restype = C.c_size_t
+        g("svd3").argtypes = [C.c_void_p] * 4
+        g("volumetric_update").argtypes = [C.c_int] + [C.c_double] * 4 + [C.c_void_p, ct, C.c_void_p, C.c_void_p]
         g("finalize").argtypes = [C.c_void_p]
         g("rebuild_mapping").argtypes = [C.c_void_p, C.c_int]
         g("calc_fem").argtypes = [C.c_void_p, ct]
@@ -170,7 +175,7 @@ _VIEWS = {
     "grid_momentum": ("T", "cells", 3), "grid_v_star": ("T", "cells", 3),
     "grid_touched_flags": ("u", "blocks", 1), "grid_touched_ids": ("u", "blocks", 1),
     "grid_Hess": ("T", "cells", 9), "grid_Grad": ("T", "cells", 3), "grid_Dir": ("T", "cells", 3),
-    "contact_vel": ("T", "Nc", 3), "contact_vel0": ("T", "Nc", 3), "contact_sort_keys": ("u", "Nc", 1),
+    "particle_F": ("T", "Nv", 9), "contact_vel": ("T", "Nc", 3), "contact_vel0": ("T", "Nc", 3), "contact_sort_keys": ("u", "Nc", 1),
 }
 
 
@@ -207,6 +212,16 @@ class OracleMpm:
         tri = np.ascontiguousarray(indices, np.int32).reshape(-1, 3)
         self._f("add_qr_cloth")(self.h, _ptr(pos), _ptr(vel), pos.shape[0], _ptr(tri), tri.shape[0])
 
+    MODELS = {"fixed_corotated": 1, "stvk_hencky": 2, "drucker_prager": 3}
+
+    def AddParticles(self, pos, vel, volume, model="fixed_corotated", youngs=1e5, poisson=0.3, friction_angle_deg=30.0,
+                     cohesion=0.0):
+        pos = np.ascontiguousarray(pos, self.dtype).reshape(-1, 3)
+        vel = np.ascontiguousarray(vel, self.dtype).reshape(-1, 3)
+        vol = np.ascontiguousarray(np.broadcast_to(np.asarray(volume, self.dtype), (pos.shape[0],)))
+        self._f("add_particles")(self.h, _ptr(pos), _ptr(vel), _ptr(vol), pos.shape[0], self.MODELS[model],
+                                 float(youngs), float(poisson), float(friction_angle_deg), float(cohesion))
+
     def Finalize(self):
         self._f("finalize")(self.h)
 
@@ -232,7 +247,8 @@ class OracleMpm:
     def read(self, name):
         kind, dim, comp = _VIEWS[name]
         n = {"N": self.n_particles, "F": self.n_faces, "cells": self._f("n_cells")(self.h),
-             "blocks": self._f("n_cells")(self.h) // 64, "Nc": self.n_contacts}[dim]
+             "blocks": self._f("n_cells")(self.h) // 64, "Nc": self.n_contacts,
+             "Nv": self._f("n_volumetric")(self.h)}[dim]
         dt = {"T": self.dtype, "i": np.dtype(np.int32), "u": np.dtype(np.uint32)}[kind]
         p = self._f("view")(self.h, name.encode())
         if not p or n == 0:
@@ -244,7 +260,8 @@ class OracleMpm:
         """Writable numpy array ALIASING the oracle's buffer (valid until the next call that reallocates)."""
         kind, dim, comp = _VIEWS[name]
         n = {"N": self.n_particles, "F": self.n_faces, "cells": self._f("n_cells")(self.h),
-             "blocks": self._f("n_cells")(self.h) // 64, "Nc": self.n_contacts}[dim]
+             "blocks": self._f("n_cells")(self.h) // 64, "Nc": self.n_contacts,
+             "Nv": self._f("n_volumetric")(self.h)}[dim]
         dt = {"T": self.dtype, "i": np.dtype(np.int32), "u": np.dtype(np.uint32)}[kind]
         p = self._f("view")(self.h, name.encode())
         buf = (C.c_char * (n * comp * dt.itemsize)).from_address(p)

@@ -410,7 +410,8 @@ def test_device_pairs_follow_a_resort_issued_after_the_snapshot():
         vis_pos = st.read("positions").reshape(-1, 3)
         st.Destroy()
     assert np.array_equal(got[0][0], got[1][0])
-    assert np.array_equal(got[0][1], got[1][1])
+    # two separate runs: the vertex forces of the constitutive kernel are summed with atomics -> equal to rounding
+    assert np.max(np.abs(got[0][1] - got[1][1])) <= 1e-12
 
 
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
@@ -437,7 +438,8 @@ def test_culled_snapshot_gives_the_host_query_the_same_pairs(dtype):
         assert 0 < inside.sum() < N
         assert np.array_equal(ph[inside], full[inside])
         assert np.all(ph[~inside] == dtype(1e30))
-        assert st.snapshot_d2h_bytes() == 4 + int(inside.sum()) * (4 + 3 * np.dtype(dtype).itemsize)
+        per = 4 + 3 * np.dtype(dtype).itemsize        # the fetch is speculative: at least the candidates, at most
+        assert 4 + int(inside.sum()) * per <= st.snapshot_d2h_bytes() <= 4 + (int(inside.sum()) * 9 // 8 + 200) * per
         a = scenes.box_contacts(ph, *BOX, rigid_id=1)
         b = scenes.box_contacts(full, *BOX, rigid_id=1)
         for x, y in zip(a, b):

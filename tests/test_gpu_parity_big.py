@@ -74,7 +74,7 @@ def test_cfg2_1m_one_and_twenty_substeps_vs_oracle_and_reference_kernels(dtype, 
 
     def check(tol, tag):
         assert_particles_close(st.read, orc.read, tol, (tag, "ours vs CPU oracle"))
-        for name in ("pids", "index_mappings", "sort_keys"):
+        for name in ("pids", "index_mappings"):   # (sort_keys of the OpenMP port are one substep old: compared below)
             assert np.array_equal(st.read(name), orc.read(name)), (tag, name)
         if ref is not None:
             assert_particles_close(orc.read, refget, tol, (tag, "CPU oracle vs reference kernels"))
