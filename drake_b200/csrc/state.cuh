@@ -1323,6 +1323,7 @@ struct State {
       h_prev_idx.clear();
     }
     cull_on = true;
+    cand_last = 0;  // new bounds: nothing to speculate on
   }
   void clear_query_bounds() {
     if (cull_on) wait_positions();
