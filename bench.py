@@ -37,11 +37,36 @@ for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
         sys.path.insert(0, p)
 
 N_SHEETS = 34
-DT = 1e-3
 SORT_EVERY = 40
 METRIC = "particle_steps_per_sec"
 UNIT = "particle-steps/s"
-WORKLOAD = "cfg-2: 34 stacked 100x100 cloth sheets, N=1006468 per GPU, fp64, dt=1e-3, no contact, dx=1/128"
+DX = 1.0 / 128
+E_BLOCK, NU_BLOCK = 1e5, 0.3
+
+# BASELINE.json configs.  "cfg2" (default, the driver's line) is the parity-PINNED stand-in for configs[1]: the
+# reference's only material is the QR cloth, so 1M particles are 34 stacked sheets.  The others are the configs as
+# NAMED, on the particle-only extension (parity unpinned upstream, oracle = oracle/gmpm_oracle_vol.inc).
+CONFIGS = {
+    "cfg2": {"dt": 1e-3, "scaling": "weak",
+             "workload": "cfg-2: 34 stacked 100x100 cloth sheets, N=1006468 per GPU, fp64, dt=1e-3, no contact, dx=1/128"},
+    "cfg2-block": {"dt": 2e-4, "scaling": "weak",
+                   "workload": "cfg-2 as named: 1M-particle fixed-corotated elastic block drop (100^3 particles, 8 per cell, "
+                               "E=1e5, nu=0.3), per GPU, dt=2e-4, no rigid contact, dx=1/128"},
+    "cfg3": {"dt": 2e-4, "scaling": "strong",
+             "workload": "cfg-3: 4M-particle (3 993 600) Drucker-Prager sand column collapse (80x80x78 cells, 8 per cell, "
+                         "friction angle 30 deg), x-slabs over the ranks, dt=2e-4, 128^3 grid, dx=1/128"},
+    "cfg5": {"dt": 2e-4, "scaling": "weak",
+             "workload": "cfg-5: 8M fixed-corotated particles per GPU (100^3 cells, 8 per cell), blocks adjacent in a 2x2x2 "
+                         "arrangement, 512^3 grid at dx=1/128, dt=2e-4"},
+}
+CFG = "cfg2"
+DT = CONFIGS[CFG]["dt"]
+WORKLOAD = CONFIGS[CFG]["workload"]
+
+
+def set_config(name):
+    global CFG, DT, WORKLOAD
+    CFG, DT, WORKLOAD = name, CONFIGS[name]["dt"], CONFIGS[name]["workload"]
 
 
 def env_int(name, default):
@@ -51,24 +76,62 @@ def env_int(name, default):
         return default
 
 
-def build_scene(cls_factory, dtype, rank=0, world=1):
-    """N = 1: cfg-2 as the reference would run it (128^3 unit cube).  N > 1: every rank owns one such
-    34-sheet stack of ONE larger scene on a 256^3 grid with the same dx = 1/128 (domain [0,2]^3): ranks
-    2c and 2c+1 are stacked in z in column c (the upper stack rests on the lower one: their boundary
-    sheets reach common grid blocks, which the ranks sum every substep), columns sit 1.0 apart in x / y."""
+def scene_params(world):
+    if CFG == "cfg5":
+        return {"domain_bits": 9, "dx": DX}
+    if CFG == "cfg3":
+        return {}
+    return {} if world == 1 else {"domain_bits": 8, "dx": DX}
+
+
+def add_rank_bodies(st, dtype, r, world):
+    """The part of the scene rank r owns, added to `st` (GpuMpmState, OracleMpm or RefMpm: same method names)."""
     from drake_b200 import scenes
-    st = cls_factory()
-    for r in (rank if isinstance(rank, (list, tuple)) else [rank]):   # a list: the stacks of several ranks in ONE state
-        col, lvl = r // 2, r % 2
-        ox, oy = (float(col % 2), float(col // 2)) if world > 1 else (0.0, 0.0)
+    col, lvl = r // 2, r % 2
+    ox, oy = (float(col % 2), float(col // 2)) if world > 1 else (0.0, 0.0)
+    if CFG == "cfg2":
+        # N = 1: the 128^3 unit cube of the reference.  N > 1: one 34-sheet stack per rank of ONE scene on a 256^3
+        # grid (same dx): ranks 2c and 2c+1 are stacked in z in column c (the upper stack rests on the lower one: their
+        # boundary sheets reach common grid blocks, which the ranks sum every substep); columns sit 1.0 apart
         z0 = 0.15 + lvl * N_SHEETS * 0.02
         for pos, vel, tri in scenes.stacked_sheets(N_SHEETS, z0=z0, dtype=dtype, seed=scenes.SEED + r):
             pos = pos.astype(np.float64)
             pos[:, 0] += ox
             pos[:, 1] += oy
             st.AddQRCloth(pos.astype(dtype), vel, tri)
+    elif CFG == "cfg2-block":
+        lo = np.array([0.3 + ox, 0.3 + oy, 0.35 + lvl * 50 * DX])        # the upper block sits on the lower one
+        pos, vel, vol = scenes.particle_block(lo, lo + 50 * DX, dx=DX, dtype=dtype, seed=scenes.SEED + r)
+        st.AddParticles(pos, vel, vol, "fixed_corotated", E_BLOCK, NU_BLOCK)
+    elif CFG == "cfg3":
+        c0, c1 = 80 * r // world, 80 * (r + 1) // world                   # this rank's x-slab of the column, in cells
+        lo = np.array([0.19 + c0 * DX, 0.19, 3 * DX + 0.5 * DX])
+        hi = np.array([0.19 + c1 * DX, 0.19 + 80 * DX, 3 * DX + 0.5 * DX + 78 * DX])
+        pos, vel, vol = scenes.particle_block(lo, hi, dx=DX, dtype=dtype, seed=scenes.SEED + r)
+        st.AddParticles(pos, vel, vol, "drucker_prager", E_BLOCK, NU_BLOCK, 30.0, 0.0)
+    elif CFG == "cfg5":
+        off = np.array([r & 1, (r >> 1) & 1, (r >> 2) & 1], np.float64) * 100 * DX
+        lo = np.array([0.5, 0.5, 0.3]) + off
+        pos, vel, vol = scenes.particle_block(lo, lo + 100 * DX, dx=DX, dtype=dtype, seed=scenes.SEED + r)
+        st.AddParticles(pos, vel, vol, "fixed_corotated", E_BLOCK, NU_BLOCK)
+
+
+def build_scene(cls_factory, dtype, rank=0, world=1):
+    """`rank` may be a list: the parts of several ranks in ONE state (the merged scene of the parity pass)."""
+    st = cls_factory()
+    for r in (rank if isinstance(rank, (list, tuple)) else [rank]):
+        add_rank_bodies(st, dtype, r, world)
     st.Finalize()
     return st
+
+
+def interacting_ranks(rank, world):
+    """The ranks whose parts can reach rank's particles within the parity pass (the merged checker scene)."""
+    if CFG in ("cfg2", "cfg2-block"):
+        return sorted((rank, rank ^ 1))       # pile partners; the columns are a metre apart
+    if CFG == "cfg3":
+        return list(range(world))             # one column
+    return list(range(world)) if world <= 2 else None   # cfg5: all eight blocks touch; 64M particles do not fit a check
 
 
 def _rel(a, b):
@@ -76,20 +139,24 @@ def _rel(a, b):
     return float(np.max(np.abs(a - b)) / max(float(np.max(np.abs(b))), 1e-300))
 
 
+def by_pid(st, name, comps):
+    v = np.asarray(st.read(name)).reshape(-1, comps)
+    out = np.empty_like(v)
+    out[np.asarray(st.read("pids"))] = v
+    return out
+
+
 def parity_single(st, dtype, steps):
     """N = 1: the state the product just computed (`steps` substeps from the fresh scene, re-sort on the first)
     against the CPU oracle (strict -O2 -ffp-contract=off build) run over the same substeps.  Checker only."""
     import oracle_py as O
-    from drake_b200 import scenes
-    orc = O.OracleMpm(dtype)
-    for pos, vel, tri in scenes.stacked_sheets(N_SHEETS, dtype=dtype):
-        orc.AddQRCloth(pos, vel, tri)
-    orc.Finalize()
+    orc = build_scene(lambda: O.OracleMpm(dtype, O.default_params(**scene_params(1))), dtype)
     cores = os.cpu_count() or 1
     orc.RebuildMapping(True)
     for _ in range(steps):
         orc.substep_omp(DT, -1, cores)
-    out = {"against": "CPU oracle (oracle/gmpm_oracle.c, strict build), same scene, same substeps", "steps": steps,
+    out = {"against": "CPU oracle (oracle/gmpm_oracle.c%s, strict build), same scene, same substeps"
+                      % ("" if CFG == "cfg2" else " + gmpm_oracle_vol.inc, parity unpinned upstream"), "steps": steps,
            "max_rel_positions": _rel(st.read("positions"), orc.read("positions")),
            "max_rel_velocities": _rel(st.read("velocities"), orc.read("velocities")),
            "pids_equal": bool(np.array_equal(st.read("pids"), orc.read("pids")))}
@@ -98,24 +165,35 @@ def parity_single(st, dtype, steps):
 
 
 def parity_multi(st, dtype, steps, rank, world, local, make_state):
-    """N > 1: this rank's vertices after `steps` substeps of the multi-rank path (fused peer-window exchange)
-    against ONE state holding the merged scene of its column (this rank's stack and its pile partner's: the
-    columns are a metre apart and never interact), stepped on this GPU without any exchange."""
+    """N > 1: this rank's particles after `steps` substeps of the multi-rank path (fused peer-window exchange) against
+    ONE state holding the merged scene of every rank that can interact with it, stepped on this GPU without any
+    exchange.  Particles are matched by their original ids (the merged state numbers [faces | verts | volumetric] over
+    all its bodies)."""
     from drake_b200.gpu_mpm import GpuMpmSolver
-    partner = rank ^ 1
-    both = sorted((rank, partner))
-    merged = build_scene(make_state, dtype, both, world)
+    group = interacting_ranks(rank, world)
+    if group is None:
+        return None
+    merged = build_scene(make_state, dtype, group, world)
     GpuMpmSolver().RunSubsteps(merged, steps, DT, -1, SORT_EVERY)
-    mv, _ = merged.DumpCpuState()
-    mine, _ = st.DumpCpuState()
-    v = mine.shape[0]
-    ref = mv[:v] if rank == both[0] else mv[mv.shape[0] - v:]
+    if st.n_faces():
+        mv, _ = merged.DumpCpuState()           # vertices in mesh order
+        mine, _ = st.DumpCpuState()
+        v, k = mine.shape[0], group.index(rank)
+        ref = mv[k * v:(k + 1) * v]             # equal-sized meshes per rank
+    else:
+        mv, mine = by_pid(merged, "positions", 3), by_pid(st, "positions", 3)
+        counts = [0] * len(group)
+        # volumetric bodies only: the merged pids are the ranks' pids, concatenated in group order
+        import torch
+        import torch.distributed as dist
+        t = torch.zeros(world, dtype=torch.int64, device="cuda")
+        t[rank] = mine.shape[0]
+        dist.all_reduce(t)
+        counts = [int(t[g]) for g in group]
+        o = sum(counts[:group.index(rank)])
+        ref = mv[o:o + mine.shape[0]]
     merged.Destroy()
     return _rel(mine, ref)
-
-
-def scene_params(world):
-    return {} if world == 1 else {"domain_bits": 8, "dx": 1.0 / 128}
 
 
 class ClockSampler(threading.Thread):
@@ -187,10 +265,7 @@ def cpu_baseline(dtype, budget_s=12.0):
     cores = os.cpu_count() or 1
     # timing-only build of the oracle sources: -O3 -march=native, contraction allowed, compiled on this host
     # (the bit-exact -O2 -ffp-contract=off build is the parity checker, never the timed one)
-    orc = O.OracleMpm(dtype, fast=True)
-    for pos, vel, tri in scenes.stacked_sheets(N_SHEETS, dtype=dtype):
-        orc.AddQRCloth(pos, vel, tri)
-    orc.Finalize()
+    orc = build_scene(lambda: O.OracleMpm(dtype, O.default_params(**scene_params(1)), fast=True), dtype)
     n = orc.n_particles
     orc.substep_omp(DT, -1, cores)  # warm-up (page faults, first touched-block list)
     t0 = time.perf_counter()
@@ -346,6 +421,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=80)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"])
+    ap.add_argument("--config", default="cfg2", choices=sorted(CONFIGS),
+                    help="BASELINE.json config (default cfg2 = the driver's line; the others are builder runs)")
     ap.add_argument("--parity-steps", type=int, default=20,
                     help="substeps of the fresh scene checked against the oracle before the timed region (0 = off)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -358,6 +435,7 @@ def main():
                     help="N>1: exchange the shared blocks with an NCCL all-reduce instead of the peer-memory windows")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    set_config(args.config)
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
 
     if args.impl == "reference":
@@ -399,7 +477,7 @@ def main():
     if world > 1:
         from drake_b200 import slab
         peer = world <= 8 and not args.no_peer             # block sums through peer-memory windows (csrc/halo.cuh)
-        ex = slab.SlabExchange(slab.GpuHaloBackend(st), peer=peer)
+        ex = slab.SlabExchange(slab.GpuHaloBackend(st), peer=peer, peer_cap_blocks=32768 if CFG == "cfg5" else 8192)
 
     # interior UpdateGrid/G2P work hides the all-reduce; pays off once the collective is slow (measured: loses
     # 20 us at 2 ranks, wins 18 us at 8)
@@ -440,11 +518,14 @@ def main():
         else:
             mine = parity_multi(st, dtype, P, rank, world, local,
                                 lambda: GpuMpmState(dtype, device=local, **scene_params(world)))
-            t = torch.tensor([mine], dtype=torch.float64, device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            parity = {"against": "one state per column holding the merged scene of both sharers, no exchange",
-                      "steps": P, "max_rel_vertex_positions": float(t[0]), "ranks_checked": world,
-                      "tolerance": tol, "ok": bool(float(t[0]) <= tol)}
+            if mine is None:
+                parity = {"unchecked": "the merged scene of all interacting ranks does not fit one GPU check"}
+            else:
+                t = torch.tensor([mine], dtype=torch.float64, device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                parity = {"against": "one state holding the merged scene of every rank that interacts with this one, "
+                                     "no exchange", "steps": P, "max_rel_positions": float(t[0]), "ranks_checked": world,
+                          "tolerance": tol, "ok": bool(float(t[0]) <= tol)}
         print("[bench] rank %d parity: %s" % (rank, parity), file=sys.stderr)
 
     sampler = ClockSampler(local)
@@ -572,13 +653,13 @@ def main():
                     "algorithmic_bytes_per_launch": alg[dom], "touched_cells_per_particle": c,
                     "timing": "CUDA events between launches on the library stream, separate pass of %d steps" % Kp}
         line = {"metric": METRIC, "value": N_all * K / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
-                "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": CONFIGS[CFG]["scaling"], "vs_baseline": None,
                 "dtype": args.dtype, "data": "synthetic",
                 "config": {"workload": WORKLOAD, "sort_every": SORT_EVERY, "particles_per_gpu": N,
                            "particle_blocks": pblocks, "touched_grid_blocks": touched,
                            "l2": "inputs larger than L2 (particle state %.0f MB per step > 126 MB)" % (N * (44 * T + 8) / 1e6),
                            "parallelism": "single GPU" if world == 1 else
-                           "%d ranks, one 34-sheet stack each of one scene on a 256^3 grid (dx = 1/128); grid blocks "
+                           "%d ranks, each owning its part of ONE scene (see workload; whole bodies per rank); grid blocks "
                            "reached by two ranks are summed every substep: all-reduce of block flags (NCCL, side stream, "
                            "one substep ahead) + %s of %d shared blocks (%.0f KB/step all-reduced)%s"
                            % (world, "stores into the sharers' peer-memory windows (NVLink) with device-side delivery flags"
@@ -601,12 +682,12 @@ def main():
             cb = cpu_baseline(dtype)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "flags")}
             line["speedup_vs_cpu_port"] = {"device": line["value"] / cb["value"], "e2e": line["e2e"]["value"] / cb["value"]}
-        if world == 1 and not args.no_ref_gpu:
+        if world == 1 and not args.no_ref_gpu and CFG == "cfg2":   # the reference's kernels know the cloth only
             try:
                 line["reference_gpu"] = reference_gpu(dtype, 100)
             except Exception as e:  # checker library missing or failed: not fatal for the product line
                 line["reference_gpu"] = {"unavailable": repr(e)}
-        if world == 1 and args.dtype == "f64" and not args.no_f32:
+        if world == 1 and args.dtype == "f64" and not args.no_f32 and CFG == "cfg2":
             try:
                 line["f32"] = f32_line(local, peak, min(K, 400))
             except Exception as e:
