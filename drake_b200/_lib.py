@@ -52,7 +52,7 @@ PLAIN_SYMBOLS = ["gmpm_default_params", "gmpm_last_error", "gmpm_version", "gmpm
                  "gmpm_morton_code", "gmpm_cell_index", "gmpm_inverse_cell_index", "gmpm_radix_sort_pairs"]
 TYPED_SYMBOLS = ["create", "destroy", "add_qr_cloth", "finalize", "rebuild_mapping", "calc_fem", "p2g",
                  "update_grid", "g2p", "sync", "sync_particle_state_to_cpu", "sync_particle_state_to_cpu_async",
-                 "positions_host", "set_query_bounds", "add_particles", "n_volumetric", "clear_query_bounds", "snapshot_d2h_bytes", "halo_flags", "halo_plan_async", "halo_pack", "halo_unpack", "halo_peer_init", "halo_peer_window", "halo_peer_attach", "halo_peer_send", "halo_peer_recv", "update_grid_part", "g2p_part", "stream", "halo_stream", "copy_contact_pairs",
+                 "positions_host", "set_query_bounds", "add_particles", "migrate_out", "migrate_in", "n_volumetric", "clear_query_bounds", "snapshot_d2h_bytes", "halo_flags", "halo_plan_async", "halo_reset_plan", "halo_pack", "halo_unpack", "halo_peer_init", "halo_peer_window", "halo_peer_attach", "halo_peer_send", "halo_peer_recv", "update_grid_part", "g2p_part", "stream", "halo_stream", "copy_contact_pairs",
                  "generate_contact_pairs", "run_driver_substeps", "set_driver_geometry_frozen", "update_contact", "reallocate_external_bodies", "external_body_force_to_host",
                  "dump_cpu_state", "n_verts", "n_faces", "n_particles", "n_cells", "num_contacts",
                  "grid_touched_cnt_host", "read", "checkpoint_bytes", "save_state", "load_state", "run_substeps", "kernel_launches", "set_profiling",
@@ -97,6 +97,8 @@ def _declare(L):
         g("destroy").argtypes = [vp]
         g("add_qr_cloth").argtypes = [vp, vp, vp, sz, vp, sz]
         g("add_particles").argtypes = [vp, vp, vp, vp, sz, C.POINTER(Material)]
+        g("migrate_out").argtypes = [vp, C.c_int, ct, ct, vp, vp, vp, sz, C.POINTER(C.c_size_t)]
+        g("migrate_in").argtypes = [vp, vp, sz, vp]
         g("n_volumetric").argtypes = [vp]
         g("n_volumetric").restype = sz
         g("finalize").argtypes = [vp]
@@ -115,6 +117,7 @@ def _declare(L):
         g("load_state").argtypes = [vp, vp, sz]
         g("halo_flags").argtypes = [vp, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
         g("halo_plan_async").argtypes = [vp]
+        g("halo_reset_plan").argtypes = [vp]
         g("halo_pack").argtypes = [vp, C.POINTER(C.c_uint32), C.POINTER(C.c_void_p)]
         g("halo_unpack").argtypes = [vp]
         g("halo_peer_init").argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32]

@@ -7,6 +7,7 @@
 #include "checkpoint.cuh"
 #include "contact_gen.cuh"
 #include "getters.cuh"
+#include "migrate.cuh"
 #include "state.cuh"
 
 namespace {
@@ -152,6 +153,16 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
                                const gmpm_material* mat) {                                                     \
     return guarded([&] { s->st.add_particles(pos, vel, volume, n, mat); });                                    \
   }                                                                                                            \
+  int gmpm_migrate_out_##SUF(gmpm_state_##SUF* s, int axis, T lo, T hi, const T* park, T* records, int* pids,  \
+                             size_t cap, size_t* n) {                                                          \
+    return guarded([&] {                                                                                       \
+      const size_t c = s->st.migrate_out(axis, lo, hi, park, records, pids, cap);                              \
+      if (n) *n = c;                                                                                           \
+    });                                                                                                        \
+  }                                                                                                            \
+  int gmpm_migrate_in_##SUF(gmpm_state_##SUF* s, const T* records, size_t n, int* pids) {                      \
+    return guarded([&] { s->st.migrate_in(records, n, pids); });                                               \
+  }                                                                                                            \
   int gmpm_finalize_##SUF(gmpm_state_##SUF* s) { return guarded([&] { s->st.finalize(); }); }                  \
   int gmpm_rebuild_mapping_##SUF(gmpm_state_##SUF* s, int sort) {                                              \
     return guarded([&] { s->st.rebuild_mapping(sort != 0); });                                                 \
@@ -241,6 +252,7 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
     });                                                                                                        \
   }                                                                                                            \
   int gmpm_halo_plan_async_##SUF(gmpm_state_##SUF* s) { return guarded([&] { s->st.halo_plan_async(); }); }      \
+  int gmpm_halo_reset_plan_##SUF(gmpm_state_##SUF* s) { return guarded([&] { s->st.halo_reset_plan(); }); }      \
   int gmpm_halo_pack_##SUF(gmpm_state_##SUF* s, uint32_t* n_shared, void** packed_dev) {                       \
     return guarded([&] {                                                                                       \
       if (!n_shared || !packed_dev) throw std::invalid_argument("null out pointer");                           \

@@ -990,6 +990,12 @@ struct State {
     halo_next_slot = slot;
     halo_plan_pending = true;
   }
+  void halo_reset_plan() {
+    if (halo_stream) GMPM_CUDA(cudaStreamSynchronize(halo_stream));
+    if (stream) GMPM_CUDA(cudaStreamSynchronize(stream));
+    halo_planned = halo_plan_pending = halo_flags_out = halo_own_valid = halo_packed_out = false;
+    halo_sent = halo_recv_pending = false;
+  }
   int halo_next_slot = 0;
   bool halo_plan_pending = false;
   // Start of an exchange: picks up the list planned for it (count through pinned memory), checks containment,
@@ -1437,6 +1443,9 @@ struct State {
   void run_driver_substeps(int n, T dt, int bc, int sort_every, const gmpm_analytic_geometry* geoms, size_t n_geoms,
                            int query_every, T mu, T stiffness, T damping, bool exact, int max_it,
                            gmpm_driver_stats* out);      // contact_gen.cuh
+  void invalidate_after_particle_edit();                 // migrate.cuh
+  size_t migrate_out(int axis, T lo, T hi, const T* park, T* records, int* pids_out, size_t cap);
+  void migrate_in(const T* records, size_t n, int* pids_out);
   size_t checkpoint_bytes() const;                       // checkpoint.cuh
   size_t save_state(void* out, size_t cap);
   void load_state(const void* in, size_t bytes);

@@ -80,7 +80,11 @@ __device__ inline void svd3(const T* F, T (&U)[3][3], T (&sig)[3], T (&V)[3][3])
       A[i][j] = F[0 * 3 + i] * F[0 * 3 + j] + F[1 * 3 + i] * F[1 * 3 + j] + F[2 * 3 + i] * F[2 * 3 + j];
       V[i][j] = i == j ? T(1) : T(0);
     }
+  // cyclic sweeps until the off-diagonal part is below rounding (quadratic convergence: 3-5 sweeps for the
+  // deformation gradients of a simulation; kSvdSweeps bounds the loop)
+  const T thr = sizeof(T) == 8 ? T(1e-16) : T(1e-7);
   for (int sweep = 0; sweep < kSvdSweeps; ++sweep) {
+    if (tabs(A[0][1]) + tabs(A[0][2]) + tabs(A[1][2]) <= thr * (tabs(A[0][0]) + tabs(A[1][1]) + tabs(A[2][2]))) break;
     jacobi_rotate<T, 0, 1>(A, V);
     jacobi_rotate<T, 0, 2>(A, V);
     jacobi_rotate<T, 1, 2>(A, V);

@@ -204,6 +204,9 @@ class GpuMpmState:
         check(self._f("stream")(self._h, C.byref(p)))
         return p.value or 0
 
+    def halo_reset_plan(self):
+        check(self._f("halo_reset_plan")(self._h))
+
     def halo_flags(self):
         """-> (device pointer of uint8[n_blocks], n_blocks)"""
         p, n = C.c_void_p(), C.c_size_t()
@@ -308,6 +311,27 @@ class GpuMpmState:
             raise ValueError("pos and vel must have the same shape")
         m = _lib.Material(_lib.MATERIAL_MODELS[model], 0, float(youngs), float(poisson), float(friction_angle_deg), float(cohesion))
         check(self._f("add_particles")(self._h, _ptr(pos), _ptr(vel), _ptr(vol), pos.shape[0], C.byref(m)))
+
+    MIGRATE_RECORD = 26   # pos 3, vel 3, C 9, volume, F 9, material index
+
+    def migrate_out(self, axis, lo, hi, park, cap):
+        """Extension: active volumetric particles outside [lo, hi) along `axis` leave the state.
+        -> (records (n, 26), local particle ids (n,)), sorted by id; at most cap."""
+        rec = np.zeros((cap, self.MIGRATE_RECORD), self.dtype)
+        pids = np.zeros(cap, np.int32)
+        park = np.ascontiguousarray(park, self.dtype)
+        n = C.c_size_t()
+        check(self._f("migrate_out")(self._h, int(axis), self._ct(lo), self._ct(hi), _ptr(park), _ptr(rec), _ptr(pids),
+                                     cap, C.byref(n)))
+        return rec[:n.value].copy(), pids[:n.value].copy()
+
+    def migrate_in(self, records):
+        """Extension: the records take over inactive particles (volume 0).  -> the local particle ids they took."""
+        rec = np.ascontiguousarray(records, self.dtype).reshape(-1, self.MIGRATE_RECORD)
+        pids = np.zeros(rec.shape[0], np.int32)
+        if rec.shape[0]:
+            check(self._f("migrate_in")(self._h, _ptr(rec), rec.shape[0], _ptr(pids)))
+        return pids
 
     def n_volumetric(self):
         return self._f("n_volumetric")(self._h)

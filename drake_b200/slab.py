@@ -113,6 +113,9 @@ class GpuHaloBackend:
     def halo_plan_async(self):
         self.state.halo_plan_async()
 
+    def reset_plan(self):
+        self.state.halo_reset_plan()
+
     def halo_pack(self):
         n_shared, ptr = self.state.halo_pack()
         if n_shared == 0:
@@ -308,3 +311,97 @@ def substep(solver, state, exchange, dt, mpm_bc=-1, sort=False, overlap=False):
         exchange.exchange()
         solver.UpdateGrid(state, mpm_bc)
         solver.GridToParticle(state, dt)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Position-owned slabs with particle migration.  Volumetric particles only: cloth
+# meshes stay whole (partition_meshes above).
+# ---------------------------------------------------------------------------------------------------------------
+def slab_edges(positions, world, axis=0):
+    """Interior edges of `world` slabs along `axis` holding equal particle counts (the initial partition):
+    world - 1 ascending coordinates; rank r owns [edge[r-1], edge[r])."""
+    x = np.sort(np.asarray(positions, np.float64).reshape(-1, 3)[:, axis])
+    return np.array([x[(len(x) * r) // world] for r in range(1, world)], np.float64)
+
+
+def owner_of(x, edges):
+    return np.searchsorted(np.asarray(edges, np.float64), np.asarray(x, np.float64), side="right")
+
+
+class SlabMigrator:
+    """Keeps the volumetric particles of ONE rank inside its slab [edges[rank-1] - margin, edges[rank] + margin).
+
+    The state must have been created with spare inactive particles (AddParticles with volume 0 at `park`).  `gid` maps
+    the state's local particle ids to scene-wide ids (-1: inactive) so that results can be compared across
+    decompositions.  migrate() is collective: every rank calls it between GridToParticle and the next RebuildMapping,
+    every `every` substeps; `all_gather` is torch.distributed.all_gather_object-like (list of per-rank objects).
+    Ownership never changes a result (shared grid blocks are summed by the exchange); the margin only keeps particles
+    that oscillate around an edge from bouncing between ranks."""
+
+    def __init__(self, state, rank, world, edges, gid, park, axis=0, margin=0.0, cap=1 << 16, all_gather=None):
+        self.state, self.rank, self.world = state, rank, world
+        self.edges = np.asarray(edges, np.float64)
+        self.gid = np.asarray(gid, np.int64).copy()
+        self.park = np.asarray(park, np.float64)
+        self.axis, self.margin, self.cap = axis, float(margin), int(cap)
+        self.all_gather = all_gather
+        self.moved_out = self.moved_in = 0
+
+    def bounds(self):
+        lo = -np.inf if self.rank == 0 else self.edges[self.rank - 1] - self.margin
+        hi = np.inf if self.rank == self.world - 1 else self.edges[self.rank] + self.margin
+        big = 1e30
+        return max(lo, -big), min(hi, big)
+
+    def extract(self):
+        """-> {destination rank: (records, gids)} of the particles that left this rank's slab."""
+        lo, hi = self.bounds()
+        rec, pids = self.state.migrate_out(self.axis, lo, hi, self.park, self.cap)
+        gids = self.gid[pids]
+        self.gid[pids] = -1
+        dest = owner_of(rec[:, self.axis], self.edges) if len(pids) else np.zeros(0, np.int64)
+        self.moved_out += len(pids)
+        return {int(d): (rec[dest == d], gids[dest == d]) for d in np.unique(dest)}
+
+    def insert(self, parcels):
+        """parcels: list over source ranks of {destination: (records, gids)}."""
+        recs = [p[self.rank][0] for p in parcels if self.rank in p]
+        gids = [p[self.rank][1] for p in parcels if self.rank in p]
+        if not recs:
+            return 0
+        rec, g = np.concatenate(recs), np.concatenate(gids)
+        order = np.argsort(g, kind="stable")          # arrival order must not depend on who sent first
+        pids = self.state.migrate_in(rec[order])
+        self.gid[pids] = g[order]
+        self.moved_in += len(pids)
+        return len(pids)
+
+    def migrate(self):
+        out = self.extract()
+        parcels = self.all_gather(out)
+        self.insert(parcels)
+        return sum(len(p[d][1]) for p in parcels for d in p)   # particles that changed hands, scene-wide
+
+
+def dist_all_gather(group=None):
+    import torch.distributed as dist
+
+    def gather(obj):
+        out = [None] * dist.get_world_size(group)
+        dist.all_gather_object(out, obj, group=group)
+        return out
+    return gather
+
+
+def migrate_in_process(migrators, exchange=None):
+    """The same for several states living in one process (tests).  Returns the number of particles moved."""
+    parcels = [m.extract() for m in migrators]
+    for m in migrators:
+        m.insert(parcels)
+    moved = sum(len(p[d][1]) for p in parcels for d in p)
+    if moved and exchange is not None:
+        exchange.planned = False          # the shared-block plan was made for the old ownership: plan afresh
+        for b in getattr(exchange, "backends", []):
+            if hasattr(b, "reset_plan"):
+                b.reset_plan()
+    return moved

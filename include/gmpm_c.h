@@ -129,6 +129,17 @@ int gmpm_device_sync(void);
   /* AddQRCloth entry point (cuda_mpm_model.cu:16-33); their pids follow the cloth's [faces | verts]. */\
   int gmpm_add_particles_##SUF(gmpm_state_##SUF* s, const T* pos, const T* vel, const T* volume,    \
                                size_t n, const gmpm_material* material);                            \
+  /* Extension (multi-GPU): migration of volumetric particles between the states of a      */\
+  /* position-owned decomposition.  A state is given spare INACTIVE particles (gmpm_add_particles      */\
+  /* with volume 0).  migrate_out copies out the active volumetric particles whose coordinate `axis`   */\
+  /* lies outside [lo, hi) -- 26 scalars each: pos 3, vel 3, C 9, volume, F 9, material index -- with  */\
+  /* their local particle ids, sorted by id, and turns their slots inactive (parked at park[3]);       */\
+  /* at most cap (the others stay for the next call).  migrate_in hands n such records to inactive     */\
+  /* slots (pids <- the local ids they took; may be null).  Both belong between GridToParticle and     */\
+  /* the next RebuildMapping; all states of a scene must declare their materials in the same order.    */\
+  int gmpm_migrate_out_##SUF(gmpm_state_##SUF* s, int axis, T lo, T hi, const T* park, T* records,  \
+                             int* pids, size_t cap, size_t* n);                                     \
+  int gmpm_migrate_in_##SUF(gmpm_state_##SUF* s, const T* records, size_t n, int* pids);            \
   /* GpuMpmState<T>::Finalize, cuda_mpm_model.cu:36-122 (+ initialize_fem_state_kernel) */          \
   int gmpm_finalize_##SUF(gmpm_state_##SUF* s);                                                     \
   /* GpuMpmSolver<T>::RebuildMapping, cuda_mpm_solver.cu:18-70 */                                   \
@@ -234,6 +245,9 @@ int gmpm_device_sync(void);
   /* than one grid block in one substep).                                                             */\
   int gmpm_halo_flags_##SUF(gmpm_state_##SUF* s, void** flags_dev, size_t* n_blocks);               \
   int gmpm_halo_plan_async_##SUF(gmpm_state_##SUF* s);                                              \
+  /* forgets the shared-block plan (made one substep ahead for the old particle ownership): the next  */\
+  /* exchange plans afresh after its P2G, as at start-up.  Call on EVERY rank after a migration.      */\
+  int gmpm_halo_reset_plan_##SUF(gmpm_state_##SUF* s);                                              \
   int gmpm_halo_pack_##SUF(gmpm_state_##SUF* s, uint32_t* n_shared, void** packed_dev);             \
   int gmpm_halo_unpack_##SUF(gmpm_state_##SUF* s);                                                  \
   /* Peer mode (<= 8 ranks of one NVSwitch domain): the exchange itself goes through receive windows  */\

@@ -88,6 +88,9 @@ typedef struct ogmpm_contact_stats {
                                  size_t n, int model, double youngs, double poisson,             \
                                  double friction_angle_deg, double cohesion);                    \
   size_t ogmpm_n_volumetric_##SUF(const ogmpm_state_##SUF* s);                                   \
+  size_t ogmpm_migrate_out_##SUF(ogmpm_state_##SUF* s, int axis, T lo, T hi, const T* park,      \
+                                 T* records, int* pids, size_t cap);                             \
+  int ogmpm_migrate_in_##SUF(ogmpm_state_##SUF* s, const T* records, size_t n, int* pids);       \
   void ogmpm_svd3_##SUF(const T* F, T* U9, T* sig, T* V9);                                       \
   void ogmpm_volumetric_update_##SUF(int model, double youngs, double poisson,                   \
                                      double friction_angle_deg, double cohesion, const T* C,     \

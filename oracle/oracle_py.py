@@ -120,6 +120,9 @@ def _declare(L):
         g("destroy").argtypes = [C.c_void_p]
         g("add_qr_cloth").argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
         g("add_particles").argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int] + [C.c_double] * 4
+        g("migrate_out").argtypes = [C.c_void_p, C.c_int, ct, ct, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+        g("migrate_out").restype = C.c_size_t
+        g("migrate_in").argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         g("n_volumetric").argtypes = [C.c_void_p]
         g("n_volumetric").restype = C.c_size_t
         g("svd3").argtypes = [C.c_void_p] * 4
@@ -221,6 +224,20 @@ class OracleMpm:
         vol = np.ascontiguousarray(np.broadcast_to(np.asarray(volume, self.dtype), (pos.shape[0],)))
         self._f("add_particles")(self.h, _ptr(pos), _ptr(vel), _ptr(vol), pos.shape[0], self.MODELS[model],
                                  float(youngs), float(poisson), float(friction_angle_deg), float(cohesion))
+
+    def migrate_out(self, axis, lo, hi, park, cap):
+        rec = np.zeros((cap, 26), self.dtype)
+        pids = np.zeros(cap, np.int32)
+        park = np.ascontiguousarray(park, self.dtype)
+        n = self._f("migrate_out")(self.h, int(axis), self.ct(lo), self.ct(hi), _ptr(park), _ptr(rec), _ptr(pids), cap)
+        return rec[:n].copy(), pids[:n].copy()
+
+    def migrate_in(self, records):
+        rec = np.ascontiguousarray(records, self.dtype).reshape(-1, 26)
+        pids = np.zeros(rec.shape[0], np.int32)
+        if rec.shape[0]:
+            assert self._f("migrate_in")(self.h, _ptr(rec), rec.shape[0], _ptr(pids)) == 0, "no inactive particle left"
+        return pids
 
     def Finalize(self):
         self._f("finalize")(self.h)

@@ -84,6 +84,12 @@ class OracleHaloBackend:
     def _touched(self):
         return self.orc.view("grid_touched_flags") != 0
 
+    def reset_plan(self):
+        """After particles changed hands (slab.SlabMigrator): forget the plan made for the old ownership."""
+        self.planned_own = None
+        self.next_shared = None
+        self.have_mass = False
+
     def halo_flags(self):
         touched = self._touched()
         if self.planned_own is not None:

@@ -1,0 +1,222 @@
+"""Position-owned slabs with particle migration: a volumetric body split over two
+(three) states by x-slabs, particles handed over as they cross the slab edges, must reproduce the single-state run.
+CPU: the oracle backend (in process and over gloo, world size 2).  GPU: several states on one device."""
+import multiprocessing as mp
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import oracle_py as O
+from drake_b200 import scenes, slab
+from oracle_halo import OracleHaloBackend
+
+DT, DX = 2e-4, 1.0 / 128
+MAT = dict(model="drucker_prager", youngs=1e5, poisson=0.3, friction_angle_deg=30.0, cohesion=0.0)
+
+
+def moving_block(dtype, cells=(10, 6, 6)):
+    """A sand block sliding in +x with a shear: within ~60 substeps a good part of it crosses the slab edges."""
+    lo = np.array([0.40, 0.45, 0.30])
+    pos, vel, vol = scenes.particle_block(lo, lo + np.array(cells) * DX, dtype=dtype, seed=11)
+    vel = np.zeros_like(pos, dtype=np.float64)
+    vel[:, 0] = 2.0 + 6.0 * (pos[:, 2] - lo[2])
+    vel[:, 2] = -0.5
+    return pos, vel.astype(dtype), vol
+
+
+def park_of(rank):
+    return np.array([4.5 * DX, 4.5 * DX, (4.5 + 8 * rank) * DX])
+
+
+def make_part(factory, dtype, pos, vel, vol, mine, rank, spare):
+    st = factory()
+    st.AddParticles(pos[mine], vel[mine], vol, **MAT)
+    st.AddParticles(np.tile(park_of(rank), (spare, 1)), np.zeros((spare, 3)), 0.0, **MAT)
+    st.Finalize()
+    gid = np.concatenate([np.nonzero(mine)[0], -np.ones(spare, np.int64)])
+    return st, gid
+
+
+def gathered(parts, migrators, n_total, name="positions", comps=3):
+    """Scene-wide array by global particle id from the active particles of all parts."""
+    out = np.full((n_total, comps), np.nan)
+    for st, m in zip(parts, migrators):
+        v = np.asarray(st.read(name), np.float64).reshape(-1, comps)
+        pids = np.asarray(st.read("pids"))
+        by_pid = np.empty_like(v)
+        by_pid[pids] = v
+        act = m.gid >= 0
+        out[m.gid[act]] = by_pid[act]
+    assert not np.isnan(out).any()
+    return out
+
+
+def run_split(make_state, make_backend, step, dtype, world, steps, every, sync=None):
+    pos, vel, vol = moving_block(dtype)
+    n = len(pos)
+    edges = slab.slab_edges(pos, world)
+    own = slab.owner_of(pos[:, 0], edges)
+    parts, migs = [], []
+    for r in range(world):
+        st, gid = make_part(make_state, dtype, pos, vel, vol, own == r, r, spare=n // 2)
+        parts.append(st)
+        migs.append(slab.SlabMigrator(st, r, world, edges, gid, park_of(r), margin=0.5 * DX, cap=n))
+    ex = slab.InProcessExchange([make_backend(s) for s in parts], sync=sync)
+    moved = 0
+    for it in range(steps):
+        step(parts, ex, it)
+        if (it + 1) % every == 0:
+            moved += slab.migrate_in_process(migs, ex)
+    return parts, migs, moved, (pos, vel, vol)
+
+
+def oracle_step(parts, ex, it):
+    for s in parts:
+        s.RebuildMapping(it % 7 == 0); s.CalcFemStateAndForce(DT); s.ParticleToGrid(DT)
+    ex.exchange()
+    for s in parts:
+        s.UpdateGrid(-1); s.GridToParticle(DT)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_oracle_slabs_with_migration_match_single_state(world):
+    dtype = np.float64
+    parts, migs, moved, (pos, vel, vol) = run_split(lambda: O.OracleMpm(dtype), OracleHaloBackend, oracle_step, dtype,
+                                                    world, steps=60, every=4)
+    assert moved > len(pos) // 10, moved                      # the test really migrates
+    full = O.OracleMpm(dtype)
+    full.AddParticles(pos, vel, vol, **MAT)
+    full.Finalize()
+    for it in range(60):
+        full.substep(DT, -1, it % 7 == 0)
+    ref = np.empty((len(pos), 3))
+    ref[full.read("pids")] = full.read("positions").reshape(-1, 3)
+    got = gathered(parts, migs, len(pos))
+    assert np.max(np.abs(got - ref)) <= 1e-12
+    # every particle sits in its slab (+ margin) and the bookkeeping is a partition of the scene
+    gids = np.concatenate([m.gid[m.gid >= 0] for m in migs])
+    assert np.array_equal(np.sort(gids), np.arange(len(pos)))
+    for m, st in zip(migs, parts):
+        lo, hi = m.bounds()
+        x = got[m.gid[m.gid >= 0], 0]
+        # migration ran 4 substeps ago at most: a particle moves < 0.2 cells per substep here
+        assert np.all(x >= lo - DX) and np.all(x < hi + DX)
+
+
+def free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _gloo_worker(rank, world, port, ret):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    dtype = np.float64
+    pos, vel, vol = moving_block(dtype)
+    edges = slab.slab_edges(pos, world)
+    own = slab.owner_of(pos[:, 0], edges)
+    st, gid = make_part(lambda: O.OracleMpm(dtype), dtype, pos, vel, vol, own == rank, rank, spare=len(pos) // 2)
+    backend = OracleHaloBackend(st)
+    ex = slab.SlabExchange(backend)
+    mig = slab.SlabMigrator(st, rank, world, edges, gid, park_of(rank), margin=0.5 * DX, cap=len(pos),
+                            all_gather=slab.dist_all_gather())
+    moved = 0
+    for it in range(40):
+        st.RebuildMapping(it % 7 == 0); st.CalcFemStateAndForce(DT); st.ParticleToGrid(DT)
+        ex.exchange()
+        st.UpdateGrid(-1); st.GridToParticle(DT)
+        if (it + 1) % 4 == 0:
+            n = mig.migrate()
+            moved += n
+            if n:
+                ex.planned = False
+                backend.reset_plan()
+    v = st.read("positions").reshape(-1, 3)
+    by_pid = np.empty_like(v)
+    by_pid[st.read("pids")] = v
+    act = mig.gid >= 0
+    ret[rank] = (mig.gid[act], by_pid[act], moved)
+    dist.destroy_process_group()
+
+
+def test_gloo_world2_slabs_with_migration_match_single_state():
+    world, port = 2, free_port()
+    with mp.Manager() as mgr:
+        ret = mgr.dict()
+        ps = [mp.Process(target=_gloo_worker, args=(r, world, port, ret)) for r in range(world)]
+        [p.start() for p in ps]
+        [p.join(180) for p in ps]
+        assert all(p.exitcode == 0 for p in ps), [p.exitcode for p in ps]
+        res = dict(ret)
+    dtype = np.float64
+    pos, vel, vol = moving_block(dtype)
+    full = O.OracleMpm(dtype)
+    full.AddParticles(pos, vel, vol, **MAT)
+    full.Finalize()
+    for it in range(40):
+        full.substep(DT, -1, it % 7 == 0)
+    ref = np.empty((len(pos), 3))
+    ref[full.read("pids")] = full.read("positions").reshape(-1, 3)
+    got = np.full((len(pos), 3), np.nan)
+    for r in range(world):
+        got[res[r][0]] = res[r][1]
+    assert res[0][2] == res[1][2] > 100
+    assert not np.isnan(got).any() and np.max(np.abs(got - ref)) <= 1e-12
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype,tol,world", [(np.float64, 1e-10, 2), (np.float64, 1e-10, 3), (np.float32, 5e-4, 2)])
+def test_gpu_slabs_with_migration_match_single_state_and_oracle(dtype, tol, world):
+    import torch
+    from drake_b200.gpu_mpm import GpuMpmSolver, GpuMpmState
+    sv = GpuMpmSolver()
+    parts_box = []
+
+    def sync_all():
+        for s in parts_box:
+            sv.GpuSync(s)
+        torch.cuda.synchronize()
+
+    def make_state():
+        s = GpuMpmState(dtype)
+        parts_box.append(s)
+        return s
+
+    def step(parts, ex, it):
+        for s in parts:
+            sv.RebuildMapping(s, it % 7 == 0); sv.CalcFemStateAndForce(s, DT); sv.ParticleToGrid(s, DT)
+        ex.exchange()
+        for s in parts:
+            sv.UpdateGrid(s, -1); sv.GridToParticle(s, DT)
+
+    parts, migs, moved, (pos, vel, vol) = run_split(make_state, slab.GpuHaloBackend, step, dtype, world, steps=60,
+                                                    every=4, sync=sync_all)
+    assert moved > len(pos) // 10
+    full, orc = GpuMpmState(dtype), O.OracleMpm(dtype)
+    for s in (full, orc):
+        s.AddParticles(pos, vel, vol, **MAT)
+        s.Finalize()
+    for it in range(60):
+        s = it % 7 == 0
+        sv.RebuildMapping(full, s); sv.CalcFemStateAndForce(full, DT); sv.ParticleToGrid(full, DT)
+        sv.UpdateGrid(full, -1); sv.GridToParticle(full, DT)
+        orc.substep(DT, -1, s)
+    got = gathered(parts, migs, len(pos))
+    for ref_state in (full, orc):
+        ref = np.empty((len(pos), 3))
+        ref[ref_state.read("pids")] = np.asarray(ref_state.read("positions"), np.float64).reshape(-1, 3)
+        assert np.max(np.abs(got - ref)) <= tol * np.max(np.abs(ref))
+    gotF = gathered(parts, migs, len(pos), "particle_F_by_pid", 9) if False else None
+    gids = np.concatenate([m.gid[m.gid >= 0] for m in migs])
+    assert np.array_equal(np.sort(gids), np.arange(len(pos)))
+    # the inactive particles stay parked and massless
+    for st, m in zip(parts, migs):
+        vol_by_pid = np.empty(st.n_particles())
+        vol_by_pid[st.read("pids")] = st.read("volumes")
+        assert np.all(vol_by_pid[m.gid < 0] == 0) and np.all(vol_by_pid[m.gid >= 0] > 0)
+    for s in parts + [full]:
+        s.Destroy()
