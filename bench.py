@@ -84,7 +84,15 @@ def scene_params(world):
     return {} if world == 1 else {"domain_bits": 8, "dx": DX}
 
 
-def add_rank_bodies(st, dtype, r, world):
+SPARE_FRACTION = 0.25      # cfg3, N > 1: inactive particles per rank that arrivals of the migration take over
+MIGRATE_EVERY = 16
+
+
+def park_of(rank):
+    return np.array([4.5 * DX, 4.5 * DX, (4.5 + 8 * rank) * DX])
+
+
+def add_rank_bodies(st, dtype, r, world, spare=False):
     """The part of the scene rank r owns, added to `st` (GpuMpmState, OracleMpm or RefMpm: same method names)."""
     from drake_b200 import scenes
     col, lvl = r // 2, r % 2
@@ -109,6 +117,9 @@ def add_rank_bodies(st, dtype, r, world):
         hi = np.array([0.19 + c1 * DX, 0.19 + 80 * DX, 3 * DX + 0.5 * DX + 78 * DX])
         pos, vel, vol = scenes.particle_block(lo, hi, dx=DX, dtype=dtype, seed=scenes.SEED + r)
         st.AddParticles(pos, vel, vol, "drucker_prager", E_BLOCK, NU_BLOCK, 30.0, 0.0)
+        if spare and world > 1:   # position-owned x-slabs: room for the particles that migrate in (slab.SlabMigrator)
+            n = int(len(pos) * SPARE_FRACTION)
+            st.AddParticles(np.tile(park_of(r), (n, 1)), np.zeros((n, 3)), 0.0, "drucker_prager", E_BLOCK, NU_BLOCK, 30.0, 0.0)
     elif CFG == "cfg5":
         off = np.array([r & 1, (r >> 1) & 1, (r >> 2) & 1], np.float64) * 100 * DX
         lo = np.array([0.5, 0.5, 0.3]) + off
@@ -116,11 +127,11 @@ def add_rank_bodies(st, dtype, r, world):
         st.AddParticles(pos, vel, vol, "fixed_corotated", E_BLOCK, NU_BLOCK)
 
 
-def build_scene(cls_factory, dtype, rank=0, world=1):
+def build_scene(cls_factory, dtype, rank=0, world=1, spare=False):
     """`rank` may be a list: the parts of several ranks in ONE state (the merged scene of the parity pass)."""
     st = cls_factory()
     for r in (rank if isinstance(rank, (list, tuple)) else [rank]):
-        add_rank_bodies(st, dtype, r, world)
+        add_rank_bodies(st, dtype, r, world, spare)
     st.Finalize()
     return st
 
@@ -164,7 +175,7 @@ def parity_single(st, dtype, steps):
     return out
 
 
-def parity_multi(st, dtype, steps, rank, world, local, make_state):
+def parity_multi(st, dtype, steps, rank, world, local, make_state, mig=None):
     """N > 1: this rank's particles after `steps` substeps of the multi-rank path (fused peer-window exchange) against
     ONE state holding the merged scene of every rank that can interact with it, stepped on this GPU without any
     exchange.  Particles are matched by their original ids (the merged state numbers [faces | verts | volumetric] over
@@ -192,6 +203,9 @@ def parity_multi(st, dtype, steps, rank, world, local, make_state):
         counts = [int(t[g]) for g in group]
         o = sum(counts[:group.index(rank)])
         ref = mv[o:o + mine.shape[0]]
+        if mig is not None:   # migrating slabs: local ids are slots that change hands; match by scene-wide id
+            act = mig.gid >= 0
+            mine, ref = mine[act], mv[mig.gid[act]]
     merged.Destroy()
     return _rel(mine, ref)
 
@@ -469,15 +483,30 @@ def main():
     from drake_b200.gpu_mpm import GpuMpmSolver, GpuMpmState, MpmParticleContactPairs
     dtype = np.float64 if args.dtype == "f64" else np.float32
     T = np.dtype(dtype).itemsize
-    st = build_scene(lambda: GpuMpmState(dtype, device=local, **scene_params(world)), dtype, rank, world)
+    st = build_scene(lambda: GpuMpmState(dtype, device=local, **scene_params(world)), dtype, rank, world, spare=True)
     sv = GpuMpmSolver()
     N = st.n_particles()
+    n_spare = int((N / (1 + SPARE_FRACTION)) * SPARE_FRACTION + 0.5) if (CFG == "cfg3" and world > 1) else 0
+    N -= n_spare                                           # throughput counts the particles of the scene only
     K, W = args.steps, args.warmup
     ex = None
     if world > 1:
         from drake_b200 import slab
         peer = world <= 8 and not args.no_peer             # block sums through peer-memory windows (csrc/halo.cuh)
-        ex = slab.SlabExchange(slab.GpuHaloBackend(st), peer=peer, peer_cap_blocks=32768 if CFG == "cfg5" else 8192)
+        backend = slab.GpuHaloBackend(st)
+        ex = slab.SlabExchange(backend, peer=peer, peer_cap_blocks=32768 if CFG == "cfg5" else 8192)
+    mig = None
+    if world > 1 and CFG == "cfg3":
+        # position-owned x-slabs: scene-wide ids = the merged scene's particle order (ranks in turn)
+        counts = torch.zeros(world, dtype=torch.int64, device="cuda")
+        counts[rank] = N
+        dist.all_reduce(counts)
+        off = int(counts[:rank].sum())
+        gid = np.concatenate([np.arange(off, off + N), -np.ones(n_spare, np.int64)])
+        edges = np.array([0.19 + (80 * r // world) * DX for r in range(1, world)])
+        mig = slab.SlabMigrator(st, rank, world, edges, gid, park_of(rank), margin=2 * DX, cap=max(1, n_spare),
+                                all_gather=slab.dist_all_gather())
+    migrated = [0]
 
     # interior UpdateGrid/G2P work hides the all-reduce; pays off once the collective is slow (measured: loses
     # 20 us at 2 ranks, wins 18 us at 8)
@@ -489,6 +518,12 @@ def main():
             return
         for i in range(first, first + n):                  # the exchange sits between P2G and UpdateGrid
             slab.substep(sv, st, ex, DT, -1, i % SORT_EVERY == 0, overlap=overlap)
+            if mig is not None and (i + 1) % MIGRATE_EVERY == 0:
+                moved = mig.migrate()                      # collective; the count is the same on every rank
+                migrated[0] += moved
+                if moved:
+                    ex.planned = False                     # plan afresh after the next P2G, as at start-up
+                    backend.reset_plan()
 
     # host slack: the only call of the substep that can block is the start of the exchange (it waits for the
     # plan issued one substep earlier); time spent there = how far the host runs ahead of the device
@@ -517,7 +552,7 @@ def main():
             parity["ok"] = bool(worst <= tol and parity["pids_equal"])
         else:
             mine = parity_multi(st, dtype, P, rank, world, local,
-                                lambda: GpuMpmState(dtype, device=local, **scene_params(world)))
+                                lambda: GpuMpmState(dtype, device=local, **scene_params(world)), mig)
             if mine is None:
                 parity = {"unchecked": "the merged scene of all interacting ranks does not fit one GPU check"}
             else:
@@ -678,6 +713,9 @@ def main():
                                       "what": "the same loop as upstream issues it: all positions to the host every substep"},
                 "gpu_launches": launches_all, "gpu_launches_per_step": launches_all / K / world,
                 "roofline": roofline, "kernels": kern, "parity": parity}
+        if mig is not None:
+            line["migration"] = {"every_substeps": MIGRATE_EVERY, "particles_moved_total": int(migrated[0]),
+                                 "spare_fraction": SPARE_FRACTION, "margin_cells": 2}
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_baseline(dtype)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "flags")}
