@@ -88,8 +88,11 @@ SPARE_FRACTION = 0.25      # cfg3, N > 1: inactive particles per rank that arriv
 MIGRATE_EVERY = 16
 
 
-def park_of(rank):
-    return np.array([4.5 * DX, 4.5 * DX, (4.5 + 8 * rank) * DX])
+def park_of(rank, world):
+    """cfg3: the inactive particles of a rank wait scattered over the lower part of its own x-slab (massless: they
+    add nothing to the grid, and they touch no block another rank would not share anyway)."""
+    c0, c1 = 80 * rank // world, 80 * (rank + 1) // world
+    return np.array([0.19 + (c0 + 1) * DX, 0.19 + DX, 4.5 * DX, 0.19 + (c1 - 1) * DX, 0.19 + 79 * DX, 40.5 * DX])
 
 
 def add_rank_bodies(st, dtype, r, world, spare=False):
@@ -119,7 +122,9 @@ def add_rank_bodies(st, dtype, r, world, spare=False):
         st.AddParticles(pos, vel, vol, "drucker_prager", E_BLOCK, NU_BLOCK, 30.0, 0.0)
         if spare and world > 1:   # position-owned x-slabs: room for the particles that migrate in (slab.SlabMigrator)
             n = int(len(pos) * SPARE_FRACTION)
-            st.AddParticles(np.tile(park_of(r), (n, 1)), np.zeros((n, 3)), 0.0, "drucker_prager", E_BLOCK, NU_BLOCK, 30.0, 0.0)
+            from drake_b200 import slab
+            st.AddParticles(slab.park_points(park_of(r, world), n), np.zeros((n, 3)), 0.0, "drucker_prager", E_BLOCK, NU_BLOCK,
+                            30.0, 0.0)
     elif CFG == "cfg5":
         off = np.array([r & 1, (r >> 1) & 1, (r >> 2) & 1], np.float64) * 100 * DX
         lo = np.array([0.5, 0.5, 0.3]) + off
@@ -504,7 +509,7 @@ def main():
         off = int(counts[:rank].sum())
         gid = np.concatenate([np.arange(off, off + N), -np.ones(n_spare, np.int64)])
         edges = np.array([0.19 + (80 * r // world) * DX for r in range(1, world)])
-        mig = slab.SlabMigrator(st, rank, world, edges, gid, park_of(rank), margin=2 * DX, cap=max(1, n_spare),
+        mig = slab.SlabMigrator(st, rank, world, edges, gid, park_of(rank, world), margin=2 * DX, cap=max(1, n_spare),
                                 all_gather=slab.dist_all_gather())
     migrated = [0]
 

@@ -4,7 +4,7 @@
 //
 // Ownership of a VOLUMETRIC particle may change hands (cloth meshes stay whole: a triangle gathers its vertices by
 // index, cuda_mpm_kernels.cuh:183-294).  A state is created with spare INACTIVE particles -- rest volume 0, parked
-// in a corner cell: they carry no mass and no stress, so every transfer sees them as zeros -- and migration swaps
+// at scattered points of a parking box: they carry no mass and no stress, so every transfer sees them as zeros -- and migration swaps
 // roles: a leaver's record (pos 3, vel 3, C 9, volume, F 9, material index = 26 scalars) is copied out and its slot
 // becomes inactive; an arrival takes over an inactive slot (and its local particle id).  The transport between the
 // ranks is the host layer's (drake_b200/slab.py: torch.distributed).  Results do not depend on who owns a particle
@@ -17,8 +17,21 @@ namespace gmpm {
 
 constexpr int kMigrateRecord = 26;
 
+struct ParkBox {
+  double lo[3], hi[3];
+};
+// Where inactive particle q waits: a low-discrepancy point (R3 sequence) of the parking box, so that the massless
+// particles never pile up in one grid block (a block with 10^5 particles is 10^3 P2G tiles to sum).
+__host__ __device__ inline void park_position(const ParkBox& b, uint32_t q, double (&x)[3]) {
+  const double a[3] = {0.8191725133961645, 0.6710436067037893, 0.5497004779019703};
+  for (int d = 0; d < 3; ++d) {
+    const double t = (double)(q + 1u) * a[d];
+    x[d] = b.lo[d] + (t - floor(t)) * (b.hi[d] - b.lo[d]);
+  }
+}
+
 template <typename T>
-__global__ void migrate_out_kernel(uint32_t N, uint32_t n_cloth, int axis, T lo, T hi, T px, T py, T pz,
+__global__ void migrate_out_kernel(uint32_t N, uint32_t n_cloth, int axis, T lo, T hi, ParkBox park,
                                    const int* __restrict__ pid, T* __restrict__ pos, T* __restrict__ vel,
                                    T* __restrict__ C, T* __restrict__ vol, T* __restrict__ Fv,
                                    const uint8_t* __restrict__ mat_id, uint32_t cap, uint32_t* __restrict__ count,
@@ -49,7 +62,9 @@ __global__ void migrate_out_kernel(uint32_t N, uint32_t n_cloth, int axis, T lo,
   r[25] = T(mat_id[q]);
   out_pid[o] = (int)p;
   // the slot becomes an inactive particle
-  pos[s] = px; pos[(size_t)N + s] = py; pos[(size_t)2 * N + s] = pz;
+  double pk[3];
+  park_position(park, q, pk);
+  pos[s] = T(pk[0]); pos[(size_t)N + s] = T(pk[1]); pos[(size_t)2 * N + s] = T(pk[2]);
 #pragma unroll
   for (int d = 0; d < 3; ++d) vel[(size_t)d * N + s] = T(0);
 #pragma unroll
@@ -121,7 +136,12 @@ size_t State<T>::migrate_out(int axis, T lo, T hi, const T* park, T* records, in
   int* d_pid = reinterpret_cast<int*>(buf + 16 + rec_bytes);
   GMPM_CUDA(cudaMemsetAsync(d_count, 0, sizeof(uint32_t), stream));
   launch("migrate_out");
-  migrate_out_kernel<T><<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, n_cloth(), axis, lo, hi, park[0], park[1], park[2],
+  ParkBox box;
+  for (int d = 0; d < 3; ++d) {
+    box.lo[d] = (double)park[d];
+    box.hi[d] = (double)park[3 + d];
+  }
+  migrate_out_kernel<T><<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, n_cloth(), axis, lo, hi, box,
                                                                pid[cur], pos[cur], vel[cur], C[cur], vol[cur], Fv, mat_id,
                                                                (uint32_t)cap, d_count, d_rec, d_pid);
   GMPM_CUDA(cudaGetLastError());

@@ -324,6 +324,14 @@ def slab_edges(positions, world, axis=0):
     return np.array([x[(len(x) * r) // world] for r in range(1, world)], np.float64)
 
 
+def park_points(park, n, start=0):
+    """n scattered points of the parking box (the sequence migrate_out uses, csrc/migrate.cuh park_position)."""
+    park = np.asarray(park, np.float64).reshape(6)
+    a = np.array([0.8191725133961645, 0.6710436067037893, 0.5497004779019703])
+    t = (np.arange(start, start + n, dtype=np.float64)[:, None] + 1.0) * a
+    return park[:3] + (t - np.floor(t)) * (park[3:] - park[:3])
+
+
 def owner_of(x, edges):
     return np.searchsorted(np.asarray(edges, np.float64), np.asarray(x, np.float64), side="right")
 
@@ -331,7 +339,8 @@ def owner_of(x, edges):
 class SlabMigrator:
     """Keeps the volumetric particles of ONE rank inside its slab [edges[rank-1] - margin, edges[rank] + margin).
 
-    The state must have been created with spare inactive particles (AddParticles with volume 0 at `park`).  `gid` maps
+    The state must have been created with spare inactive particles (AddParticles with volume 0, scattered over the
+    parking box `park` = lo xyz, hi xyz inside the rank's own slab: see park_points).  `gid` maps
     the state's local particle ids to scene-wide ids (-1: inactive) so that results can be compared across
     decompositions.  migrate() is collective: every rank calls it between GridToParticle and the next RebuildMapping,
     every `every` substeps; `all_gather` is torch.distributed.all_gather_object-like (list of per-rank objects).
@@ -342,7 +351,7 @@ class SlabMigrator:
         self.state, self.rank, self.world = state, rank, world
         self.edges = np.asarray(edges, np.float64)
         self.gid = np.asarray(gid, np.int64).copy()
-        self.park = np.asarray(park, np.float64)
+        self.park = np.asarray(park, np.float64).reshape(6)   # parking box of the inactive particles: lo xyz, hi xyz
         self.axis, self.margin, self.cap = axis, float(margin), int(cap)
         self.all_gather = all_gather
         self.moved_out = self.moved_in = 0

@@ -133,7 +133,8 @@ int gmpm_device_sync(void);
   /* position-owned decomposition.  A state is given spare INACTIVE particles (gmpm_add_particles      */\
   /* with volume 0).  migrate_out copies out the active volumetric particles whose coordinate `axis`   */\
   /* lies outside [lo, hi) -- 26 scalars each: pos 3, vel 3, C 9, volume, F 9, material index -- with  */\
-  /* their local particle ids, sorted by id, and turns their slots inactive (parked at park[3]);       */\
+  /* their local particle ids, sorted by id, and turns their slots inactive (parked at a scattered    */\
+  /* point of the box park[6] = lo xyz, hi xyz: choose it inside the state's own slab);                */\
   /* at most cap (the others stay for the next call).  migrate_in hands n such records to inactive     */\
   /* slots (pids <- the local ids they took; may be null).  Both belong between GridToParticle and     */\
   /* the next RebuildMapping; all states of a scene must declare their materials in the same order.    */\

@@ -27,13 +27,14 @@ def moving_block(dtype, cells=(10, 6, 6)):
 
 
 def park_of(rank):
-    return np.array([4.5 * DX, 4.5 * DX, (4.5 + 8 * rank) * DX])
+    """Parking box of rank's inactive particles: a slab of cells off to the side of the scene."""
+    return np.array([4.5 * DX, 4.5 * DX, (4.5 + 12 * rank) * DX, 24.5 * DX, 24.5 * DX, (12.5 + 12 * rank) * DX])
 
 
 def make_part(factory, dtype, pos, vel, vol, mine, rank, spare):
     st = factory()
     st.AddParticles(pos[mine], vel[mine], vol, **MAT)
-    st.AddParticles(np.tile(park_of(rank), (spare, 1)), np.zeros((spare, 3)), 0.0, **MAT)
+    st.AddParticles(slab.park_points(park_of(rank), spare), np.zeros((spare, 3)), 0.0, **MAT)
     st.Finalize()
     gid = np.concatenate([np.nonzero(mine)[0], -np.ones(spare, np.int64)])
     return st, gid
