@@ -67,6 +67,9 @@ template <typename T> struct Abi;
     static constexpr auto create = gmpm_create_##SUF;                                                \
     static constexpr auto destroy = gmpm_destroy_##SUF;                                              \
     static constexpr auto add_qr_cloth = gmpm_add_qr_cloth_##SUF;                                    \
+    static constexpr auto add_particles = gmpm_add_particles_##SUF;                                  \
+    static constexpr auto migrate_out = gmpm_migrate_out_##SUF;                                      \
+    static constexpr auto migrate_in = gmpm_migrate_in_##SUF;                                        \
     static constexpr auto finalize = gmpm_finalize_##SUF;                                            \
     static constexpr auto rebuild_mapping = gmpm_rebuild_mapping_##SUF;                              \
     static constexpr auto calc_fem = gmpm_calc_fem_##SUF;                                            \
@@ -140,6 +143,32 @@ struct GpuMpmState {
                                       reinterpret_cast<const T*>(vel.data()), pos.size(), indices.data(),
                                       indices.size() / 3),
                     "AddQRCloth");
+  }
+  // Extension: a particle-only body with a volumetric material (gmpm_material: fixed corotated,
+  // StVK-Hencky, Drucker-Prager).  Generalises AddQRCloth; `volume` is the rest volume of each particle.
+  void AddParticles(const std::vector<Vec3<T>>& pos, const std::vector<Vec3<T>>& vel, const std::vector<T>& volume,
+                    const gmpm_material& material) {
+    if (!h_) Create(nullptr);
+    if (pos.size() != vel.size() || pos.size() != volume.size()) throw std::invalid_argument("AddParticles: inconsistent sizes");
+    internal::Check(Abi::add_particles(raw(), reinterpret_cast<const T*>(pos.data()), reinterpret_cast<const T*>(vel.data()),
+                                       volume.data(), pos.size(), &material),
+                    "AddParticles");
+  }
+  // Extension: particle migration between the states of a position-owned decomposition; 26 scalars
+  // per record (gmpm_c.h).  Returns the number of particles that left / the local ids the arrivals took.
+  size_t MigrateOut(int axis, T lo, T hi, const T (&park_box)[6], std::vector<T>* records, std::vector<int>* pids, size_t cap) {
+    records->resize(cap * 26);
+    pids->resize(cap);
+    size_t n = 0;
+    internal::Check(Abi::migrate_out(raw(), axis, lo, hi, park_box, records->data(), pids->data(), cap, &n), "MigrateOut");
+    records->resize(n * 26);
+    pids->resize(n);
+    return n;
+  }
+  std::vector<int> MigrateIn(const std::vector<T>& records) {
+    std::vector<int> pids(records.size() / 26);
+    internal::Check(Abi::migrate_in(raw(), records.data(), pids.size(), pids.data()), "MigrateIn");
+    return pids;
   }
   // cuda_mpm_model.cu:36-122: every device allocation happens here.
   void Finalize() {

@@ -44,6 +44,7 @@ struct Vec3 {
   const T* data() const { return v; }
   static Vec3 Zero() { return Vec3(); }
   Vec3& operator/=(T s) { v[0] /= s; v[1] /= s; v[2] /= s; return *this; }
+  template <typename U> Vec3<U> cast() const { return Vec3<U>(U(v[0]), U(v[1]), U(v[2])); }  // Eigen's .cast<U>()
 };
 #endif
 static_assert(sizeof(Vec3<float>) == 3 * sizeof(float) && sizeof(Vec3<double>) == 3 * sizeof(double),

@@ -26,5 +26,38 @@ def build(force=False):
     return OUT
 
 
+REF_DRIVER = "/root/reference/multibody/plant/deformable_driver.h"
+EXCERPT = os.path.join(HERE, "_build", "driver_excerpt.inc")
+OUT_EXCERPT = os.path.join(HERE, "_build", "test_driver_excerpt")
+
+
+def build_excerpt(force=False):
+    """The drop-in compile proof: deformable_driver.h:196-271 (the MPM method bodies) extracted from the reference
+    tree WHERE IT LIES into the git-ignored _build/ directory and compiled against include/.  Only possible where
+    /root/reference exists (the build container); the binary travels to the GPU box.  Returns the path or None."""
+    src = os.path.join(HERE, "test_driver_excerpt.cc")
+    if not os.path.exists(REF_DRIVER):
+        return OUT_EXCERPT if os.path.exists(OUT_EXCERPT) else None
+    deps = [src, REF_DRIVER, os.path.join(ROOT, "drake_b200", "lib", "libgmpm_b200.so")]
+    deps += [os.path.join(ROOT, "include", "multibody", "gpu_mpm", f) for f in os.listdir(os.path.join(ROOT, "include", "multibody", "gpu_mpm"))]
+    if not force and os.path.exists(OUT_EXCERPT) and os.path.getmtime(OUT_EXCERPT) >= max(os.path.getmtime(d) for d in deps):
+        return OUT_EXCERPT
+    os.makedirs(os.path.dirname(EXCERPT), exist_ok=True)
+    lines = open(REF_DRIVER).read().split("\n")
+    with open(EXCERPT, "w") as f:
+        f.write("// generated at build time from %s lines 196-271 (not part of the repository)\n" % REF_DRIVER)
+        f.write("\n".join(lines[195:271]) + "\n")
+    gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    cmd = [gxx, "-std=c++17", "-O2", "-Wall", "-Wno-unused-variable", "-Wno-unused-parameter", "-Wno-format",
+           "-I" + os.path.join(ROOT, "include"), "-I" + os.path.dirname(EXCERPT), src, "-o", OUT_EXCERPT,
+           "-L" + os.path.join(ROOT, "drake_b200", "lib"), "-lgmpm_b200", "-Wl,-rpath,$ORIGIN/../../../drake_b200/lib"]
+    env = dict(os.environ)
+    env.pop("CC", None)
+    env.pop("CXX", None)
+    subprocess.check_call(cmd, env=env)
+    return OUT_EXCERPT
+
+
 if __name__ == "__main__":
+    print(build_excerpt(force=True))
     print(build(force=True))

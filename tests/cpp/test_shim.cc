@@ -34,6 +34,15 @@ void instantiate_extensions(GpuMpmState<S>* st, const GpuMpmSolver<S>& sv) {
   sv.GenerateContactPairs(st, geoms);
   sv.RunDriverSubsteps(st, 1, S(1e-3), geoms, -1, 0, 1, S(0), S(0), S(0), false);
   st->LoadState(st->SaveState());
+  gmpm_material mat{GMPM_MAT_DRUCKER_PRAGER, 0, 1e5, 0.3, 30.0, 0.0};
+  st->AddParticles({}, {}, {}, mat);
+  std::vector<S> rec;
+  std::vector<int> pids;
+  const S box[6] = {0, 0, 0, 1, 1, 1};
+  st->MigrateOut(0, S(0), S(1), box, &rec, &pids, 0);
+  st->MigrateIn(rec);
+  st->SetContactQueryBounds({});
+  st->ClearContactQueryBounds();
 }
 template void instantiate_extensions<float>(GpuMpmState<float>*, const GpuMpmSolver<float>&);
 template void instantiate_extensions<double>(GpuMpmState<double>*, const GpuMpmSolver<double>&);
