@@ -631,7 +631,9 @@ __device__ __forceinline__ uint32_t p2g_derive(const P2GRaw<T>& r, T* row, T dt,
   if ((b[0] & 3u) >= 2u) reach |= reach << 4;
   if ((b[1] & 3u) >= 2u) reach |= reach << 2;
   if ((b[2] & 3u) >= 2u) reach |= reach << 1;
-  return reach;
+  // a massless particle (an inactive spare of the migration, csrc/migrate.cuh) deposits zeros: it must not make a
+  // grid block "touched" -- the exchange plans the reachable blocks from the mass on the grid
+  return mass > T(0) ? reach : 0u;
 }
 
 template <typename T>

@@ -144,7 +144,9 @@ __device__ __forceinline__ uint32_t p2g_derive_col(const P2GRaw<T>& r, unsigned 
   if ((b[0] & 3u) >= 2u) reach |= reach << 4;
   if ((b[1] & 3u) >= 2u) reach |= reach << 2;
   if ((b[2] & 3u) >= 2u) reach |= reach << 1;
-  return reach;
+  // a massless particle (an inactive spare of the migration, csrc/migrate.cuh) deposits zeros: it must not make a
+  // grid block "touched" -- the exchange plans the reachable blocks from the mass on the grid
+  return mass > T(0) ? reach : 0u;
 }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }

@@ -13,6 +13,7 @@
 #include "halo.cuh"
 #include "kernels.cuh"
 #include "p2g_col.cuh"
+#include "p2g_pair.cuh"
 #include "volumetric.cuh"
 #include "sort.cuh"
 
@@ -260,6 +261,7 @@ struct State {
   int sm_count = 148;
   static constexpr int kP2GDefault = 0;  // 0 tile (default: fastest at fp32, within 3 % at fp64), 1 column, 2 column + bulk tile store (profiles/r02_p2g_ab.txt)
   int p2g_variant = kP2GDefault;
+  int p2g_threads = kP2GThreads;
   size_t p2g_smem = 0;
   int p2g_ctas_per_sm = 1, g2p_ctas_per_sm = 1, fem_ctas_per_sm = 1, bin_ctas = 0, sort_ctas = 0;
   bool g2p_queue_ready = false;
@@ -540,12 +542,15 @@ struct State {
     }
     {
       const char* v = std::getenv("GMPM_P2G");  // A/B switch: "tile" (round-1 kernel), "col", "colbulk"
-      p2g_variant = !v ? kP2GDefault : !std::strcmp(v, "tile") ? 0 : !std::strcmp(v, "col") ? 1 : 2;
+      p2g_variant = !v ? kP2GDefault : !std::strcmp(v, "tile") ? 0 : !std::strcmp(v, "col") ? 1
+                                       : !std::strcmp(v, "colbulk") ? 2 : 3;
       const void* fn = p2g_variant == 0 ? (const void*)p2g_tile_kernel<T>
-                       : p2g_variant == 1 ? (const void*)p2g_col_kernel<T, false> : (const void*)p2g_col_kernel<T, true>;
-      p2g_smem = p2g_variant == 0 ? sizeof(P2GSmem<T>) : sizeof(P2GColSmem<T>);
+                       : p2g_variant == 1 ? (const void*)p2g_col_kernel<T, false>
+                       : p2g_variant == 2 ? (const void*)p2g_col_kernel<T, true> : (const void*)p2g_pair_kernel<T>;
+      p2g_smem = p2g_variant == 0 ? sizeof(P2GSmem<T>) : p2g_variant == 3 ? sizeof(P2GPairSmem<T>) : sizeof(P2GColSmem<T>);
+      p2g_threads = p2g_variant == 3 ? kP2GPairThreads : kP2GThreads;
       GMPM_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p2g_smem));
-      GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p2g_ctas_per_sm, fn, kP2GThreads, p2g_smem));
+      GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p2g_ctas_per_sm, fn, p2g_threads, p2g_smem));
       if (p2g_ctas_per_sm < 1) throw CudaError(cudaErrorLaunchOutOfResources, "the P2G kernel does not fit on an SM");
     }
     GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g2p_ctas_per_sm, g2p_kernel<T>, kG2PWarps * 32, 0));
@@ -742,8 +747,10 @@ struct State {
       p2g_tile_kernel<T><<<persistent_ctas(p2g_ctas_per_sm), kP2GThreads, p2g_smem, stream>>>(GMPM_P2G_ARGS);
     else if (p2g_variant == 1)
       p2g_col_kernel<T, false><<<persistent_ctas(p2g_ctas_per_sm), kP2GThreads, p2g_smem, stream>>>(GMPM_P2G_ARGS);
-    else
+    else if (p2g_variant == 2)
       p2g_col_kernel<T, true><<<persistent_ctas(p2g_ctas_per_sm), kP2GThreads, p2g_smem, stream>>>(GMPM_P2G_ARGS);
+    else
+      p2g_pair_kernel<T><<<persistent_ctas(p2g_ctas_per_sm), kP2GPairThreads, p2g_smem, stream>>>(GMPM_P2G_ARGS);
 #undef GMPM_P2G_ARGS
     g2p_queue_ready = true;  // the prologue reset both work queues
     launch("clean_stale_blocks");
