@@ -85,7 +85,7 @@ def scene_params(world):
 
 
 SPARE_FRACTION = 0.25      # cfg3, N > 1: inactive particles per rank that arrivals of the migration take over
-MIGRATE_EVERY = 16
+MIGRATE_EVERY = 32
 
 
 def park_of(rank, world):
@@ -499,7 +499,7 @@ def main():
         from drake_b200 import slab
         peer = world <= 8 and not args.no_peer             # block sums through peer-memory windows (csrc/halo.cuh)
         backend = slab.GpuHaloBackend(st)
-        ex = slab.SlabExchange(backend, peer=peer, peer_cap_blocks=32768 if CFG == "cfg5" else 8192)
+        ex = slab.SlabExchange(backend, peer=peer, peer_cap_blocks={"cfg5": 32768, "cfg3": 16384}.get(CFG, 8192))
     mig = None
     if world > 1 and CFG == "cfg3":
         # position-owned x-slabs: scene-wide ids = the merged scene's particle order (ranks in turn)

@@ -188,7 +188,9 @@ void State<T>::migrate_in(const T* records, size_t n, int* pids_out) {
                              " inactive particles left: create the state with more spare particles (volume 0)");
   std::vector<uint32_t> slots(n_free);
   to_host(slots.data(), d_slots, sizeof(uint32_t) * n_free);
-  std::sort(slots.begin(), slots.end());
+  // the n lowest free slots, ascending (reproducible assignment) -- without sorting the whole free list
+  std::nth_element(slots.begin(), slots.begin() + (n - 1), slots.end());
+  std::sort(slots.begin(), slots.begin() + n);
   GMPM_CUDA(cudaMemcpyAsync(d_slots, slots.data(), sizeof(uint32_t) * n, cudaMemcpyHostToDevice, stream));
   GMPM_CUDA(cudaMemcpyAsync(d_rec, records, sizeof(T) * kMigrateRecord * n, cudaMemcpyHostToDevice, stream));
   launch("migrate_in");

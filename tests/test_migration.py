@@ -221,3 +221,36 @@ def test_gpu_slabs_with_migration_match_single_state_and_oracle(dtype, tol, worl
         assert np.all(vol_by_pid[m.gid < 0] == 0) and np.all(vol_by_pid[m.gid >= 0] > 0)
     for s in parts + [full]:
         s.Destroy()
+
+
+@pytest.mark.gpu
+def test_inactive_particles_are_invisible_to_the_grid():
+    """Spare particles of volume 0 deposit nothing and do not mark grid blocks as touched (the exchange plans the
+    reachable blocks from the mass on the grid): a state with spares parked far from the body steps exactly like one
+    without, and its touched-block set is the same."""
+    from drake_b200.gpu_mpm import GpuMpmSolver, GpuMpmState
+    dtype = np.float64
+    pos, vel, vol = moving_block(dtype)
+    sv = GpuMpmSolver()
+    outs = []
+    for spare in (0, 5000):
+        st = GpuMpmState(dtype)
+        st.AddParticles(pos, vel, vol, **MAT)
+        if spare:
+            st.AddParticles(slab.park_points([0.7, 0.7, 0.7, 0.9, 0.9, 0.9], spare), np.zeros((spare, 3)), 0.0, **MAT)
+        st.Finalize()
+        for it in range(8):
+            sv.RebuildMapping(st, it == 3); sv.CalcFemStateAndForce(st, DT); sv.ParticleToGrid(st, DT)
+            if it == 7:
+                flags = st.read("grid_touched_flags").copy()
+                mass = st.read("grid_masses").copy()
+            sv.UpdateGrid(st, -1); sv.GridToParticle(st, DT)
+        v = np.asarray(st.read("positions")).reshape(-1, 3)
+        by_pid = np.empty_like(v)
+        by_pid[st.read("pids")] = v
+        outs.append((flags, mass, by_pid[:len(pos)], by_pid[len(pos):]))
+        st.Destroy()
+    assert np.array_equal(outs[0][0], outs[1][0]) and outs[0][0].sum() > 0
+    assert np.array_equal(outs[0][1], outs[1][1])
+    assert np.max(np.abs(outs[0][2] - outs[1][2])) <= 1e-13
+    assert np.array_equal(outs[1][3], slab.park_points([0.7, 0.7, 0.7, 0.9, 0.9, 0.9], 5000))   # the spares never moved
