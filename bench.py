@@ -85,6 +85,7 @@ def scene_params(world):
 
 
 SPARE_FRACTION = 0.25      # cfg3, N > 1: inactive particles per rank that arrivals of the migration take over
+                           # (set to 1.0 at 8 ranks: the collapsing column piles up in the 10-cell edge slabs)
 MIGRATE_EVERY = 32
 
 
@@ -444,6 +445,8 @@ def main():
                     help="BASELINE.json config (default cfg2 = the driver's line; the others are builder runs)")
     ap.add_argument("--parity-steps", type=int, default=20,
                     help="substeps of the fresh scene checked against the oracle before the timed region (0 = off)")
+    ap.add_argument("--no-final-parity", action="store_true",
+                    help="cfg3, N>1: skip the check of the final state against the merged single-GPU run")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-gpu", action="store_true")
     ap.add_argument("--no-f32", action="store_true", help="skip the fp32 (reference product dtype) sub-line")
@@ -455,6 +458,9 @@ def main():
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     set_config(args.config)
+    global SPARE_FRACTION
+    if env_int("WORLD_SIZE", 1) >= 8:
+        SPARE_FRACTION = 1.0
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
 
     if args.impl == "reference":
@@ -510,7 +516,7 @@ def main():
         gid = np.concatenate([np.arange(off, off + N), -np.ones(n_spare, np.int64)])
         edges = np.array([0.19 + (80 * r // world) * DX for r in range(1, world)])
         mig = slab.SlabMigrator(st, rank, world, edges, gid, park_of(rank, world), margin=2 * DX, cap=max(1, n_spare),
-                                all_gather=slab.dist_all_gather())
+                                all_gather=slab.dist_all_gather_packed(torch.device("cuda", local)))
     migrated = [0]
 
     # interior UpdateGrid/G2P work hides the all-reduce; pays off once the collective is slow (measured: loses
@@ -593,6 +599,19 @@ def main():
     halo_bytes_per_step = (ex.bytes_reduced - shared0) / K if ex else 0
     halo_blocks = ex.last_n_shared if ex else 0
     clocks = sampler.summary(w0, w1)
+
+    # ---- migrating slabs: the state after the WHOLE run (parity pass + warm-up + timed substeps, with every
+    # migration in between) against the merged scene stepped the same number of substeps on one GPU.  The sand
+    # column is a chaotic system (non-smooth return mapping): summation-order differences grow with the step count,
+    # so this is reported with its own, looser bar.
+    parity_run = None
+    if mig is not None and not args.no_final_parity:
+        worst = parity_multi(st, dtype, P + W + K, rank, world, local,
+                             lambda: GpuMpmState(dtype, device=local, **scene_params(world)), mig)
+        t = torch.tensor([worst], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        parity_run = {"against": "the merged scene on one GPU, same number of substeps", "steps": P + W + K,
+                      "migrations": (P + W + K) // MIGRATE_EVERY, "max_rel_positions": float(t[0])}
 
     # ---- end-to-end region: the driver substep with host buffers ---------------------------------
     # deformable_driver.h:240-260 as the drop-in shim issues it: SyncParticleStateToCpu starts the
@@ -719,6 +738,7 @@ def main():
                 "gpu_launches": launches_all, "gpu_launches_per_step": launches_all / K / world,
                 "roofline": roofline, "kernels": kern, "parity": parity}
         if mig is not None:
+            line["parity_after_run"] = parity_run
             line["migration"] = {"every_substeps": MIGRATE_EVERY, "particles_moved_total": int(migrated[0]),
                                  "spare_fraction": SPARE_FRACTION, "margin_cells": 2}
         if world == 1 and not args.no_cpu_baseline:

@@ -387,6 +387,21 @@ class SlabMigrator:
 
     def migrate(self):
         out = self.extract()
+        if getattr(self.all_gather, "packed", False):
+            # NCCL path: the packed records travel as ONE padded tensor all-gather (rows = destination, scene-wide id,
+            # 26 scalars) after a MAX all-reduce of the counts -- two small collectives instead of pickled objects
+            rows = [np.concatenate([np.full((len(g), 1), d, np.float64), g[:, None].astype(np.float64), r.astype(np.float64)], axis=1)
+                    for d, (r, g) in out.items()]
+            mine = np.concatenate(rows) if rows else np.zeros((0, 28))
+            everything = self.all_gather(mine)
+            sel = everything[everything[:, 0] == self.rank]
+            moved = len(everything)
+            if len(sel):
+                order = np.argsort(sel[:, 1], kind="stable")
+                pids = self.state.migrate_in(sel[order, 2:])
+                self.gid[pids] = sel[order, 1].astype(np.int64)
+                self.moved_in += len(pids)
+            return moved
         parcels = self.all_gather(out)
         self.insert(parcels)
         return sum(len(p[d][1]) for p in parcels for d in p)   # particles that changed hands, scene-wide
@@ -399,6 +414,29 @@ def dist_all_gather(group=None):
         out = [None] * dist.get_world_size(group)
         dist.all_gather_object(out, obj, group=group)
         return out
+    return gather
+
+
+def dist_all_gather_packed(device, group=None):
+    """all_gather for SlabMigrator over NCCL tensors: f(rows (n, 28) float64) -> the rows of all ranks, concatenated."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+
+    def gather(rows):
+        n = torch.tensor([rows.shape[0]], dtype=torch.int64, device=device)
+        dist.all_reduce(n, op=dist.ReduceOp.MAX, group=group)
+        m = int(n.item())
+        if m == 0:
+            return np.zeros((0, rows.shape[1]))
+        buf = torch.full((m, rows.shape[1]), -1.0, dtype=torch.float64, device=device)
+        if rows.shape[0]:
+            buf[:rows.shape[0]] = torch.from_numpy(np.ascontiguousarray(rows)).to(device)
+        out = torch.empty((world, m, rows.shape[1]), dtype=torch.float64, device=device)
+        dist.all_gather_into_tensor(out, buf, group=group)
+        allr = out.reshape(-1, rows.shape[1]).cpu().numpy()
+        return allr[allr[:, 0] >= 0]
+    gather.packed = True
     return gather
 
 
