@@ -317,8 +317,10 @@ class GpuMpmState:
     def migrate_out(self, axis, lo, hi, park, cap):
         """Extension: active volumetric particles outside [lo, hi) along `axis` leave the state.
         -> (records (n, 26), local particle ids (n,)), sorted by id; at most cap."""
-        rec = np.zeros((cap, self.MIGRATE_RECORD), self.dtype)
-        pids = np.zeros(cap, np.int32)
+        buf = getattr(self, "_migrate_buf", None)       # reused: zero-filling 26 * cap scalars per call costs milliseconds
+        if buf is None or buf[0].shape[0] < cap:
+            buf = self._migrate_buf = (np.empty((cap, self.MIGRATE_RECORD), self.dtype), np.empty(cap, np.int32))
+        rec, pids = buf
         park = np.ascontiguousarray(park, self.dtype)
         n = C.c_size_t()
         check(self._f("migrate_out")(self._h, int(axis), self._ct(lo), self._ct(hi), _ptr(park), _ptr(rec), _ptr(pids),
