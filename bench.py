@@ -739,6 +739,9 @@ def main():
                 "roofline": roofline, "kernels": kern, "parity": parity}
         if mig is not None:
             line["parity_after_run"] = parity_run
+            print("[bench] migration host time on rank 0: extract %.1f ms, transport %.1f ms, insert %.1f ms in total"
+                  % (1e3 * getattr(mig, "t_extract", 0), 1e3 * getattr(mig, "t_comm", 0), 1e3 * getattr(mig, "t_insert", 0)),
+                  file=sys.stderr)
             line["migration"] = {"every_substeps": MIGRATE_EVERY, "particles_moved_total": int(migrated[0]),
                                  "spare_fraction": SPARE_FRACTION, "margin_cells": 2}
         if world == 1 and not args.no_cpu_baseline:

@@ -386,7 +386,11 @@ class SlabMigrator:
         return len(pids)
 
     def migrate(self):
+        import time
+        t0 = time.perf_counter()
         out = self.extract()
+        t1 = time.perf_counter()
+        self.t_extract = getattr(self, "t_extract", 0.0) + (t1 - t0)
         if getattr(self.all_gather, "packed", False):
             # NCCL path: the packed records travel as ONE padded tensor all-gather (rows = destination, scene-wide id,
             # 26 scalars) after a MAX all-reduce of the counts -- two small collectives instead of pickled objects
@@ -394,6 +398,7 @@ class SlabMigrator:
                     for d, (r, g) in out.items()]
             mine = np.concatenate(rows) if rows else np.zeros((0, 28))
             everything = self.all_gather(mine)
+            t2 = time.perf_counter()
             sel = everything[everything[:, 0] == self.rank]
             moved = len(everything)
             if len(sel):
@@ -401,6 +406,9 @@ class SlabMigrator:
                 pids = self.state.migrate_in(sel[order, 2:])
                 self.gid[pids] = sel[order, 1].astype(np.int64)
                 self.moved_in += len(pids)
+            t3 = time.perf_counter()
+            self.t_comm = getattr(self, "t_comm", 0.0) + (t2 - t1)
+            self.t_insert = getattr(self, "t_insert", 0.0) + (t3 - t2)
             return moved
         parcels = self.all_gather(out)
         self.insert(parcels)
