@@ -84,7 +84,7 @@ def scene_params(world):
     return {} if world == 1 else {"domain_bits": 8, "dx": DX}
 
 
-SPARE_FRACTION = 0.25      # cfg3, N > 1: inactive particles per rank that arrivals of the migration take over
+SPARE_FRACTION = 0.15      # cfg3, N > 1: inactive particles per rank that arrivals of the migration take over
                            # (set to 1.0 at 8 ranks: the collapsing column piles up in the 10-cell edge slabs)
 MIGRATE_EVERY = 32
 

@@ -216,6 +216,12 @@ __global__ void volumetric_stress_kernel(uint32_t N, uint32_t n_cloth, const int
   const uint32_t p = (uint32_t)pid[s];
   if (p < n_cloth) return;
   const uint32_t q = p - n_cloth;
+  const T v0 = vol[s];
+  if (!(v0 > T(0))) {  // inactive spare of the migration (csrc/migrate.cuh): no mass, no stress, F stays I
+#pragma unroll
+    for (int e = 0; e < 6; ++e) taus[(size_t)e * N + s] = T(0);
+    return;
+  }
   T Cl[9], F[9], tau[6];
 #pragma unroll
   for (int e = 0; e < 9; ++e) {
@@ -223,7 +229,6 @@ __global__ void volumetric_stress_kernel(uint32_t N, uint32_t n_cloth, const int
     F[e] = Fv[(size_t)q * 9 + e];
   }
   volumetric_update<T>(mats.m[mat_id[q]], Cl, dt, F, tau);
-  const T v0 = vol[s];
 #pragma unroll
   for (int e = 0; e < 9; ++e) Fv[(size_t)q * 9 + e] = F[e];
 #pragma unroll
