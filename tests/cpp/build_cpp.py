@@ -26,6 +26,29 @@ def build(force=False):
     return OUT
 
 
+OUT_TWO_RANK = os.path.join(HERE, "_build", "test_two_rank_host")
+
+
+def build_two_rank(force=False):
+    """tests/cpp/test_two_rank_host.cc: the multi-rank exchange driven from C++ through the peer-window ABI."""
+    src = os.path.join(HERE, "test_two_rank_host.cc")
+    deps = [src, os.path.join(ROOT, "drake_b200", "lib", "libgmpm_b200.so"), os.path.join(ROOT, "include", "gmpm_c.h")]
+    if not force and os.path.exists(OUT_TWO_RANK) and os.path.getmtime(OUT_TWO_RANK) >= max(os.path.getmtime(d) for d in deps):
+        return OUT_TWO_RANK
+    os.makedirs(os.path.dirname(OUT_TWO_RANK), exist_ok=True)
+    gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    cmd = [gxx, "-std=c++17", "-O2", "-Wall", "-Wextra", "-Werror", "-I" + os.path.join(ROOT, "include"),
+           "-I" + os.path.join(cuda, "include"), src, "-o", OUT_TWO_RANK, "-L" + os.path.join(ROOT, "drake_b200", "lib"),
+           "-lgmpm_b200", "-L" + os.path.join(cuda, "lib64"), "-lcudart",
+           "-Wl,-rpath,$ORIGIN/../../../drake_b200/lib:" + os.path.join(cuda, "lib64")]
+    env = dict(os.environ)
+    env.pop("CC", None)
+    env.pop("CXX", None)
+    subprocess.check_call(cmd, env=env)
+    return OUT_TWO_RANK
+
+
 REF_DRIVER = "/root/reference/multibody/plant/deformable_driver.h"
 EXCERPT = os.path.join(HERE, "_build", "driver_excerpt.inc")
 OUT_EXCERPT = os.path.join(HERE, "_build", "test_driver_excerpt")
@@ -60,4 +83,5 @@ def build_excerpt(force=False):
 
 if __name__ == "__main__":
     print(build_excerpt(force=True))
+    print(build_two_rank(force=True))
     print(build(force=True))

@@ -41,3 +41,17 @@ def test_reference_driver_method_bodies_run_through_the_c_abi():
     r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "OK driver excerpt" in r.stdout, r.stdout
+
+
+def test_two_rank_cpp_host_compiles():
+    assert os.path.exists(build_cpp.build_two_rank())
+
+
+@pytest.mark.gpu
+def test_two_rank_cpp_host_matches_the_single_state():
+    """INTEGRATION.md section 5 as a C++ program: two states coupled through gmpm_halo_peer_* (windows attached by
+    pointer, flag all-reduce on the host) reproduce the single-state run."""
+    exe = build_cpp.build_two_rank()
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.startswith("OK two-rank"), r.stdout
