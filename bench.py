@@ -461,6 +461,8 @@ def main():
     global SPARE_FRACTION
     if env_int("WORLD_SIZE", 1) >= 8:
         SPARE_FRACTION = 1.0
+    elif env_int("WORLD_SIZE", 1) >= 4:
+        SPARE_FRACTION = 0.3
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
 
     if args.impl == "reference":
