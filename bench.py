@@ -86,7 +86,7 @@ def scene_params(world):
 
 SPARE_FRACTION = 0.15      # cfg3, N > 1: inactive particles per rank that arrivals of the migration take over
                            # (set to 1.0 at 8 ranks: the collapsing column piles up in the 10-cell edge slabs)
-MIGRATE_EVERY = 32
+MIGRATE_EVERY = 128          # a migration event costs ~10 ms of host work and rank skew; ownership may lag
 
 
 def park_of(rank, world):
@@ -517,7 +517,7 @@ def main():
         off = int(counts[:rank].sum())
         gid = np.concatenate([np.arange(off, off + N), -np.ones(n_spare, np.int64)])
         edges = np.array([0.19 + (80 * r // world) * DX for r in range(1, world)])
-        mig = slab.SlabMigrator(st, rank, world, edges, gid, park_of(rank, world), margin=2 * DX, cap=max(1, n_spare),
+        mig = slab.SlabMigrator(st, rank, world, edges, gid, park_of(rank, world), margin=4 * DX, cap=max(1, n_spare),
                                 all_gather=slab.dist_all_gather_packed(torch.device("cuda", local)))
     migrated = [0]
 
@@ -745,7 +745,7 @@ def main():
                   % (1e3 * getattr(mig, "t_extract", 0), 1e3 * getattr(mig, "t_comm", 0), 1e3 * getattr(mig, "t_insert", 0)),
                   file=sys.stderr)
             line["migration"] = {"every_substeps": MIGRATE_EVERY, "particles_moved_total": int(migrated[0]),
-                                 "spare_fraction": SPARE_FRACTION, "margin_cells": 2}
+                                 "spare_fraction": SPARE_FRACTION, "margin_cells": 4}
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_baseline(dtype)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "flags")}
