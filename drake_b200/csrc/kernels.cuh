@@ -1047,6 +1047,15 @@ clean_stale_blocks_kernel(const uint32_t* __restrict__ prev_list, const DevCount
 // order follows the spatial order with one step of lag and next step's loads stay coalesced.
 // ------------------------------------------------------------------------------------------------
 constexpr int kG2PWarps = 4;
+// A/B switches (profiles/r02_g2p_ab.txt): velocity-tile buffers per warp (2 = the next chunk's tile is in flight while
+// this one is gathered; 1 = half the shared memory, twice the resident CTAs) and the register cap via min CTAs per SM.
+#ifndef GMPM_G2P_BUFS
+#define GMPM_G2P_BUFS 2
+#endif
+#ifndef GMPM_G2P_MIN_CTAS
+#define GMPM_G2P_MIN_CTAS 4
+#endif
+constexpr int kG2PBufs = GMPM_G2P_BUFS;
 
 // 4- or 8-byte asynchronous global -> shared copy (LDGSTS); src_bytes = 0 writes zeros.
 template <typename T>
@@ -1069,7 +1078,7 @@ __device__ __forceinline__ void cp_async_wait() {
 // the queue ticket of chunk c+2 is outstanding; the first batch of positions of chunk c+1 is loaded
 // during the last batch of chunk c.  No load is followed directly by its use.
 template <typename T>
-__global__ void __launch_bounds__(kG2PWarps * 32, 5)
+__global__ void __launch_bounds__(kG2PWarps * 32, GMPM_G2P_MIN_CTAS)
 g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __restrict__ pb_work, uint32_t work_cap,
            const T* __restrict__ g_vel, const T* __restrict__ pos, const T* __restrict__ vol,
            const int* __restrict__ pid, T* __restrict__ pos_out, T* __restrict__ vel_out, T* __restrict__ C_out,
@@ -1078,7 +1087,7 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __rest
            const uint8_t* __restrict__ mark = nullptr, int want = -1, uint32_t n_cloth = 0xFFFFFFFFu) {
   // mark / want (multi-GPU): want = 0 -> only chunks whose stencils stay clear of the blocks exchanged with
   // other ranks (they can run while the exchange is in flight), want = 1 -> only the others, -1 -> all.
-  __shared__ T s_vel[kG2PWarps][2][3][kTileNodes];
+  __shared__ T s_vel[kG2PWarps][kG2PBufs][3][kTileNodes];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t n_big = ctr->n_big, n_work = n_big + ctr->n_small;
   const uint32_t blocks_per_axis = (uint32_t)k.domain_size >> 2;
@@ -1156,11 +1165,15 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __rest
   for (;;) {
     uint32_t t2 = ticket();  // the chunk after next
     if (wn.tile != kNone) {
-      stage(wn, buf ^ 1);
+      if (kG2PBufs == 2) stage(wn, buf ^ 1);
       load_sidx(wn, sidx_n);
     }
-    cp_async_commit();       // (possibly empty) group of the next chunk
-    cp_async_wait<1>();      // this chunk's tile has landed
+    if (kG2PBufs == 2) {
+      cp_async_commit();     // (possibly empty) group of the next chunk
+      cp_async_wait<1>();    // this chunk's tile has landed
+    } else {
+      cp_async_wait<0>();    // single buffer: the tile was staged at the end of the previous chunk
+    }
     __syncwarp();
     const T* tv = &s_vel[warp][buf][0][0];
     uint32_t i = w.begin + lane;
@@ -1261,11 +1274,15 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __rest
     }
     __syncwarp();  // every lane is done with this tile before the buffer is staged again
     if (wn.tile == kNone) break;
+    if (kG2PBufs == 1) {     // single buffer: stage the next chunk's tile now that this one has been consumed
+      stage(wn, 0);
+      cp_async_commit();
+    }
     w = wn;
 #pragma unroll
     for (int b4 = 0; b4 < 4; ++b4) sidx[b4] = sidx_n[b4];
     wn = resolve(t2);
-    buf ^= 1;
+    if (kG2PBufs == 2) buf ^= 1;
   }
   cp_async_wait<0>();
 }

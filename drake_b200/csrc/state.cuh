@@ -717,7 +717,7 @@ struct State {
     }
     if (n_vol) {
       launch("volumetric_stress");
-      volumetric_stress_kernel<T><<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, n_cloth(), pid[cur], C[cur], vol[cur], Fv,
+      volumetric_stress_kernel<T><<<blocks_for(N, kVolThreads), kVolThreads, 0, stream>>>((uint32_t)N, n_cloth(), pid[cur], C[cur], vol[cur], Fv,
                                                                          mat_id, mat_table, taus, dt);
       GMPM_CUDA(cudaGetLastError());
     }

@@ -206,8 +206,15 @@ __device__ inline void volumetric_update(const MaterialDev<T>& m, const T* C, T 
 
 // CalcFemStateAndForce for the volumetric particles: one thread per physical slot (C, vol, taus are planar by slot:
 // coalesced); F lives by volumetric particle id (72 contiguous bytes per particle).
+#ifndef GMPM_VOL_THREADS
+#define GMPM_VOL_THREADS 128
+#endif
+#ifndef GMPM_VOL_MIN_CTAS
+#define GMPM_VOL_MIN_CTAS 8
+#endif
+constexpr int kVolThreads = GMPM_VOL_THREADS;
 template <typename T>
-__global__ void volumetric_stress_kernel(uint32_t N, uint32_t n_cloth, const int* __restrict__ pid,
+__global__ void __launch_bounds__(GMPM_VOL_THREADS, GMPM_VOL_MIN_CTAS) volumetric_stress_kernel(uint32_t N, uint32_t n_cloth, const int* __restrict__ pid,
                                          const T* __restrict__ C, const T* __restrict__ vol, T* __restrict__ Fv,
                                          const uint8_t* __restrict__ mat_id, MaterialTable<T> mats, T* __restrict__ taus,
                                          T dt) {
