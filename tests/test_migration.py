@@ -211,7 +211,6 @@ def test_gpu_slabs_with_migration_match_single_state_and_oracle(dtype, tol, worl
         ref = np.empty((len(pos), 3))
         ref[ref_state.read("pids")] = np.asarray(ref_state.read("positions"), np.float64).reshape(-1, 3)
         assert np.max(np.abs(got - ref)) <= tol * np.max(np.abs(ref))
-    gotF = gathered(parts, migs, len(pos), "particle_F_by_pid", 9) if False else None
     gids = np.concatenate([m.gid[m.gid >= 0] for m in migs])
     assert np.array_equal(np.sort(gids), np.arange(len(pos)))
     # the inactive particles stay parked and massless
