@@ -55,6 +55,9 @@ CONFIGS = {
     "cfg3": {"dt": 2e-4, "scaling": "strong",
              "workload": "cfg-3: 4M-particle (3 993 600) Drucker-Prager sand column collapse (80x80x78 cells, 8 per cell, "
                          "friction angle 30 deg), x-slabs over the ranks, dt=2e-4, 128^3 grid, dx=1/128"},
+    "cfg4": {"dt": 1e-3, "scaling": "weak",
+             "workload": "cfg-4: 2M-particle cloth stack (68 sheets, N=2012936) squeezed by two moving box pads, convex "
+                         "Jacobi-Newton contact solve per substep (mu=1, k=1e6, d=1e-5), fp64, dt=1e-3, single GPU"},
     "cfg5": {"dt": 2e-4, "scaling": "weak",
              "workload": "cfg-5: 8M fixed-corotated particles per GPU (100^3 cells, 8 per cell), blocks adjacent in a 2x2x2 "
                          "arrangement, 512^3 grid at dx=1/128, dt=2e-4"},
@@ -403,6 +406,162 @@ def f32_line(local, peak, steps):
     return out
 
 
+def cfg4_pads(step):
+    """Two gripper pads (mpm_cloth_folding.cc:32-34 scaled to the stack) closing in along x at 0.1 m/s."""
+    half = np.array([0.02, 0.10, 0.10])
+    centers = [np.array([0.27, 0.5, 0.45]), np.array([0.73, 0.5, 0.45])]
+    vel = [np.array([0.1, 0.0, 0.0]), np.array([-0.1, 0.0, 0.0])]
+    return [(centers[b] + vel[b] * DT * step - half, centers[b] + vel[b] * DT * step + half, b + 1, vel[b],
+             centers[b] + vel[b] * DT * step) for b in range(2)]
+
+
+def cfg4_host_pairs(ph, step):
+    """What CalcMpmContactPairs does on the host (deformable_driver.h:120-194), analytic boxes for the FCL query."""
+    from drake_b200 import scenes
+    parts = [scenes.box_contacts(ph, lo, hi, rigid_id=rid, rigid_v=v, rigid_p_WB=c) for lo, hi, rid, v, c in cfg4_pads(step)]
+    return tuple(np.concatenate([p[i] for p in parts]) for i in range(7))
+
+
+def run_cfg4(args, local):
+    """BASELINE.json configs[3] on one GPU: the coupled DeformableDriver substep with the contact solve."""
+    import oracle_py as O
+    from drake_b200 import scenes
+    from drake_b200.gpu_mpm import GpuMpmSolver, GpuMpmState, MpmParticleContactPairs
+    dtype, T = np.float64, 8
+    MU, K_N, DAMP = 1.0, 1e6, 1e-5
+    sheets = scenes.stacked_sheets(68, dz=0.01, dtype=dtype)
+    st, orc = GpuMpmState(dtype, device=local), O.OracleMpm(dtype)
+    for s in (st, orc):
+        for sh in sheets:
+            s.AddQRCloth(*sh)
+        s.Finalize()
+        s.ReallocateExternelBodies(3)
+    sv = GpuMpmSolver()
+    N = st.n_particles()
+    cores = os.cpu_count() or 1
+
+    def coupled(i, max_it, with_oracle):
+        sv.SyncParticleStateToCpu(st)
+        sv.RebuildMapping(st, False); sv.CalcFemStateAndForce(st, DT); sv.ParticleToGrid(st, DT); sv.UpdateGrid(st, -1)
+        c = cfg4_host_pairs(st.positions_host(), i)
+        pairs = MpmParticleContactPairs(dtype)
+        pairs.extend(*c)
+        sv.CopyContactPairs(st, pairs)
+        stats = sv.UpdateContact(st, 0, i, DT, MU, K_N, DAMP, False, False, max_it)
+        sv.GridToParticle(st, DT)
+        t_orc = 0.0
+        if with_oracle:
+            t0 = time.perf_counter()
+            orc.RebuildMapping(False); orc.CalcFemStateAndForce(DT); orc.ParticleToGrid(DT); orc.UpdateGrid(-1)
+            orc.CopyContactPairs(*c)
+            orc.UpdateContact(DT, MU, K_N, DAMP, False, max_it)
+            orc.GridToParticle(DT)
+            t_orc = time.perf_counter() - t0
+        return stats, len(c[0]), t_orc
+
+    # ---- parity pass: 2 free substeps, then 2 coupled substeps with the first 3 Newton iterations, against the oracle
+    sv.RunSubsteps(st, 2, DT, -1, 40)
+    orc.RebuildMapping(True)
+    for _ in range(2):
+        orc.substep_omp(DT, -1, cores)
+    for i in range(2):
+        coupled(i, 3, True)
+    parity = {"against": "CPU oracle: 2 free + 2 coupled substeps (host pairs, 3 Newton iterations each)", "steps": 4,
+              "max_rel_positions": _rel(st.read("positions"), orc.read("positions")),
+              "max_rel_velocities": _rel(st.read("velocities"), orc.read("velocities")),
+              "pids_equal": bool(np.array_equal(st.read("pids"), orc.read("pids"))), "tolerance": 1e-7}
+    parity["ok"] = bool(max(parity["max_rel_positions"], parity["max_rel_velocities"]) <= 1e-7 and parity["pids_equal"])
+    print("[bench] parity: %s" % parity, file=sys.stderr)
+    sampler = ClockSampler(local)
+    sampler.start()
+    K, W = max(1, args.steps), max(3, args.warmup)
+    geoms = lambda i: [{"kind": "box", "rigid_id": rid, "lo": lo, "hi": hi, "velocity": v, "p_WB": c}
+                       for lo, hi, rid, v, c in cfg4_pads(i)]
+    # ---- device-timed: the coupled loop on the library side of the ABI (pairs generated on the device)
+    sv.RunDriverSubsteps(st, W, DT, geoms(2), -1, 0, 1, MU, K_N, DAMP, False)
+    sv.GpuSync(st)
+    l0 = st.kernel_launches()
+    w0 = time.perf_counter()
+    st.timer_mark(0)
+    ds = sv.RunDriverSubsteps(st, K, DT, geoms(2 + W), -1, 0, 1, MU, K_N, DAMP, False)
+    st.timer_mark(1)
+    sv.GpuSync(st)
+    w1 = time.perf_counter()
+    ms = st.timer_elapsed_ms(0, 1)
+    launches = st.kernel_launches() - l0
+    clocks = sampler.summary(w0, w1)
+    # ---- e2e: the driver substep as upstream issues it, host buffers: all positions D2H, host query, pairs H2D
+    Ke = max(3, min(K, 20))
+    coupled(2 + W + K, 0, False)
+    sv.GpuSync(st)
+    e0 = time.perf_counter()
+    e_pairs, e_iters = 0, 0
+    for i in range(Ke):
+        s_, n_, _ = coupled(3 + W + K + i, 0, False)
+        e_pairs += n_
+        e_iters += s_.iterations
+    sv.GpuSync(st)
+    e_ms = (time.perf_counter() - e0) * 1e3
+    # ---- per-kernel pass
+    Kp = max(2, min(K, 10))
+    st.set_profiling(True)
+    dsp = sv.RunDriverSubsteps(st, Kp, DT, geoms(3 + W + K + Ke), -1, 0, 1, MU, K_N, DAMP, False)
+    sv.GpuSync(st)
+    prof = st.profile_report()
+    st.set_profiling(False)
+    pblocks, touched = st.block_counts()
+    sampler.stop_flag.set()
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    kern, alg, c = kernel_table(prof, Kp, N, st.n_faces(), touched, T, peak)
+    newton = next((k for k in prof if "contact" in k and "newton" in k), None) or max(prof, key=lambda k: prof[k][0])
+    us_per_iter = prof[newton][0] * 1e3 / max(1, dsp.newton_iterations)
+    # ---- CPU baseline: the oracle's coupled substep (full solve), bounded sample
+    t_cpu, n_cpu = 0.0, 0
+    if not args.no_cpu_baseline:
+        # (the oracle's state is that of the parity pass; the pairs come from the product's current positions: a timing
+        # sample of the same amount of work -- as many Newton iterations as the product's solve takes on average)
+        it_cap = max(1, int(round(ds.newton_iterations / max(1, ds.substeps))))
+        while n_cpu < 2 and t_cpu < 25.0:
+            _, _, t = coupled(100 + n_cpu, it_cap, True)
+            t_cpu += t
+            n_cpu += 1
+    line = {"metric": METRIC, "value": N * K / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "particles_per_gpu": N, "touched_grid_blocks": touched,
+                       "l2": "inputs larger than L2", "parallelism": "single GPU",
+                       "loop": "gmpm_run_driver_substeps: pairs generated on the device every substep, full solve"},
+            "clocks": clocks,
+            "contact": {"pairs_mean": ds.contact_pairs / max(1, ds.substeps),
+                        "newton_iterations_per_substep": ds.newton_iterations / max(1, ds.substeps),
+                        "newton_iterations_max": ds.newton_iterations_max, "us_per_newton_iteration": us_per_iter,
+                        "last_residual": ds.last_residual},
+            "e2e": {"value": N * Ke / (e_ms * 1e-3), "unit": UNIT, "steps": Ke, "ms_per_step": e_ms / Ke,
+                    "h2d_bytes_per_step": int(e_pairs / Ke * (2 * 4 + 13 * T)), "d2h_bytes_per_step": int(3 * T * N),
+                    "newton_iterations_per_substep": e_iters / Ke,
+                    "what": "DeformableDriver substep through the C ABI: SyncParticleStateToCpu (all positions), host "
+                            "contact query on positions_host(), CopyContactPairs (H2D), UpdateContact, 5 solver calls"},
+            "gpu_launches": int(launches), "gpu_launches_per_step": launches / K,
+            "roofline": {"kernel": "p2g_tile", "bound": "hbm", "achieved": kern["p2g_tile"]["achieved_gbs"], "peak": peak,
+                         "unit": "GB/s", "frac": kern["p2g_tile"]["achieved_gbs"] / peak, "traffic": None,
+                         "note": "the substep is dominated by the contact solve (latency: grid barriers per Newton "
+                                 "iteration); the roofline entry is the dominant HBM kernel of the transfer part"},
+            "kernels": kern, "parity": parity}
+    if n_cpu:
+        cpu_v = N * n_cpu / t_cpu
+        line["cpu_baseline"] = {"value": cpu_v, "unit": UNIT, "cores": 1, "kind": "port",
+                                "sample": "%d coupled substeps of the full scene with the oracle's serial contact solve capped at %d "
+                                          "Newton iterations (the product's mean), %.1f s" % (n_cpu, it_cap, t_cpu)}
+        line["speedup_vs_cpu_port"] = {"device": line["value"] / cpu_v, "e2e": line["e2e"]["value"] / cpu_v}
+    emit(line)
+    st.Destroy()
+
+
 _REAL_STDOUT = None
 
 
@@ -473,6 +632,11 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     torch.cuda.set_device(local)
+    if CFG == "cfg4":
+        if world > 1:
+            raise SystemExit("bench.py --config cfg4: the contact solve is single-GPU (DESIGN.md section 8)")
+        run_cfg4(args, local)
+        return
     dist = None
     if world > 1:
         cpus = bind_to_gpu_numa_node(torch, local)
