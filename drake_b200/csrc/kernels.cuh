@@ -358,6 +358,25 @@ __global__ void __launch_bounds__(kSortThreads, 2) bin_particles_kernel(BinArgs 
 // the slot indices of the NEXT face of a thread are resolved while the current face is computed, and
 // every load of the current face (F, Dm^-1, C, volume, the three vertices' x and v) is issued before
 // the first use, so a face costs about one memory round trip instead of a dozen serialized ones.
+// Cell keys of the face particles at the centroids the constitutive kernel is about to move them to (the same
+// expression as fem_kernel below): with the keys known up front the particle binning -- latency bound, a fifth of
+// the SMs' warps -- runs on a second stream UNDER the constitutive kernel instead of after it (State::calc_fem).
+template <typename T>
+__global__ void face_keys_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ fid, const int* __restrict__ tri,
+                                 const int* __restrict__ slot_of_pid, const T* __restrict__ pos,
+                                 uint32_t* __restrict__ key, Consts<T> k) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n_faces) return;
+  const int sf = slot_of_pid[fid[j]];
+  const int s0 = slot_of_pid[tri[j]], s1 = slot_of_pid[tri[n_faces + j]], s2 = slot_of_pid[tri[2 * n_faces + j]];
+  T xc[3];
+#pragma unroll
+  for (int d = 0; d < 3; ++d)
+    xc[d] = (pos[(size_t)d * N + s0] + pos[(size_t)d * N + s1] + pos[(size_t)d * N + s2]) / T(3);
+  key[sf] = cell_key(base_node(xc[0], k.dx_inv, k.domain_size), base_node(xc[1], k.dx_inv, k.domain_size),
+                     base_node(xc[2], k.dx_inv, k.domain_size));
+}
+
 #ifndef GMPM_FEM_MIN_CTAS
 #define GMPM_FEM_MIN_CTAS 3
 #endif
@@ -431,8 +450,9 @@ fem_kernel(uint32_t n_faces, uint32_t N, const int* __restrict__ fid, const int*
       pos[(size_t)d * N + sf] = xc[d];
       vel[(size_t)d * N + sf] = (v0[d] + v1[d] + v2[d]) / T(3);
     }
-    // the face particle moved: refresh its cell key (binning happens after this kernel)
-    key[sf] = cell_key(base_node(xc[0], k.dx_inv, k.domain_size), base_node(xc[1], k.dx_inv, k.domain_size),
+    // the face particle moved: refresh its cell key (unless face_keys_kernel has done so and the binning is
+    // already running beside this kernel)
+    if (key) key[sf] = cell_key(base_node(xc[0], k.dx_inv, k.domain_size), base_node(xc[1], k.dx_inv, k.domain_size),
                        base_node(xc[2], k.dx_inv, k.domain_size));
     T ctF[9];
     ctF[0] = F[0];

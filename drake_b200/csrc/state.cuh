@@ -333,6 +333,14 @@ struct State {
   }
 
   void destroy() {
+    if (bin_stream) {
+      cudaStreamSynchronize(bin_stream);
+      cudaStreamDestroy(bin_stream);
+      cudaEventDestroy(ev_prekeys);
+      cudaEventDestroy(ev_bin_done);
+      bin_stream = nullptr;
+      bin_async_pending = false;
+    }
     if (stream) cudaStreamSynchronize(stream);
     for (void* p : allocs) cudaFree(p);
     allocs.clear();
@@ -572,6 +580,7 @@ struct State {
 
   void ensure_keys() {
     if (keys_valid || N == 0) return;
+    join_binning();  // an early binning may still be reading the keys
     launch("compute_keys");
     compute_keys_kernel<T><<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, pos[cur], key, k);
     GMPM_CUDA(cudaGetLastError());
@@ -582,10 +591,33 @@ struct State {
   const uint32_t* order() const { return svals[sres]; }
   const uint32_t* sorted_keys() const { return skeys[sres]; }
 
-  void ensure_binning(bool for_p2g = false) {
+  // binning launched early (calc_fem) on its own stream: see face_keys_kernel
+  cudaStream_t bin_stream = nullptr;
+  cudaEvent_t ev_prekeys = nullptr, ev_bin_done = nullptr;
+  bool bin_async_pending = false;  // the main stream has not yet waited for the early binning
+  bool bin_rolled = false;         // ... which has also rolled the touched list on behalf of the coming P2G
+  // A/B (profiles/r02_g2p_ab.txt): measured 0.4666 ms/substep with the overlap against 0.4600 without at 1M particles --
+  // the cooperative binning and the persistent FEM kernel do not actually share the SMs, and the extra face-key pass
+  // costs more than the little that overlaps.  Off unless GMPM_BIN_OVERLAP=1.
+  bool bin_overlap = std::getenv("GMPM_BIN_OVERLAP") != nullptr;
+  void join_binning() {
+    if (!bin_async_pending) return;
+    GMPM_CUDA(cudaStreamWaitEvent(stream, ev_bin_done, 0));
+    bin_async_pending = false;
+  }
+
+  void ensure_binning(bool for_p2g = false, cudaStream_t on = nullptr) {
     ensure_keys();
     prologue_done = false;
-    if (bin_valid || N == 0) return;
+    if (N == 0) return;
+    if (bin_valid) {
+      join_binning();
+      if (for_p2g && bin_rolled) prologue_done = true;  // the early binning did p2g_prologue's job
+      if (for_p2g) bin_rolled = false;
+      return;
+    }
+    bin_rolled = false;
+    if (!on) join_binning();  // an early binning that has been invalidated still owns the sort buffers
     // one cooperative launch: stable sort of (key, slot) on all key bits + block ranges + work records
     ++bin_epoch;
     BinArgs a{};
@@ -609,7 +641,7 @@ struct State {
     void* kargs[] = {&a};
     launch("bin_particles");
     GMPM_CUDA(cudaLaunchCooperativeKernel((void*)bin_particles_kernel, dim3(bin_ctas), dim3(kSortThreads), kargs,
-                                          kSortSmemBytes, stream));
+                                          kSortSmemBytes, on ? on : stream));
     g2p_queue_ready = false;
     bin_valid = true;
   }
@@ -706,14 +738,39 @@ struct State {
     forces_zero = n_faces == 0;
     if (n_faces) {
       // the particles are in spatial order from the first G2P on: refresh after it, then periodically
+      join_binning();  // (a second CalcFemStateAndForce without ParticleToGrid in between)
       if (fem_calls % kFaceRefreshEvery == 1) refresh_face_order();
       ++fem_calls;
+      // Binning under the constitutive kernel: the face keys are computed up front, the (cooperative, latency-bound)
+      // binning is launched FIRST on its own stream so that all its CTAs are resident, the persistent FEM CTAs fill
+      // the rest of the SMs.  Off while profiling (per-kernel times are taken on one stream).
+      const bool early = bin_overlap && !prof.on;
+      if (early) {
+        if (!bin_stream) {
+          GMPM_CUDA(cudaStreamCreateWithFlags(&bin_stream, cudaStreamNonBlocking));
+          GMPM_CUDA(cudaEventCreateWithFlags(&ev_prekeys, cudaEventDisableTiming));
+          GMPM_CUDA(cudaEventCreateWithFlags(&ev_bin_done, cudaEventDisableTiming));
+        }
+        launch("face_keys");
+        face_keys_kernel<T><<<blocks_for(n_faces), kThreads, 0, stream>>>((uint32_t)n_faces, (uint32_t)N, fid, tri, slot_of_pid,
+                                                                         pos[cur], key, k);
+        GMPM_CUDA(cudaGetLastError());
+        GMPM_CUDA(cudaEventRecord(ev_prekeys, stream));
+        GMPM_CUDA(cudaStreamWaitEvent(bin_stream, ev_prekeys, 0));
+        bin_valid = false;
+        ensure_binning(true, bin_stream);
+        GMPM_CUDA(cudaEventRecord(ev_bin_done, bin_stream));
+        bin_async_pending = true;
+        bin_rolled = true;
+        prologue_done = false;
+      }
       launch("fem");
       const uint32_t ctas = std::min<uint32_t>(blocks_for(n_faces, kFemThreads), persistent_ctas(fem_ctas_per_sm));
       fem_kernel<T><<<ctas, kFemThreads, 0, stream>>>((uint32_t)n_faces, (uint32_t)N, fid, tri, slot_of_pid, vol[cur], C[cur],
-                                                      Dm_inv, pos[cur], vel[cur], Fd, forces, taus, key, dt, k, fem_reverse);
+                                                      Dm_inv, pos[cur], vel[cur], Fd, forces, taus, early ? nullptr : key, dt, k,
+                                                      fem_reverse);
       GMPM_CUDA(cudaGetLastError());
-      bin_valid = false;  // face particles moved to their centroids
+      if (!early) bin_valid = false;  // face particles moved to their centroids
     }
     if (n_vol) {
       launch("volumetric_stress");
@@ -1230,6 +1287,7 @@ struct State {
 
   void sync() {
     bind_device();
+    if (bin_async_pending) GMPM_CUDA(cudaStreamSynchronize(bin_stream));
     GMPM_CUDA(cudaStreamSynchronize(stream));
     if (prof.on) prof.flush(stream);
   }
