@@ -560,6 +560,8 @@ struct State {
       GMPM_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p2g_smem));
       GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p2g_ctas_per_sm, fn, p2g_threads, p2g_smem));
       if (p2g_ctas_per_sm < 1) throw CudaError(cudaErrorLaunchOutOfResources, "the P2G kernel does not fit on an SM");
+      if (const char* c = std::getenv("GMPM_P2G_CTAS"))  // development: fewer resident warps than the occupancy allows
+        p2g_ctas_per_sm = std::max(1, std::min(p2g_ctas_per_sm, std::atoi(c)));
     }
     GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g2p_ctas_per_sm, g2p_kernel<T>, kG2PWarps * 32, 0));
     g2p_ctas_per_sm = std::max(1, std::min(g2p_ctas_per_sm, 8));
