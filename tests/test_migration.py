@@ -253,3 +253,55 @@ def test_inactive_particles_are_invisible_to_the_grid():
     assert np.array_equal(outs[0][1], outs[1][1])
     assert np.max(np.abs(outs[0][2] - outs[1][2])) <= 1e-13
     assert np.array_equal(outs[1][3], slab.park_points([0.7, 0.7, 0.7, 0.9, 0.9, 0.9], 5000))   # the spares never moved
+
+
+def test_packed_transport_path_of_the_migrator_on_two_threads():
+    """SlabMigrator.migrate() with an all_gather that carries one packed array per rank (the NCCL tensor path of
+    slab.dist_all_gather_packed), driven by two threads standing in for two ranks: same result as the object path."""
+    import threading
+    dtype = np.float64
+    world = 2
+    pos, vel, vol = moving_block(dtype)
+    edges = slab.slab_edges(pos, world)
+    own = slab.owner_of(pos[:, 0], edges)
+    barrier = threading.Barrier(world)
+    box = [None] * world
+
+    def make_gather(rank):
+        def gather(rows):
+            box[rank] = rows
+            barrier.wait()
+            out = np.concatenate([b for b in box if len(b)]) if any(len(b) for b in box) else np.zeros((0, 28))
+            barrier.wait()
+            return out
+        gather.packed = True
+        return gather
+
+    parts, migs = [], []
+    for r in range(world):
+        st, gid = make_part(lambda: O.OracleMpm(dtype), dtype, pos, vel, vol, own == r, r, spare=len(pos) // 2)
+        parts.append(st)
+        migs.append(slab.SlabMigrator(st, r, world, edges, gid, park_of(r), margin=0.5 * DX, cap=len(pos),
+                                      all_gather=make_gather(r)))
+    ex = slab.InProcessExchange([OracleHaloBackend(s) for s in parts])
+    moved = [0] * world
+    for it in range(24):
+        oracle_step(parts, ex, it)
+        if (it + 1) % 4 == 0:
+            def work(r):
+                moved[r] += migs[r].migrate()
+            ts = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+            [t.start() for t in ts]
+            [t.join() for t in ts]
+            ex.planned = False
+            for b in ex.backends:
+                b.reset_plan()
+    assert moved[0] == moved[1] > 50
+    full = O.OracleMpm(dtype)
+    full.AddParticles(pos, vel, vol, **MAT)
+    full.Finalize()
+    for it in range(24):
+        full.substep(DT, -1, it % 7 == 0)
+    ref = np.empty((len(pos), 3))
+    ref[full.read("pids")] = full.read("positions").reshape(-1, 3)
+    assert np.max(np.abs(gathered(parts, migs, len(pos)) - ref)) <= 1e-12
