@@ -49,7 +49,8 @@ class ContactStats(C.Structure):
 
 # every symbol include/gmpm_c.h declares (checked by tests/test_abi.py against the header text)
 PLAIN_SYMBOLS = ["gmpm_default_params", "gmpm_last_error", "gmpm_version", "gmpm_device_count", "gmpm_device_sync",
-                 "gmpm_morton_code", "gmpm_cell_index", "gmpm_inverse_cell_index", "gmpm_radix_sort_pairs"]
+                 "gmpm_morton_code", "gmpm_cell_index", "gmpm_inverse_cell_index", "gmpm_radix_sort_pairs",
+                 "gmpm_radix_sort_pairs_static_scratch"]
 TYPED_SYMBOLS = ["create", "destroy", "add_qr_cloth", "finalize", "rebuild_mapping", "calc_fem", "p2g",
                  "update_grid", "g2p", "sync", "sync_particle_state_to_cpu", "sync_particle_state_to_cpu_async",
                  "positions_host", "set_query_bounds", "add_particles", "migrate_out", "migrate_in", "n_volumetric", "clear_query_bounds", "snapshot_d2h_bytes", "halo_flags", "halo_plan_async", "halo_reset_plan", "halo_pack", "halo_unpack", "halo_peer_init", "halo_peer_window", "halo_peer_attach", "halo_peer_send", "halo_peer_recv", "update_grid_part", "g2p_part", "stream", "halo_stream", "copy_contact_pairs",
@@ -91,6 +92,7 @@ def _declare(L):
     L.gmpm_inverse_cell_index.argtypes = [C.c_uint32, u32p]
     L.gmpm_inverse_cell_index.restype = None
     L.gmpm_radix_sort_pairs.argtypes = [vp, vp, sz, C.c_int, vp, vp]
+    L.gmpm_radix_sort_pairs_static_scratch.argtypes = [vp, vp, sz, C.c_int, vp, vp, vp]
     for suf, ct in (("f32", C.c_float), ("f64", C.c_double)):
         g = lambda n: getattr(L, "gmpm_%s_%s" % (n, suf))
         g("create").argtypes = [C.POINTER(Params), C.POINTER(vp)]

@@ -1,5 +1,7 @@
 // gmpm_capi.cu -- the extern "C" boundary of libgmpm_b200.so (include/gmpm_c.h).
+#include <mutex>
 #include <new>
+#include <string>
 #define GMPM_STR2(x) #x
 #define GMPM_STR(x) GMPM_STR2(x)
 
@@ -115,6 +117,121 @@ int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_
     cudaFree(kin);
     cudaFree(vin);
     cudaFree(scratch);
+  });
+}
+
+// ---------------------------------------------------------------------------------------------------
+// gmpm_radix_sort_pairs_static_scratch: the same sort for callers that must not allocate (see gmpm_c.h).
+// Everything the sort needs beyond the caller's input and output arrays lives in ONE array that is part
+// of the library image: the driver places it on every GPU that loads the library and keeps it there
+// until the process exits.  Layout (uint32 words), sized for kStaticSortMaxPairs pairs:
+//   [0, M)        the "other" key buffer of the ping-pong (the caller's keys_out is the final one)
+//   [M, 2M)       the "other" id buffer
+//   [2M, 2M + H)  per-tile digit histograms and digit totals (H = radix_sort_scratch_words(M))
+constexpr size_t kStaticSortMaxPairs = GMPM_RADIX_SORT_STATIC_MAX_PAIRS;  // gmpm_c.h
+constexpr size_t kStaticSortHistWords =
+    (size_t)gmpm::kMaxRadix * ((kStaticSortMaxPairs + gmpm::kSortWarps * 32 * gmpm::kSortItemsSmall - 1) /
+                               (gmpm::kSortWarps * 32 * gmpm::kSortItemsSmall)) + gmpm::kMaxRadix;
+constexpr size_t kStaticSortWords = 2 * kStaticSortMaxPairs + kStaticSortHistWords;
+static __device__ __align__(256) uint32_t g_static_sort_scratch[kStaticSortWords];
+
+namespace {
+constexpr int kStaticSortMaxDevices = 64;
+std::mutex g_static_sort_mu;
+uint32_t* g_static_sort_ptr[kStaticSortMaxDevices] = {};  // device address of the array, per device ordinal
+int g_static_sort_ctas[kStaticSortMaxDevices] = {};       // co-resident CTAs of radix_sort_kernel, per device
+
+// Set-up of the CURRENT device, done by the first call that runs on it.  In host code the name
+// g_static_sort_scratch is only a handle for the runtime, not somewhere a kernel could read or write:
+// the address the kernel gets is whatever cudaGetSymbolAddress reports for the device that is current.
+void static_sort_setup(int dev, uint32_t** scratch, int* max_ctas) {
+  if (dev < 0 || dev >= kStaticSortMaxDevices) throw std::invalid_argument("device ordinal beyond the per-device table");
+  std::lock_guard<std::mutex> lock(g_static_sort_mu);
+  if (!g_static_sort_ptr[dev]) {
+    uint32_t* ptr = nullptr;
+    GMPM_CUDA(cudaGetSymbolAddress((void**)&ptr, g_static_sort_scratch));
+    if (!ptr) throw gmpm::CudaError(cudaErrorInvalidSymbol, "cudaGetSymbolAddress returned a null scratch address");
+    int sms = 0, occ = 0;
+    GMPM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    GMPM_CUDA(cudaFuncSetAttribute(gmpm::radix_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)gmpm::kSortSmemBytes));
+    GMPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gmpm::radix_sort_kernel, gmpm::kSortThreads,
+                                                            gmpm::kSortSmemBytes));
+    if (occ < 1) throw gmpm::CudaError(cudaErrorLaunchOutOfResources, "radix sort kernel does not fit on an SM");
+    g_static_sort_ctas[dev] = sms * occ;
+    g_static_sort_ptr[dev] = ptr;
+  }
+  *scratch = g_static_sort_ptr[dev];
+  *max_ctas = g_static_sort_ctas[dev];
+}
+
+// true if the pointer is one a kernel running on the current device may dereference
+bool device_readable(const void* p) {
+  cudaPointerAttributes at{};
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+bool ranges_overlap(const void* a, const void* b, size_t bytes) {
+  const uintptr_t x = (uintptr_t)a, y = (uintptr_t)b;
+  return x < y + bytes && y < x + bytes;
+}
+}  // namespace
+
+int gmpm_radix_sort_pairs_static_scratch(const uint32_t* keys_in_dev, const uint32_t* ids_in_dev, size_t n, int num_bit,
+                                         uint32_t* keys_out_dev, uint32_t* ids_out_dev, void* cuda_stream) {
+  return guarded([&] {
+    if (num_bit < 0 || num_bit > 32) throw std::invalid_argument("num_bit out of range");
+    if (n > kStaticSortMaxPairs)
+      throw std::invalid_argument("gmpm_radix_sort_pairs_static_scratch: n = " + std::to_string(n) +
+                                  " pairs is more than the built-in scratch array holds (" +
+                                  std::to_string(kStaticSortMaxPairs) +
+                                  "); use gmpm_radix_sort_pairs, which allocates, or split the input");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+      throw gmpm::CudaError(cudaErrorNoDevice, "no CUDA device available (libgmpm_b200 has no CPU fallback)");
+    if (n == 0) return;
+    if (!keys_in_dev || !ids_in_dev || !keys_out_dev || !ids_out_dev) throw std::invalid_argument("null array pointer");
+    const void* arrays[4] = {keys_in_dev, ids_in_dev, keys_out_dev, ids_out_dev};
+    for (int i = 0; i < 4; ++i) {
+      if (!device_readable(arrays[i]))
+        throw std::invalid_argument("gmpm_radix_sort_pairs_static_scratch takes DEVICE arrays (argument " +
+                                    std::to_string(i) + " is not device memory); it cannot stage host arrays "
+                                    "because it allocates nothing");
+      for (int j = i + 1; j < 4; ++j)
+        if (ranges_overlap(arrays[i], arrays[j], n * 4))
+          throw std::invalid_argument("input and output arrays must not overlap (the sort is not in place)");
+    }
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    int dev = 0, max_ctas = 0;
+    uint32_t* scratch = nullptr;
+    GMPM_CUDA(cudaGetDevice(&dev));
+    static_sort_setup(dev, &scratch, &max_ctas);
+    if (num_bit == 0) {  // nothing to sort on: the pairs pass through in input order
+      GMPM_CUDA(cudaMemcpyAsync(keys_out_dev, keys_in_dev, n * 4, cudaMemcpyDeviceToDevice, stream));
+      GMPM_CUDA(cudaMemcpyAsync(ids_out_dev, ids_in_dev, n * 4, cudaMemcpyDeviceToDevice, stream));
+      return;
+    }
+    // pass p writes buffer pair p & 1, so the last of n_passes passes writes pair (n_passes - 1) & 1: that pair is
+    // the caller's output, the other one is the built-in array.  The input arrays are only ever read.
+    gmpm::SortPass plan[4];
+    const int last = (gmpm::plan_sort_passes(num_bit, plan) - 1) & 1;
+    uint32_t *k[2], *v[2];
+    k[last] = keys_out_dev;
+    v[last] = ids_out_dev;
+    k[last ^ 1] = scratch;
+    v[last ^ 1] = scratch + kStaticSortMaxPairs;
+    gmpm::SortArgs a =
+        gmpm::make_sort_args(keys_in_dev, ids_in_dev, k, v, (uint32_t)n, num_bit, scratch + 2 * kStaticSortMaxPairs);
+    // Nothing in the array has to start at zero: every histogram row and digit total a pass reads was written by
+    // that same pass, and the ping-pong half is written before it is read, so what the previous call left is dead.
+    const int want = a.n_tiles > 64u ? (int)a.n_tiles : 64;  // same grid as sort_grid_ctas
+    const int ctas = want < max_ctas ? want : max_ctas;
+    void* kargs[] = {&a};
+    GMPM_CUDA(cudaLaunchCooperativeKernel((void*)gmpm::radix_sort_kernel, dim3(ctas), dim3(gmpm::kSortThreads), kargs,
+                                          gmpm::kSortSmemBytes, stream));
   });
 }
 

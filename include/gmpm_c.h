@@ -322,6 +322,39 @@ void gmpm_inverse_cell_index(uint32_t index, uint32_t* xyz);
 int gmpm_radix_sort_pairs(const uint32_t* keys_in, const uint32_t* ids_in, size_t n, int num_bit,
                           uint32_t* keys_out, uint32_t* ids_out);
 
+/* No counterpart in the reference (its radix_sort cudaMallocs its block sums on every call,
+ * radix_sort.cuh:202-286): the same stable sort as gmpm_radix_sort_pairs, for callers that are not
+ * allowed to allocate device memory.  Who that is: a host whose GPU memory was handed out once at
+ * start-up and is accounted for byte by byte (a simulator embedded in a real-time control loop, where
+ * cudaMalloc may take a device-wide lock and stall every other stream for milliseconds); code that
+ * and cudaFree waits for the whole device to drain); and a plugin that runs inside a larger
+ * application which owns the device allocator and forbids cudaMalloc/cudaFree behind its back.
+ * This entry point calls no cudaMalloc, no cudaFree and no library routine that allocates.
+ *
+ * What differs from gmpm_radix_sort_pairs:
+ *   - the four arrays are DEVICE pointers of n uint32 each on the current device, supplied and owned
+ *     by the caller (with nothing allocated there is no place to stage host arrays); inputs are only
+ *     read, outputs must not overlap the inputs or each other;
+ *   - the work is enqueued on cuda_stream (a cudaStream_t; NULL = the default stream) and the call
+ *     returns without waiting: synchronise that stream before reading the outputs;
+ *   - the second ping-pong buffer and the digit histograms live in an array built into the library
+ *     image, 12.6 MB (2 x 4 MB + 4.2 MB) that every GPU which loads libgmpm_b200.so carries until the
+ *     process exits.  Its size fixes the LIMIT: n <= GMPM_RADIX_SORT_STATIC_MAX_PAIRS; a larger n
+ *     fails with GMPM_ERR_INVALID and a message naming the limit, and nothing is launched;
+ *   - there is one such array per GPU and every call on that GPU uses it.  Two calls that can run
+ *     at the same time on one GPU (different streams, different host threads, different states)
+ *     corrupt each other's result: keep them on one stream or order them with events.  Nothing in the
+ *     array needs clearing between calls -- each pass writes what it later reads -- so back-to-back
+ *     calls on one stream are fine, whatever the previous call left behind;
+ *   - the first call on each device looks up the array's address on that device and the launch
+ *     geometry (a few runtime queries, no allocation).  Make that first call outside any stream
+ *     capture; later calls on the device skip the set-up.
+ * Results are bit-identical to gmpm_radix_sort_pairs (same kernel, same pass plan). */
+#define GMPM_RADIX_SORT_STATIC_MAX_PAIRS (1u << 20)
+int gmpm_radix_sort_pairs_static_scratch(const uint32_t* keys_in_dev, const uint32_t* ids_in_dev, size_t n,
+                                         int num_bit, uint32_t* keys_out_dev, uint32_t* ids_out_dev,
+                                         void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif
