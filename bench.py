@@ -99,6 +99,9 @@ def park_of(rank, world):
     return np.array([0.19 + (c0 + 1) * DX, 0.19 + DX, 4.5 * DX, 0.19 + (c1 - 1) * DX, 0.19 + 79 * DX, 40.5 * DX])
 
 
+SPARES_ADDED = {}          # rank -> inactive spare particles add_rank_bodies gave it
+
+
 def add_rank_bodies(st, dtype, r, world, spare=False):
     """The part of the scene rank r owns, added to `st` (GpuMpmState, OracleMpm or RefMpm: same method names)."""
     from drake_b200 import scenes
@@ -126,6 +129,7 @@ def add_rank_bodies(st, dtype, r, world, spare=False):
         st.AddParticles(pos, vel, vol, "drucker_prager", E_BLOCK, NU_BLOCK, 30.0, 0.0)
         if spare and world > 1:   # position-owned x-slabs: room for the particles that migrate in (slab.SlabMigrator)
             n = int(len(pos) * SPARE_FRACTION)
+            SPARES_ADDED[r] = n                      # the one place the count is decided (run() reads it back)
             from drake_b200 import slab
             st.AddParticles(slab.park_points(park_of(r, world), n), np.zeros((n, 3)), 0.0, "drucker_prager", E_BLOCK, NU_BLOCK,
                             30.0, 0.0)
@@ -222,7 +226,7 @@ def parity_multi(st, dtype, steps, rank, world, local, make_state, mig=None):
 class ClockSampler(threading.Thread):
     """Samples SM clock / power / throttle reasons of one GPU through NVML while the timed region runs."""
 
-    def __init__(self, index, period=0.02):
+    def __init__(self, index, period=0.002):   # the default timed region is ~9 ms: sample every 2 ms
         super().__init__(daemon=True)
         self.index, self.period = index, period
         self.samples = []
@@ -306,6 +310,14 @@ def cpu_baseline(dtype, budget_s=12.0):
             "flags": " ".join(O.FAST_FLAGS), "ms_per_step": el / steps * 1e3}
 
 
+def arm_config():
+    """`config` of the JSON line: the SAME dict in both arms (the driver compares them); what only one arm knows goes
+    under other keys."""
+    return {"workload": WORKLOAD, "sort_every": SORT_EVERY,
+            "l2": "GPU arm: inputs larger than L2 (the particle state one substep streams exceeds the 126 MB L2, see "
+                  "run.particle_state_mb_per_substep); CPU arm: not applicable"}
+
+
 def run_reference_arm(args, rank, world):
     if rank != 0:
         return
@@ -315,9 +327,9 @@ def run_reference_arm(args, rank, world):
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sort_every": SORT_EVERY,
-                       "note": "the reference ships this path only as CUDA; this arm is its CPU restatement "
-                               "(oracle/, pinned against the reference's own kernels) on the host cores"},
+            "config": arm_config(),
+            "note": "the reference ships this path only as CUDA; this arm is its CPU restatement "
+                    "(oracle/, pinned against the reference's own kernels) on the host cores",
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "flags")},
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
@@ -663,7 +675,7 @@ def main():
     st = build_scene(lambda: GpuMpmState(dtype, device=local, **scene_params(world)), dtype, rank, world, spare=True)
     sv = GpuMpmSolver()
     N = st.n_particles()
-    n_spare = int((N / (1 + SPARE_FRACTION)) * SPARE_FRACTION + 0.5) if (CFG == "cfg3" and world > 1) else 0
+    n_spare = SPARES_ADDED.get(rank, 0) if (CFG == "cfg3" and world > 1) else 0
     N -= n_spare                                           # throughput counts the particles of the scene only
     K, W = args.steps, args.warmup
     ex = None
@@ -765,6 +777,7 @@ def main():
     halo_bytes_per_step = (ex.bytes_reduced - shared0) / K if ex else 0
     halo_blocks = ex.last_n_shared if ex else 0
     clocks = sampler.summary(w0, w1)
+    clocks["window"] = "the device-timed region"
 
     # ---- migrating slabs: the state after the WHOLE run (parity pass + warm-up + timed substeps, with every
     # migration in between) against the merged scene stepped the same number of substeps on one GPU.  The sand
@@ -836,6 +849,9 @@ def main():
     Ke = max(3, min(K, 200))
     e_ms, e_bytes = run_e2e(Ke)
     st.SetContactQueryBounds(None)
+    if (clocks.get("samples") or 0) < 3:     # a region of a few ms can fall between two NVML reads: widen to the e2e loops
+        clocks = sampler.summary(w0, time.perf_counter())
+        clocks["window"] = "the device-timed region and the end-to-end loops after it (same kernels, under load)"
 
     # ---- per-kernel pass (CUDA events between launches on the library's stream) ------------------
     Kp = max(3, min(K, 200))
@@ -880,27 +896,29 @@ def main():
         line = {"metric": METRIC, "value": N_all * K / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
                 "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": CONFIGS[CFG]["scaling"], "vs_baseline": None,
                 "dtype": args.dtype, "data": "synthetic",
-                "config": {"workload": WORKLOAD, "sort_every": SORT_EVERY, "particles_per_gpu": N,
-                           "particle_blocks": pblocks, "touched_grid_blocks": touched,
-                           "l2": "inputs larger than L2 (particle state %.0f MB per step > 126 MB)" % (N * (44 * T + 8) / 1e6),
-                           "parallelism": "single GPU" if world == 1 else
-                           "%d ranks, each owning its part of ONE scene (see workload; whole bodies per rank); grid blocks "
-                           "reached by two ranks are summed every substep: all-reduce of block flags (NCCL, side stream, "
-                           "one substep ahead) + %s of %d shared blocks (%.0f KB/step all-reduced)%s"
-                           % (world, "stores into the sharers' peer-memory windows (NVLink) with device-side delivery flags"
-                              if ex is not None and ex.peer else "NCCL all-reduce", halo_blocks,
-                              halo_bytes_per_step / 1e3, ", overlapped with interior G2P" if overlap else "")},
+                "config": arm_config(),
+                "run": {"particles_per_gpu": N, "particle_blocks": pblocks, "touched_grid_blocks": touched,
+                        "particle_state_mb_per_substep": N * (44 * T + 8) / 1e6,
+                        "parallelism": "single GPU" if world == 1 else
+                        "%d ranks, each owning its part of ONE scene (see workload; whole bodies per rank); grid blocks "
+                        "reached by two ranks are summed every substep: all-reduce of block flags (NCCL, side stream, "
+                        "one substep ahead) + %s of %d shared blocks (%.0f KB/step all-reduced)%s"
+                        % (world, "stores into the sharers' peer-memory windows (NVLink) with device-side delivery flags"
+                           if ex is not None and ex.peer else "NCCL all-reduce", halo_blocks,
+                           halo_bytes_per_step / 1e3, ", overlapped with interior G2P" if overlap else "")},
                 "clocks": clocks,
-                "e2e": {"value": N_all * Ke / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0,
-                        "d2h_bytes_per_step": int(e_bytes), "steps": Ke, "ms_per_step": e_ms / Ke,
-                        "what": "DeformableDriver substep through the C ABI with the scene's rigid geometry declared (cfg-2: "
-                                "none, gmpm_set_query_bounds with 0 boxes): SyncParticleStateToCpu (device gather + cull, count "
-                                "and candidates -> pinned host, overlapped with the next 4 solver calls), positions_host() wait "
-                                "+ host read, CopyContactPairs (0 pairs), 5 solver calls; bytes = measured mean per substep "
-                                "on rank 0"},
-                "e2e_full_snapshot": {"value": N_all * Kf / (full_ms * 1e-3), "unit": UNIT, "steps": Kf,
-                                      "ms_per_step": full_ms / Kf, "d2h_bytes_per_step": int(full_bytes),
-                                      "what": "the same loop as upstream issues it: all positions to the host every substep"},
+                "e2e": {"value": N_all * Kf / (full_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0,
+                        "d2h_bytes_per_step": int(full_bytes), "steps": Kf, "ms_per_step": full_ms / Kf,
+                        "what": "the DeformableDriver substep as upstream issues it (deformable_driver.h:240-260) through the C "
+                                "ABI with host buffers: SyncParticleStateToCpu moves ALL positions to the host every substep "
+                                "(device gather -> pinned mirror, overlapped with the next 4 solver calls), positions_host() "
+                                "wait + host read, CopyContactPairs (H2D; cfg-2 has no rigid contact, 0 pairs), 5 solver "
+                                "calls; bytes = measured mean per substep on rank 0"},
+                "e2e_declared_bounds": {"value": N_all * Ke / (e_ms * 1e-3), "unit": UNIT, "steps": Ke,
+                                        "ms_per_step": e_ms / Ke, "d2h_bytes_per_step": int(e_bytes),
+                                        "what": "extension, not the headline: the same loop after gmpm_set_query_bounds declared the "
+                                                "scene's rigid geometry (cfg-2: none, 0 boxes), so only the candidate count "
+                                                "crosses PCIe"},
                 "gpu_launches": launches_all, "gpu_launches_per_step": launches_all / K / world,
                 "roofline": roofline, "kernels": kern, "parity": parity}
         if mig is not None:

@@ -53,7 +53,7 @@ PLAIN_SYMBOLS = ["gmpm_default_params", "gmpm_last_error", "gmpm_version", "gmpm
                  "gmpm_radix_sort_pairs_static_scratch"]
 TYPED_SYMBOLS = ["create", "destroy", "add_qr_cloth", "finalize", "rebuild_mapping", "calc_fem", "p2g",
                  "update_grid", "g2p", "sync", "sync_particle_state_to_cpu", "sync_particle_state_to_cpu_async",
-                 "positions_host", "set_query_bounds", "add_particles", "migrate_out", "migrate_in", "n_volumetric", "clear_query_bounds", "snapshot_d2h_bytes", "halo_flags", "halo_plan_async", "halo_reset_plan", "halo_pack", "halo_unpack", "halo_peer_init", "halo_peer_window", "halo_peer_attach", "halo_peer_send", "halo_peer_recv", "update_grid_part", "g2p_part", "stream", "halo_stream", "copy_contact_pairs",
+                 "positions_host", "set_query_bounds", "add_particles", "migrate_out", "migrate_in", "migrate_count", "n_volumetric", "clear_query_bounds", "snapshot_d2h_bytes", "halo_flags", "halo_plan_async", "halo_reset_plan", "halo_pack", "halo_unpack", "halo_peer_init", "halo_peer_window", "halo_peer_attach", "halo_peer_send", "halo_peer_recv", "update_grid_part", "g2p_part", "stream", "halo_stream", "copy_contact_pairs",
                  "generate_contact_pairs", "run_driver_substeps", "set_driver_geometry_frozen", "update_contact", "reallocate_external_bodies", "external_body_force_to_host",
                  "dump_cpu_state", "n_verts", "n_faces", "n_particles", "n_cells", "num_contacts",
                  "grid_touched_cnt_host", "read", "checkpoint_bytes", "save_state", "load_state", "run_substeps", "kernel_launches", "set_profiling",
@@ -101,6 +101,7 @@ def _declare(L):
         g("add_particles").argtypes = [vp, vp, vp, vp, sz, C.POINTER(Material)]
         g("migrate_out").argtypes = [vp, C.c_int, ct, ct, vp, vp, vp, sz, C.POINTER(C.c_size_t)]
         g("migrate_in").argtypes = [vp, vp, sz, vp]
+        g("migrate_count").argtypes = [vp, C.c_int, ct, ct, vp, sz, vp, C.POINTER(C.c_size_t)]
         g("n_volumetric").argtypes = [vp]
         g("n_volumetric").restype = sz
         g("finalize").argtypes = [vp]

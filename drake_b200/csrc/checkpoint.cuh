@@ -4,7 +4,9 @@
 // DumpCpuState returns vertex positions and indices only (cuda_mpm_model.cu:245-265) -- velocities, the
 // affine matrices and the deformation gradients are lost.  A checkpoint here is one host blob in the
 // REFERENCE's layout and visible particle order (so it does not depend on the physical order the library
-// happens to keep): header, positions[3N] velocities[3N] volumes[N] affine[9N] F[9F] Dm_inv[4F] particle_F[9Nv] pids[N].
+// happens to keep): header, positions[3N] velocities[3N] volumes[N] affine[9N] F[9F] Dm_inv[4F] particle_F[9Nv] pids[N]
+// material_index[Nv] (bytes, by particle id like particle_F, padded to 8: a migration rewrites the material index of
+// the slot an arrival takes, so it is state, not something the AddParticles calls of the rebuilt scene reproduce).
 // Loading needs a finalized state built from the same meshes (same N, F, scalar); the run then continues
 // with the same arithmetic on a different physical order, i.e. equal to summation-order rounding.
 #pragma once
@@ -13,7 +15,7 @@
 namespace gmpm {
 
 struct CheckpointHeader {
-  char magic[8];          // "GMPMCKP2"
+  char magic[8];          // "GMPMCKP3" (2: without the material indices)
   uint32_t scalar_bytes;  // 4 or 8
   uint32_t domain_bits;
   uint64_t N, n_verts, n_faces, n_vol;
@@ -45,7 +47,8 @@ __global__ void iota_kernel(uint32_t n, int* __restrict__ out) {
 
 template <typename T>
 size_t State<T>::checkpoint_bytes() const {
-  return sizeof(CheckpointHeader) + sizeof(T) * (16 * N + 13 * n_faces + 9 * n_vol) + sizeof(int) * N;
+  return sizeof(CheckpointHeader) + sizeof(T) * (16 * N + 13 * n_faces + 9 * n_vol) + sizeof(int) * N +
+         ((n_vol + 7) & ~(size_t)7);
 }
 
 template <typename T>
@@ -54,7 +57,7 @@ size_t State<T>::save_state(void* out, size_t cap) {
   const size_t total = checkpoint_bytes();
   if (!out || cap < total) throw std::invalid_argument("gmpm_save_state: buffer too small (see gmpm_checkpoint_bytes)");
   CheckpointHeader h{};
-  std::memcpy(h.magic, "GMPMCKP2", 8);
+  std::memcpy(h.magic, "GMPMCKP3", 8);
   h.scalar_bytes = sizeof(T);
   h.domain_bits = (uint32_t)k.domain_bits;
   h.N = N;
@@ -68,6 +71,12 @@ size_t State<T>::save_state(void* out, size_t cap) {
   for (const char* name : {"positions", "velocities", "volumes", "affine_matrices", "deformation_gradients",
                            "Dm_inverses", "particle_F", "pids"})
     p += read(name, p, cap - (size_t)(p - static_cast<char*>(out)));
+  {
+    const size_t padded = (n_vol + 7) & ~(size_t)7;
+    std::memset(p, 0, padded);
+    if (n_vol) to_host(p, mat_id, n_vol);
+    p += padded;
+  }
   if ((size_t)(p - static_cast<char*>(out)) != total) throw std::runtime_error("gmpm_save_state: size mismatch");
   return total;
 }
@@ -78,7 +87,9 @@ void State<T>::load_state(const void* in, size_t bytes) {
   if (!in || bytes < sizeof(CheckpointHeader)) throw std::invalid_argument("gmpm_load_state: not a checkpoint");
   CheckpointHeader h;
   std::memcpy(&h, in, sizeof(h));
-  if (std::memcmp(h.magic, "GMPMCKP2", 8) != 0) throw std::invalid_argument("gmpm_load_state: bad magic");
+  if (std::memcmp(h.magic, "GMPMCKP2", 8) == 0)
+    throw std::invalid_argument("gmpm_load_state: version-2 checkpoint (no material indices): save it again with this library");
+  if (std::memcmp(h.magic, "GMPMCKP3", 8) != 0) throw std::invalid_argument("gmpm_load_state: bad magic");
   if (h.scalar_bytes != sizeof(T) || h.N != N || h.n_verts != n_verts || h.n_faces != n_faces || h.n_vol != n_vol ||
       h.domain_bits != (uint32_t)k.domain_bits || bytes != checkpoint_bytes())
     throw std::invalid_argument("gmpm_load_state: the checkpoint was taken from a different scene (sizes, scalar or grid)");
@@ -100,6 +111,12 @@ void State<T>::load_state(const void* in, size_t bytes) {
       seen[(size_t)q] = 1;
     }
   }
+  const uint8_t* h_mat = reinterpret_cast<const uint8_t*>(p + sizeof(T) * (16 * N + 13 * n_faces + 9 * n_vol) + sizeof(int) * N);
+  for (size_t q = 0; q < n_vol; ++q)
+    if (h_mat[q] >= materials.size())
+      throw std::invalid_argument("gmpm_load_state: the checkpoint refers to material " + std::to_string((int)h_mat[q]) +
+                                  " but this state has " + std::to_string(materials.size()) +
+                                  " registered (rebuild the scene with the same AddParticles materials, in the same order)");
   // one staging upload, then layout conversion on the device (slot = visible index)
   const size_t payload = bytes - sizeof(h);
   char* stage = static_cast<char*>(io(payload));
@@ -131,7 +148,10 @@ void State<T>::load_state(const void* in, size_t bytes) {
     launches += 3;
   }
   if (n_vol)  // deformation gradients of the volumetric particles: by particle id on both sides
+  {
     GMPM_CUDA(cudaMemcpyAsync(Fv, s_Fv, sizeof(T) * 9 * n_vol, cudaMemcpyDeviceToDevice, stream));
+    GMPM_CUDA(cudaMemcpyAsync(mat_id, reinterpret_cast<const uint8_t*>(s_pid + N), n_vol, cudaMemcpyDeviceToDevice, stream));
+  }
   launches += 4;
   GMPM_CUDA(cudaGetLastError());
   GMPM_CUDA(cudaStreamSynchronize(stream));  // the host blob and ht are borrowed

@@ -277,6 +277,10 @@ int gmpm_radix_sort_pairs_static_scratch(const uint32_t* keys_in_dev, const uint
       if (n) *n = c;                                                                                           \
     });                                                                                                        \
   }                                                                                                            \
+  int gmpm_migrate_count_##SUF(gmpm_state_##SUF* s, int axis, T lo, T hi, const double* edges, size_t n_edges, \
+                               size_t* leavers, size_t* n_free) {                                              \
+    return guarded([&] { s->st.migrate_count(axis, lo, hi, edges, n_edges, leavers, n_free); });               \
+  }                                                                                                            \
   int gmpm_migrate_in_##SUF(gmpm_state_##SUF* s, const T* records, size_t n, int* pids) {                      \
     return guarded([&] { s->st.migrate_in(records, n, pids); });                                               \
   }                                                                                                            \

@@ -1259,6 +1259,13 @@ g2p_kernel(uint32_t N, const uint32_t* __restrict__ order, const WorkRec* __rest
           if (ii) Mx[a] += (T(ii) * wx) * s00[a];
         }
       }
+      // an inactive spare of the migration (volumetric, rest volume 0) does not follow the flow: it keeps its
+      // parking point, with zero velocity and affine matrix, so the spares stay scattered and inside the blocks
+      // this rank exchanges
+      if ((uint32_t)p >= n_cloth && !(pvol > T(0))) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) nv[a] = Mx[a] = My[a] = Mz[a] = T(0);
+      }
       T S[9];
 #pragma unroll
       for (int a = 0; a < 3; ++a) {

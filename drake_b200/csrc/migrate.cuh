@@ -111,6 +111,61 @@ __global__ void migrate_in_kernel(uint32_t n, uint32_t N, uint32_t n_cloth, cons
   out_pid[i] = (int)p;
 }
 
+// Dry run of a migration (changes nothing): how many active volumetric particles lie outside [lo, hi), by the slab
+// that would receive them (destination = number of edges <= x, the owner_of() of slab.py), and how many inactive
+// slots this state has left.  out[0 .. n_edges] = leavers per destination, out[n_edges + 1] = free slots.
+constexpr int kMigrateMaxEdges = 63;
+struct MigrateEdges {
+  double e[kMigrateMaxEdges];
+};
+template <typename T>
+__global__ void migrate_count_kernel(uint32_t N, uint32_t n_cloth, int axis, T lo, T hi, MigrateEdges edges, int n_edges,
+                                     const int* __restrict__ pid, const T* __restrict__ pos, const T* __restrict__ vol,
+                                     uint32_t* __restrict__ out) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  bool is_free = false;
+  if (s < N && (uint32_t)pid[s] >= n_cloth) {
+    if (!(vol[s] > T(0))) {
+      is_free = true;
+    } else {
+      const T x = pos[(size_t)axis * N + s];
+      if (!(x >= lo && x < hi)) {
+        int d = 0;
+        while (d < n_edges && edges.e[d] <= (double)x) ++d;
+        atomicAdd(out + d, 1u);  // leavers are few
+      }
+    }
+  }
+  const int n_free = __syncthreads_count(is_free);  // spares are many: one atomic per CTA
+  if (threadIdx.x == 0 && n_free) atomicAdd(out + n_edges + 1, (uint32_t)n_free);
+}
+
+template <typename T>
+void State<T>::migrate_count(int axis, T lo, T hi, const double* edges, size_t n_edges, size_t* leavers, size_t* n_free) {
+  require_finalized();
+  if (axis < 0 || axis > 2) throw std::invalid_argument("migrate_count: axis must be 0, 1 or 2");
+  if (n_edges > (size_t)kMigrateMaxEdges) throw std::invalid_argument("migrate_count: at most 63 slab edges");
+  if ((n_edges && !edges) || !leavers || !n_free) throw std::invalid_argument("migrate_count: null argument");
+  for (size_t d = 0; d <= n_edges; ++d) leavers[d] = 0;
+  *n_free = 0;
+  if (!n_vol) return;
+  MigrateEdges e{};
+  for (size_t d = 0; d < n_edges; ++d) {
+    e.e[d] = edges[d];
+    if (d && !(e.e[d] >= e.e[d - 1])) throw std::invalid_argument("migrate_count: edges must ascend");
+  }
+  uint32_t* d_out = static_cast<uint32_t*>(io(sizeof(uint32_t) * (kMigrateMaxEdges + 2)));
+  GMPM_CUDA(cudaMemsetAsync(d_out, 0, sizeof(uint32_t) * (n_edges + 2), stream));
+  launch("migrate_count");
+  migrate_count_kernel<T><<<blocks_for(N), kThreads, 0, stream>>>((uint32_t)N, n_cloth(), axis, lo, hi, e, (int)n_edges,
+                                                                 pid[cur], pos[cur], vol[cur], d_out);
+  GMPM_CUDA(cudaGetLastError());
+  uint32_t h[kMigrateMaxEdges + 2];
+  to_host(h, d_out, sizeof(uint32_t) * (n_edges + 2));
+  for (size_t d = 0; d <= n_edges; ++d) leavers[d] = h[d];
+  *n_free = h[n_edges + 1];
+}
+
 template <typename T>
 void State<T>::invalidate_after_particle_edit() {
   keys_valid = bin_valid = fem_valid = vis_keys_valid = false;
@@ -172,6 +227,16 @@ void State<T>::migrate_in(const T* records, size_t n, int* pids_out) {
   if (!n) return;
   if (!records) throw std::invalid_argument("migrate_in: null records");
   if (!n_vol) throw std::invalid_argument("migrate_in: the state holds no volumetric particles (no spare slots)");
+  // the material index of a record is an index into THIS state's table (it is rank-local: all states of a scene
+  // must register their materials in the same order); an index outside the table would read past the kernel's
+  // by-value material array
+  for (size_t i = 0; i < n; ++i) {
+    const double m = (double)records[i * kMigrateRecord + 25];
+    if (!(m >= 0.0) || m >= (double)materials.size() || m != std::floor(m))
+      throw std::invalid_argument("migrate_in: record " + std::to_string(i) + " carries material index " +
+                                  std::to_string(m) + " but this state has " + std::to_string(materials.size()) +
+                                  " material(s) registered (all states of a scene must add their materials in the same order)");
+  }
   char* buf = static_cast<char*>(io(16 + sizeof(uint32_t) * N + sizeof(T) * kMigrateRecord * n + sizeof(int) * n));
   uint32_t* d_count = reinterpret_cast<uint32_t*>(buf);
   uint32_t* d_slots = reinterpret_cast<uint32_t*>(buf + 16);

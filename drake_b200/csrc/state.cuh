@@ -551,7 +551,9 @@ struct State {
     {
       const char* v = std::getenv("GMPM_P2G");  // A/B switch: "tile" (round-1 kernel), "col", "colbulk"
       p2g_variant = !v ? kP2GDefault : !std::strcmp(v, "tile") ? 0 : !std::strcmp(v, "col") ? 1
-                                       : !std::strcmp(v, "colbulk") ? 2 : 3;
+                                       : !std::strcmp(v, "colbulk") ? 2 : !std::strcmp(v, "pair") ? 3 : -1;
+      if (p2g_variant < 0)
+        throw std::invalid_argument(std::string("GMPM_P2G=") + v + " is not a P2G variant (tile, col, colbulk, pair)");
       const void* fn = p2g_variant == 0 ? (const void*)p2g_tile_kernel<T>
                        : p2g_variant == 1 ? (const void*)p2g_col_kernel<T, false>
                        : p2g_variant == 2 ? (const void*)p2g_col_kernel<T, true> : (const void*)p2g_pair_kernel<T>;
@@ -1513,6 +1515,7 @@ struct State {
   void invalidate_after_particle_edit();                 // migrate.cuh
   size_t migrate_out(int axis, T lo, T hi, const T* park, T* records, int* pids_out, size_t cap);
   void migrate_in(const T* records, size_t n, int* pids_out);
+  void migrate_count(int axis, T lo, T hi, const double* edges, size_t n_edges, size_t* leavers, size_t* n_free);
   size_t checkpoint_bytes() const;                       // checkpoint.cuh
   size_t save_state(void* out, size_t cap);
   void load_state(const void* in, size_t bytes);

@@ -327,6 +327,15 @@ class GpuMpmState:
                                      cap, C.byref(n)))
         return rec[:n.value].copy(), pids[:n.value].copy()
 
+    def migrate_count(self, axis, lo, hi, edges):
+        """Extension: dry run of migrate_out.  -> (leavers per destination slab (len(edges) + 1,), free slots)."""
+        e = np.ascontiguousarray(edges, np.float64).reshape(-1)
+        out = np.zeros(e.size + 1, np.uint64)
+        free = C.c_size_t()
+        check(self._f("migrate_count")(self._h, int(axis), self._ct(lo), self._ct(hi), _ptr(e), e.size, _ptr(out),
+                                       C.byref(free)))
+        return out.astype(np.int64), int(free.value)
+
     def migrate_in(self, records):
         """Extension: the records take over inactive particles (volume 0).  -> the local particle ids they took."""
         rec = np.ascontiguousarray(records, self.dtype).reshape(-1, self.MIGRATE_RECORD)

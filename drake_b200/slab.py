@@ -336,6 +336,11 @@ def owner_of(x, edges):
     return np.searchsorted(np.asarray(edges, np.float64), np.asarray(x, np.float64), side="right")
 
 
+class MigrationOverflow(RuntimeError):
+    """Raised by every rank alike, before any particle was taken out of a state, when some slab has fewer spare
+    slots than particles heading for it."""
+
+
 class SlabMigrator:
     """Keeps the volumetric particles of ONE rank inside its slab [edges[rank-1] - margin, edges[rank] + margin).
 
@@ -385,8 +390,38 @@ class SlabMigrator:
         self.moved_in += len(pids)
         return len(pids)
 
+    def check_room(self):
+        """Collective dry run: every rank counts its leavers per destination and its free slots (migrate_count, nothing
+        is changed), the counts are gathered, and EVERY rank raises MigrationOverflow -- from the same numbers, so
+        together -- if some destination cannot seat its arrivals.  Without this a short destination would fail alone,
+        after the sources had already parked the leavers, and the other ranks would hang in the next collective.
+        Also grows this rank's record buffer so that one migrate_out call takes all its leavers."""
+        lo, hi = self.bounds()
+        leavers, free = self.state.migrate_count(self.axis, lo, hi, self.edges)
+        row = np.concatenate([[self.rank, free], leavers]).astype(np.float64)[None, :]
+        if getattr(self.all_gather, "packed", False):
+            if row.shape[1] > 28:
+                raise ValueError("the packed transport carries at most 26 slabs")
+            table = self.all_gather(np.pad(row, ((0, 0), (0, 28 - row.shape[1]))))[:, :row.shape[1]]
+        else:
+            table = np.concatenate(self.all_gather(row))
+        table = table[np.argsort(table[:, 0])]
+        free_of, out_of = table[:, 1], table[:, 2:].sum(axis=1)
+        arrivals = table[:, 2:].sum(axis=0)
+        # a destination's own leavers free their slots before the arrivals are seated (extract runs before insert)
+        short = np.nonzero(arrivals > free_of + out_of)[0]
+        if len(short):
+            d = int(short[0])
+            raise MigrationOverflow("slab %d would receive %d particles but has %d free slots (+%d of its own leaving): "
+                                    "nothing was moved; create the states with more spare particles, migrate more often "
+                                    "or move the slab edges" % (d, arrivals[d], free_of[d], out_of[d]))
+        self.cap = max(self.cap, int(leavers.sum()))
+        return table
+
     def migrate(self):
         import time
+        if self.all_gather is not None:
+            self.check_room()
         t0 = time.perf_counter()
         out = self.extract()
         t1 = time.perf_counter()
@@ -450,6 +485,17 @@ def dist_all_gather_packed(device, group=None):
 
 def migrate_in_process(migrators, exchange=None):
     """The same for several states living in one process (tests).  Returns the number of particles moved."""
+    rows = []
+    for m in migrators:     # the dry run of SlabMigrator.check_room, all ranks at hand
+        lo, hi = m.bounds()
+        leavers, free = m.state.migrate_count(m.axis, lo, hi, m.edges)
+        rows.append((free, leavers))
+        m.cap = max(m.cap, int(leavers.sum()))
+    arrivals = np.sum([lv for _, lv in rows], axis=0)
+    for d, (free, leavers) in enumerate(rows):
+        if arrivals[d] > free + leavers.sum():
+            raise MigrationOverflow("slab %d would receive %d particles but has %d free slots: nothing was moved"
+                                    % (d, arrivals[d], free))
     parcels = [m.extract() for m in migrators]
     for m in migrators:
         m.insert(parcels)

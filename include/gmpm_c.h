@@ -141,6 +141,15 @@ int gmpm_device_sync(void);
   int gmpm_migrate_out_##SUF(gmpm_state_##SUF* s, int axis, T lo, T hi, const T* park, T* records,  \
                              int* pids, size_t cap, size_t* n);                                     \
   int gmpm_migrate_in_##SUF(gmpm_state_##SUF* s, const T* records, size_t n, int* pids);            \
+  /* Dry run of migrate_out, so that a migration can be refused BEFORE anything is taken out of a     */\
+  /* state (migrate_out destroys the leavers at the source; if their destination then has no spare   */\
+  /* slot left they are lost).  Changes nothing.  leavers[0 .. n_edges] <- the number of active       */\
+  /* volumetric particles outside [lo, hi) -- NOT limited by any cap, unlike what one migrate_out     */\
+  /* call returns -- split by destination slab: destination d = the number of edges <= the particle's */\
+  /* coordinate (edges[n_edges] ascending, doubles, <= 63).  *n_free <- inactive slots of this state.     */\
+  /* The host sums the leavers per destination over all ranks and compares with n_free there.         */\
+  int gmpm_migrate_count_##SUF(gmpm_state_##SUF* s, int axis, T lo, T hi, const double* edges,       \
+                               size_t n_edges, size_t* leavers, size_t* n_free);                      \
   /* GpuMpmState<T>::Finalize, cuda_mpm_model.cu:36-122 (+ initialize_fem_state_kernel) */          \
   int gmpm_finalize_##SUF(gmpm_state_##SUF* s);                                                     \
   /* GpuMpmSolver<T>::RebuildMapping, cuda_mpm_solver.cu:18-70 */                                   \

@@ -70,6 +70,7 @@ template <typename T> struct Abi;
     static constexpr auto add_particles = gmpm_add_particles_##SUF;                                  \
     static constexpr auto migrate_out = gmpm_migrate_out_##SUF;                                      \
     static constexpr auto migrate_in = gmpm_migrate_in_##SUF;                                        \
+    static constexpr auto migrate_count = gmpm_migrate_count_##SUF;                                  \
     static constexpr auto finalize = gmpm_finalize_##SUF;                                            \
     static constexpr auto rebuild_mapping = gmpm_rebuild_mapping_##SUF;                              \
     static constexpr auto calc_fem = gmpm_calc_fem_##SUF;                                            \
@@ -164,6 +165,13 @@ struct GpuMpmState {
     records->resize(n * 26);
     pids->resize(n);
     return n;
+  }
+  // Dry run of MigrateOut (changes nothing): leavers per destination slab (edges.size() + 1 entries) and, in
+  // *n_free, the inactive slots of this state.  Sum the leavers over the ranks before calling MigrateOut anywhere.
+  std::vector<size_t> MigrateCount(int axis, T lo, T hi, const std::vector<double>& edges, size_t* n_free) {
+    std::vector<size_t> leavers(edges.size() + 1);
+    internal::Check(Abi::migrate_count(raw(), axis, lo, hi, edges.data(), edges.size(), leavers.data(), n_free), "MigrateCount");
+    return leavers;
   }
   std::vector<int> MigrateIn(const std::vector<T>& records) {
     std::vector<int> pids(records.size() / 26);

@@ -232,6 +232,19 @@ class OracleMpm:
         n = self._f("migrate_out")(self.h, int(axis), self.ct(lo), self.ct(hi), _ptr(park), _ptr(rec), _ptr(pids), cap)
         return rec[:n].copy(), pids[:n].copy()
 
+    def migrate_count(self, axis, lo, hi, edges):
+        """Dry run of migrate_out (restates migrate_count_kernel of drake_b200/csrc/migrate.cuh): leavers per
+        destination slab (destination = number of edges <= x) and the number of inactive slots."""
+        n_cloth = self.n_faces + self.n_verts
+        volumetric = np.asarray(self.read("pids")) >= n_cloth
+        x = np.asarray(self.read("positions")).reshape(-1, 3)[:, axis]
+        vol = np.asarray(self.read("volumes"))
+        lo, hi = self.dtype.type(lo), self.dtype.type(hi)
+        leaves = volumetric & (vol > 0) & ~((x >= lo) & (x < hi))
+        edges = np.asarray(edges, np.float64).reshape(-1)
+        dest = np.searchsorted(edges, x[leaves].astype(np.float64), side="right")
+        return np.bincount(dest, minlength=len(edges) + 1).astype(np.int64), int((volumetric & ~(vol > 0)).sum())
+
     def migrate_in(self, records):
         rec = np.ascontiguousarray(records, self.dtype).reshape(-1, 26)
         pids = np.zeros(rec.shape[0], np.int32)
