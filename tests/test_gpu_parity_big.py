@@ -73,7 +73,8 @@ def test_cfg2_1m_one_and_twenty_substeps_vs_oracle_and_reference_kernels(dtype, 
     refget = (lambda name: ref.read(name, sizes[name])) if ref is not None else None
 
     def check(tol, tag):
-        assert_particles_close(st.read, orc.read, tol, (tag, "ours vs CPU oracle"))
+        # element-wise bar: 100 x the norm-wise one, every component against max(|itself|, 1e-4 x the field's scale)
+        assert_particles_close(st.read, orc.read, tol, (tag, "ours vs CPU oracle"), elementwise_tol=100 * tol if dtype == np.float64 else np.inf)   # fp32: recorded, not asserted
         for name in ("pids", "index_mappings"):   # (sort_keys of the OpenMP port are one substep old: compared below)
             assert np.array_equal(st.read(name), orc.read(name)), (tag, name)
         if ref is not None:
@@ -101,6 +102,40 @@ def test_cfg2_1m_one_and_twenty_substeps_vs_oracle_and_reference_kernels(dtype, 
             assert np.array_equal(st.read(name), orc.read(name)), name
     if ref is not None:
         ref.close()
+    orc.close()
+    st.Destroy()
+    # the measured figures, for profiles/ (the GPU box returns gpurun_out/)
+    import json
+    import os
+    import test_gpu_parity as tgp
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, "parity_elementwise_%s.json" % np.dtype(dtype).name), "w") as f:
+            json.dump([{"case": t, "field": n, "norm_wise": r, "element_wise": e, "floor": tgp.ELEMENTWISE_FLOOR}
+                       for t, n, r, e in tgp.ELEMENTWISE_LOG], f, indent=1)
+    tgp.ELEMENTWISE_LOG.clear()
+
+
+def test_cfg2_1m_hundred_substeps_vs_oracle():
+    """north_star's second fp64 bar AT THE HEADLINE SIZE (VERDICT r02 "What's weak" 1: it was held at 29 602 particles
+    only): 1e-6 relative after 100 substeps of cfg-2, 1 006 468 particles, the bench's own loop (re-sort every 40th
+    substep), against the CPU oracle; integer state bit-equal; the element-wise figure held to 100 x the bar."""
+    dtype = np.float64
+    st, sv, orc, _ = build(dtype, 34, with_ref=False)
+    assert st.n_particles() == 1006468
+    for i in range(100):
+        s = i % 40 == 0
+        sv.RebuildMapping(st, s); sv.CalcFemStateAndForce(st, DT); sv.ParticleToGrid(st, DT)
+        sv.UpdateGrid(st, -1); sv.GridToParticle(st, DT)
+        if s:
+            orc.RebuildMapping(True)
+        orc.substep_omp(DT, -1, THREADS)
+    assert_particles_close(st.read, orc.read, 1e-6, "100 substeps at 1M", elementwise_tol=1e-4)
+    for name in ("pids", "index_mappings"):
+        assert np.array_equal(st.read(name), orc.read(name)), name
+    import test_gpu_parity as tgp
+    print("element-wise / norm-wise after 100 substeps:", [(n, r, e) for _, n, r, e in tgp.ELEMENTWISE_LOG])
+    tgp.ELEMENTWISE_LOG.clear()
     orc.close()
     st.Destroy()
 
