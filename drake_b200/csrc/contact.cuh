@@ -253,28 +253,57 @@ __device__ __forceinline__ void phase_clean(const ContactArgs<T>& a, uint32_t n_
 
 // K13 contact_particle_to_grid_kernel<JACOBI=true> (:1042-1215): per-contact Jacobian row (R_CW w_ip,
 // implicit), local impulse and Hessian block, rotated to world and lumped onto the 27 nodes.
+//
+// Warp merge before the scatter (the reference's scheme, :1077-1083, :1169, :1196, same as its P2G :448-523):
+// the lanes of a warp hold CONSECUTIVE contacts, and consecutive contacts are particles that are neighbours in the
+// visible order (cell order after a sort, mesh rows before), so runs of lanes share a base cell and with it all 27
+// destination nodes.  The 12 Hess/Grad scalars of a node are summed over each run with a segmented shuffle
+// reduction and only the run's first lane issues the atomics.  Unlike upstream the contacts are not re-sorted
+// for this (the merge takes the runs the pair order already has); a warp without any run skips the shuffles.
 template <typename T>
 __device__ __forceinline__ void phase_contact_p2g(const ContactArgs<T>& a, uint32_t tid, uint32_t nth) {
-  for (uint32_t i = tid; i < a.n; i += nth) {
-    const T x[3] = {a.pos[i * 3], a.pos[i * 3 + 1], a.pos[i * 3 + 2]};
-    uint32_t base[3];
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t rounds = (a.n + nth - 1) / nth;  // uniform trip count: the shuffles need all lanes
+  for (uint32_t r = 0; r < rounds; ++r) {
+    const uint32_t i = r * nth + tid;
+    const bool valid = i < a.n;
+    uint32_t base[3] = {0u, 0u, 0u};
     T w[3][3];
-    stencil(x, a.k, base, w);
-    ContactFrame<T> f;
-    load_frame(a, i, f);
-    const T vr[3] = {a.vel[i * 3] - a.rigid_v[i * 3], a.vel[i * 3 + 1] - a.rigid_v[i * 3 + 1],
-                     a.vel[i * 3 + 2] - a.rigid_v[i * 3 + 2]};
-    T vn[3], CH[9], CG[3];
-    mul33v(f.R, vr, vn);
-    contact_grad_hess(a.epsv, f.phi0, a.dt, a.stiffness, a.damping, a.mu, f.v0, vn, CH, CG);
-    T WG[3], tmp[9], WH[9], Rt[9];
+    T WG[3], WH[9];
+    T mass = T(0);
 #pragma unroll
-    for (int r = 0; r < 3; ++r)
+    for (int q = 0; q < 3; ++q) w[q][0] = w[q][1] = w[q][2] = T(0);
 #pragma unroll
-      for (int c = 0; c < 3; ++c) Rt[r * 3 + c] = f.R[c * 3 + r];
-    mul33v(Rt, CG, WG);
-    mul33(Rt, CH, tmp);
-    mul33(tmp, f.R, WH);
+    for (int e = 0; e < 9; ++e) WH[e] = T(0);
+    WG[0] = WG[1] = WG[2] = T(0);
+    if (valid) {
+      const T x[3] = {a.pos[i * 3], a.pos[i * 3 + 1], a.pos[i * 3 + 2]};
+      stencil(x, a.k, base, w);
+      ContactFrame<T> f;
+      load_frame(a, i, f);
+      mass = f.mass;
+      const T vr[3] = {a.vel[i * 3] - a.rigid_v[i * 3], a.vel[i * 3 + 1] - a.rigid_v[i * 3 + 1],
+                       a.vel[i * 3 + 2] - a.rigid_v[i * 3 + 2]};
+      T vn[3], CH[9], CG[3];
+      mul33v(f.R, vr, vn);
+      contact_grad_hess(a.epsv, f.phi0, a.dt, a.stiffness, a.damping, a.mu, f.v0, vn, CH, CG);
+      T tmp[9], Rt[9];
+#pragma unroll
+      for (int rr = 0; rr < 3; ++rr)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) Rt[rr * 3 + c] = f.R[c * 3 + rr];
+      mul33v(Rt, CG, WG);
+      mul33(Rt, CH, tmp);
+      mul33(tmp, f.R, WH);
+    }
+    // runs of equal base cell among the lanes (a lane without a contact is a run of its own)
+    const uint32_t mykey = valid ? cell_key(base[0], base[1], base[2]) : (0xFFFFFFFFu - lane);
+    const uint32_t prevkey = __shfl_up_sync(kFullMask, mykey, 1);
+    const bool head = lane == 0u || prevkey != mykey;
+    const uint32_t heads = __ballot_sync(kFullMask, head);
+    const bool merge = heads != kFullMask;                                   // warp-uniform
+    const uint32_t above = lane == 31u ? 0u : (heads & ~((2u << lane) - 1u));  // run heads after this lane
+    const uint32_t span = (above ? (uint32_t)__ffs((int)above) - 1u : 32u) - lane;  // lanes from here to the run's end
 #pragma unroll
     for (int ii = 0; ii < 3; ++ii)
 #pragma unroll
@@ -282,15 +311,31 @@ __device__ __forceinline__ void phase_contact_p2g(const ContactArgs<T>& a, uint3
 #pragma unroll
         for (int kk = 0; kk < 3; ++kk) {
           const T wt = w[ii][0] * w[jj][1] * w[kk][2];
-          const uint32_t key = cell_key(base[0] + ii, base[1] + jj, base[2] + kk);
-          const size_t slot = a.cb_slot[key >> 6];
-          const uint32_t l = key & 63u;
-          T* H = a.Hess + slot * (9 * 64) + l;
-          T* G = a.Grad + slot * (3 * 64) + l;
+          T val[12];
 #pragma unroll
-          for (int e = 0; e < 9; ++e) atomicAdd(H + e * 64, f.mass * wt * wt * WH[e]);
+          for (int e = 0; e < 9; ++e) val[e] = mass * wt * wt * WH[e];
 #pragma unroll
-          for (int d = 0; d < 3; ++d) atomicAdd(G + d * 64, f.mass * wt * WG[d]);
+          for (int d = 0; d < 3; ++d) val[9 + d] = mass * wt * WG[d];
+          if (merge) {
+#pragma unroll
+            for (int e = 0; e < 12; ++e)
+#pragma unroll
+              for (uint32_t o = 1; o < 32u; o <<= 1) {
+                const T t = __shfl_down_sync(kFullMask, val[e], o);
+                if (o < span) val[e] += t;
+              }
+          }
+          if (valid && head) {
+            const uint32_t key = cell_key(base[0] + ii, base[1] + jj, base[2] + kk);
+            const size_t slot = a.cb_slot[key >> 6];
+            const uint32_t l = key & 63u;
+            T* H = a.Hess + slot * (9 * 64) + l;
+            T* G = a.Grad + slot * (3 * 64) + l;
+#pragma unroll
+            for (int e = 0; e < 9; ++e) atomicAdd(H + e * 64, val[e]);
+#pragma unroll
+            for (int d = 0; d < 3; ++d) atomicAdd(G + d * 64, val[9 + d]);
+          }
         }
   }
 }
